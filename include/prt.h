@@ -1,0 +1,223 @@
+/*
+ * prt.h — C ABI of the B200-native path-tracing backend (libprt_b200.so).
+ *
+ * This is the drop-in boundary for ONE hot path of Rickyeeeeee/ParallelRayTracing:
+ *   camera ray -> closest hit -> shade/scatter -> accumulate
+ * i.e. what a `Renderer` backend does between `Init` and the hand-over of one
+ * sample buffer to `Film` (reference: src/core/renderer.h:8-16).
+ *
+ * Plain pointers and sizes only; no C++/torch types.  Every entry point returns an
+ * int status (0 = PRT_OK, <0 = PRT_ERR_*) and never throws.  A context is NOT
+ * thread-safe; it is driven from one host thread, like the reference's backends
+ * (main.cpp:194-549 calls everything from the GL thread).
+ *
+ * All citations are relative to the reference tree (/root/reference).
+ */
+#ifndef PRT_H
+#define PRT_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PRT_OK                0
+#define PRT_ERR_INVALID      -1  /* bad argument / call order            */
+#define PRT_ERR_CUDA         -2  /* a CUDA runtime call failed            */
+#define PRT_ERR_NO_DEVICE    -3  /* no usable sm_100 device               */
+#define PRT_ERR_OOM          -4  /* device allocation failed              */
+#define PRT_ERR_UNSUPPORTED  -5
+
+/* Material tags: identical numbering to MatType (src/core/material_handle.h:13-19). */
+#define PRT_MAT_NONE        0
+#define PRT_MAT_LAMBERTIAN  1
+#define PRT_MAT_METAL       2
+#define PRT_MAT_DIELECTRIC  3
+#define PRT_MAT_EMISSIVE    4
+
+/* Shape tags: identical numbering to ShapeType (src/core/shape.h:10-15). */
+#define PRT_SHAPE_SPHERE    0   /* "Circle" in the reference */
+#define PRT_SHAPE_QUAD      1
+#define PRT_SHAPE_TRIANGLE  2
+
+/* Sample partition of prt_render (multi-GPU sharding). */
+#define PRT_PARTITION_SAMPLES 0  /* this rank renders samples [sample_begin, sample_begin+spp) */
+
+typedef struct prt_ctx prt_ctx;
+
+/* One material.  Replaces the 4 material structs + MaterialHandle tag dispatch
+ * (src/core/material.h:11-161).  rgb = albedo (Lambertian, Metal) or emission
+ * (Emissive); param = roughness (Metal) or refraction index (Dielectric). */
+typedef struct prt_material {
+    int32_t type;
+    float   r, g, b;
+    float   param;
+    int32_t _pad[3];
+} prt_material;              /* 32 B */
+
+/* World-space sphere = reference `Circle` (shape.h:157-203) with its Transform baked in
+ * (uniform scale s): centre = Mat*(0,0,0), radius = r*s, tmin = kShapeRayTMin*s
+ * (shape.h:128 is in LOCAL units, primitive.cpp:30 re-normalises the local direction). */
+typedef struct prt_sphere {
+    float   cx, cy, cz, radius;
+    float   tmin;
+    int32_t material;        /* index into the material table                      */
+    int32_t prim_id;         /* index in the reference's primitive list (tie rule) */
+    int32_t _pad;
+} prt_sphere;                /* 32 B */
+
+/* World-space rectangle = reference `Quad` (shape.h:213-239; local y=0 plane, extent
+ * width x height along local x / z) with its Transform baked in. u, v, n are the unit
+ * images of local x, z, y. */
+typedef struct prt_quad {
+    float   cx, cy, cz, half_w;
+    float   ux, uy, uz, half_h;
+    float   vx, vy, vz, tmin;
+    float   nx, ny, nz;
+    int32_t material;
+    int32_t prim_id;
+    int32_t _pad[3];
+} prt_quad;                  /* 80 B */
+
+/* Camera = the fields Camera::GetCameraRay reads (src/core/camera.h:104-143).
+ * right = normalize(cross(front, (0,1,0))), up = normalize(cross(right, front))
+ * (camera.h:13-15); tan_half_fov = tan(0.5f) in the reference (camera.h:111). */
+typedef struct prt_camera {
+    float   pos[3];
+    float   front[3];
+    float   right[3];
+    float   up[3];
+    float   tan_half_fov;
+    int32_t width, height;
+} prt_camera;
+
+/* A ray of the fixed-batch parity interface. Direction must be unit length. */
+typedef struct prt_ray { float ox, oy, oz, dx, dy, dz; } prt_ray;
+
+/* Closest-hit record: prim_id = reference list index (or -1 = miss), t = world distance,
+ * (b1, b2) = triangle barycentrics (weights of v1, v2), front = IsFrontFace. */
+typedef struct prt_hit {
+    float   t;
+    int32_t prim_id;
+    float   b1, b2;
+    float   px, py, pz;      /* SurfaceInteraction::Position */
+    float   nx, ny, nz;      /* SurfaceInteraction::Normal (faces the ray) */
+    int32_t front;
+    int32_t material;
+} prt_hit;                   /* 48 B */
+
+#define PRT_MAX_DEPTH 32
+
+typedef struct prt_stats {
+    uint64_t rays_total;                  /* closest-hit queries of the last prt_render      */
+    uint64_t rays_per_bounce[PRT_MAX_DEPTH];
+    uint64_t paths;                       /* camera paths started                              */
+    uint64_t nodes_visited;               /* BVH nodes fetched   (only if counters enabled)    */
+    uint64_t prims_tested;                /* leaf primitives tested (only if counters enabled) */
+    float    render_ms;                   /* device time of the last prt_render (CUDA events)  */
+    float    extend_ms;                   /* device time in the extend kernels (if timed)      */
+    float    shade_ms;
+    float    build_ms;                    /* device time of the last prt_build_bvh             */
+    int32_t  kernel_launches;             /* kernels launched by the last prt_render           */
+    int32_t  n_prims;
+    int32_t  n_nodes;
+    int32_t  _pad;
+} prt_stats;
+
+/* ---- life cycle --------------------------------------------------------------------
+ * Replaces a backend's ctor/dtor + the allocation half of Init
+ * (cuda_wavefront/renderer.cu:351-370, 436-487). device = CUDA ordinal. */
+int  prt_create(prt_ctx** out, int device);
+void prt_destroy(prt_ctx* ctx);
+const char* prt_last_error(const prt_ctx* ctx);   /* ctx may be NULL: last global error */
+const char* prt_version(void);
+
+/* ---- scene -------------------------------------------------------------------------
+ * Replaces the scene-upload half of Init (cuda_wavefront/soa.cpp:37-114,
+ * cuda_megakernel/renderer.cu:276-355): the host scene is COPIED here, host pointers are
+ * never dereferenced on the device.
+ * Triangles = reference `Triangle` (shape.h:49-82) in world space: tri_verts = nt*9 floats
+ * (v0,v1,v2), tri_normals = nt*9 floats or NULL (flat geometric normals), tri_material =
+ * nt ints or NULL (all tri_material_default). Triangle i has prim_id tri_prim_base + i.
+ * sky_rgb = radiance of a miss (the reference hard-codes (0.4,0.3,0.6): cpu/renderer.h:31). */
+int  prt_set_scene(prt_ctx* ctx,
+                   const prt_sphere* spheres, int n_spheres,
+                   const prt_quad* quads, int n_quads,
+                   const float* tri_verts, const float* tri_normals,
+                   const int32_t* tri_material, int tri_material_default,
+                   int n_tris, int tri_prim_base,
+                   const prt_material* materials, int n_materials,
+                   const float sky_rgb[3]);
+
+/* GPU LBVH build over the current scene: primitive AABBs -> scene bounds -> 30-bit Morton
+ * codes -> stable LSD radix sort -> Karras hierarchy -> bottom-up refit.
+ * The reference has no acceleration structure (primitive.cpp:26 loops over every
+ * primitive); this replaces that loop. */
+int  prt_build_bvh(prt_ctx* ctx);
+
+/* Replaces SetCamera (cuda_wavefront/renderer.cu:534-547). Resizes the accumulation
+ * buffer (and clears it) when width/height change. */
+int  prt_set_camera(prt_ctx* ctx, const prt_camera* cam);
+
+/* ---- render ------------------------------------------------------------------------
+ * Replaces ProgressiveRender (cuda_wavefront/renderer.cu:372-433), batched: renders
+ * samples [sample_begin, sample_begin + spp) of every pixel (pixel centre, no jitter:
+ * cpu/renderer.cpp:45) with at most max_depth closest-hit queries per path
+ * (cpu/renderer.cpp:59-103 semantics) and ADDS them to the accumulation buffer.
+ * Synchronous, like the reference (cudaDeviceSynchronize at renderer.cu:429). */
+int  prt_render(prt_ctx* ctx, int spp, int max_depth, uint64_t seed, int sample_begin);
+
+/* Zero the accumulation buffer (Film::Clear, film.cu:25-35). */
+int  prt_clear_accum(prt_ctx* ctx);
+
+/* Multiply the accumulation buffer by s (used by the Renderer shim to hand Film a mean
+ * with weight k: Film::AddSampleBufferGPU adds rgb*weight, film.cu:79-88). */
+int  prt_scale_accum(prt_ctx* ctx, float s);
+
+/* Device pointer to the accumulation buffer: W*H*3 fp32, interleaved RGB, row-major,
+ * index 3*(y*W+x)+c — the layout Film::AddSampleBufferGPU consumes (film.h:26-29,
+ * film.cu:79-88). Holds the SUM of all samples since the last clear. */
+float* prt_accum_device_ptr(prt_ctx* ctx);
+/* Use caller-owned device memory (W*H*3 floats) as the accumulation buffer, e.g. a
+ * torch tensor that an NCCL reduce then operates on. NULL restores the internal one. */
+int  prt_set_accum_buffer(prt_ctx* ctx, float* device_rgb);
+/* Copy the accumulation buffer to host memory (W*H*3 floats). */
+int  prt_read_accum(prt_ctx* ctx, float* host_rgb);
+/* Samples per pixel accumulated since the last clear. */
+int  prt_accum_spp(const prt_ctx* ctx);
+
+/* ---- film resolve -----------------------------------------------
+ * accum/spp -> Reinhard -> gamma -> RGBA8, Film::UpdateDisplay semantics
+ * (film.cu:134-194). host_rgba: W*H*4 bytes. */
+int  prt_resolve_display(prt_ctx* ctx, float exposure, float gamma, uint8_t* host_rgba);
+
+/* ---- parity / introspection --------------------------------------------------------
+ * Closest hit for a fixed ray batch (host buffers). use_bvh=0 brute-forces all
+ * primitives on the GPU (the reference's own algorithm, primitive.cpp:21-59). */
+int  prt_trace_batch(prt_ctx* ctx, const prt_ray* rays, int n, prt_hit* out, int use_bvh);
+
+/* LBVH internals for the bit-exact integer checks. Any pointer may be NULL.
+ *   morton[n_prims]        30-bit code per primitive, input order
+ *   sorted_prim[n_prims]   primitive index (input order) at each sorted position
+ *   node_children[2*(n-1)] left,right per internal node; >=0 internal, <0 = ~leaf_pos
+ *   node_parent[n-1]       parent of each internal node (root: -1)
+ *   node_bounds[12*(n-1)]  left box min,max then right box min,max per internal node
+ *   scene_bounds[6]        min,max of all primitive AABBs */
+int  prt_debug_lbvh(prt_ctx* ctx, uint32_t* morton, uint32_t* sorted_prim,
+                    int32_t* node_children, int32_t* node_parent,
+                    float* node_bounds, float* scene_bounds);
+int  prt_num_prims(const prt_ctx* ctx);
+
+/* Enable per-ray traversal counters (nodes fetched / primitives tested); costs speed. */
+int  prt_enable_counters(prt_ctx* ctx, int on);
+int  prt_get_stats(prt_ctx* ctx, prt_stats* out);
+
+/* Tuning knobs (all optional): "wave_paths" (paths in flight per wave),
+ * "ctas_per_sm", "use_graph". Unknown keys -> PRT_ERR_INVALID. */
+int  prt_set_option(prt_ctx* ctx, const char* key, int64_t value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PRT_H */

@@ -1,0 +1,383 @@
+// lbvh.cu — GPU LBVH build: primitive AABBs -> scene bounds -> 30-bit Morton codes ->
+// stable LSD radix sort (8-bit digits) -> Karras 2012 hierarchy -> bottom-up refit ->
+// 64-byte two-child traversal nodes + leaf-slot-ordered triangle planes.
+//
+// The reference has no acceleration structure: PrimitiveList::Intersect loops over every
+// primitive (src/core/primitive.cpp:26). This build is what makes that loop O(log n).
+// Integer outputs (Morton codes, sorted order, topology) are bit-exact against the CPU
+// restatement in oracle/prt_oracle.cpp (tests/test_lbvh_gpu.py).
+#include "prt_internal.h"
+
+namespace prt {
+
+// ------------------------------------------------------------------ helpers
+__device__ __forceinline__ int f2ord(float f) { int i = __float_as_int(f); return i >= 0 ? i : i ^ 0x7fffffff; }
+__device__ __forceinline__ float ord2f(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
+
+__global__ void k_init_bounds(int* b) {
+    if (threadIdx.x < 3) b[threadIdx.x] = 0x7fffffff;           // min = +max ordered
+    else if (threadIdx.x < 6) b[threadIdx.x] = (int)0x80000000; // max = lowest ordered
+}
+
+// AABB of primitive q (input order: spheres, quads, triangles). The exact expression
+// order is part of the bit-exact contract with the oracle.
+__global__ void k_prim_bounds(const SphereRec* __restrict__ spheres, int ns,
+                              const QuadRec* __restrict__ quads, int nq,
+                              const float4* __restrict__ tri_v, int nt,
+                              float4* __restrict__ amin, float4* __restrict__ amax,
+                              int* __restrict__ bounds) {
+    int n = ns + nq + nt;
+    int q = blockIdx.x * blockDim.x + threadIdx.x;
+    float lo[3] = {__int_as_float(0x7f800000), __int_as_float(0x7f800000), __int_as_float(0x7f800000)};
+    float hi[3] = {__int_as_float(0xff800000), __int_as_float(0xff800000), __int_as_float(0xff800000)};
+    if (q < n) {
+        if (q < ns) {
+            float4 a = spheres[q].a;
+            lo[0] = a.x - a.w; lo[1] = a.y - a.w; lo[2] = a.z - a.w;
+            hi[0] = a.x + a.w; hi[1] = a.y + a.w; hi[2] = a.z + a.w;
+        } else if (q < ns + nq) {
+            QuadRec r = quads[q - ns];
+            float c[3] = {r.a.x, r.a.y, r.a.z};
+            float a[3] = {r.b.x * r.a.w, r.b.y * r.a.w, r.b.z * r.a.w};   // u * half_w
+            float b[3] = {r.c.x * r.b.w, r.c.y * r.b.w, r.c.z * r.b.w};   // v * half_h
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                float p0 = (c[k] + a[k]) + b[k], p1 = (c[k] + a[k]) - b[k];
+                float p2 = (c[k] - a[k]) + b[k], p3 = (c[k] - a[k]) - b[k];
+                lo[k] = fminf(fminf(p0, p1), fminf(p2, p3));
+                hi[k] = fmaxf(fmaxf(p0, p1), fmaxf(p2, p3));
+            }
+        } else {
+            int t = q - ns - nq;
+            float4 v0 = tri_v[3 * t], v1 = tri_v[3 * t + 1], v2 = tri_v[3 * t + 2];
+            lo[0] = fminf(fminf(v0.x, v1.x), v2.x); hi[0] = fmaxf(fmaxf(v0.x, v1.x), v2.x);
+            lo[1] = fminf(fminf(v0.y, v1.y), v2.y); hi[1] = fmaxf(fmaxf(v0.y, v1.y), v2.y);
+            lo[2] = fminf(fminf(v0.z, v1.z), v2.z); hi[2] = fmaxf(fmaxf(v0.z, v1.z), v2.z);
+        }
+        amin[q] = make_float4(lo[0], lo[1], lo[2], 0.f);
+        amax[q] = make_float4(hi[0], hi[1], hi[2], 0.f);
+    }
+    // block reduction of the scene bounds (min/max are exact, so order does not matter)
+    __shared__ float s_lo[3][8], s_hi[3][8];
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        float a = lo[k], b = hi[k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            a = fminf(a, __shfl_xor_sync(0xffffffffu, a, o));
+            b = fmaxf(b, __shfl_xor_sync(0xffffffffu, b, o));
+        }
+        if (lane == 0) { s_lo[k][w] = a; s_hi[k][w] = b; }
+    }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+        int k = threadIdx.x;
+        float a = s_lo[k][0], b = s_hi[k][0];
+        for (int i = 1; i < (int)(blockDim.x >> 5); ++i) { a = fminf(a, s_lo[k][i]); b = fmaxf(b, s_hi[k][i]); }
+        if (a <= b) { atomicMin(&bounds[k], f2ord(a)); atomicMax(&bounds[3 + k], f2ord(b)); }
+    }
+}
+
+__device__ __forceinline__ uint32_t expand10(uint32_t v) {
+    v = (v * 0x00010001u) & 0xFF0000FFu;
+    v = (v * 0x00000101u) & 0x0F00F00Fu;
+    v = (v * 0x00000011u) & 0xC30C30C3u;
+    v = (v * 0x00000005u) & 0x49249249u;
+    return v;
+}
+__device__ __forceinline__ uint32_t quant10(float c, float lo, float hi) {
+    float e = hi - lo;
+    float x = e > 0.0f ? (c - lo) / e : 0.0f;
+    int xi = (int)(x * 1024.0f);
+    xi = xi < 0 ? 0 : (xi > 1023 ? 1023 : xi);
+    return (uint32_t)xi;
+}
+
+__global__ void k_morton(const float4* __restrict__ amin, const float4* __restrict__ amax, int n,
+                         const int* __restrict__ bounds, uint32_t* __restrict__ keys,
+                         uint32_t* __restrict__ vals, uint32_t* __restrict__ morton_out) {
+    int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= n) return;
+    float lx = ord2f(bounds[0]), ly = ord2f(bounds[1]), lz = ord2f(bounds[2]);
+    float hx = ord2f(bounds[3]), hy = ord2f(bounds[4]), hz = ord2f(bounds[5]);
+    float4 a = amin[q], b = amax[q];
+    float cx = (a.x + b.x) * 0.5f, cy = (a.y + b.y) * 0.5f, cz = (a.z + b.z) * 0.5f;
+    uint32_t code = (expand10(quant10(cx, lx, hx)) << 2) | (expand10(quant10(cy, ly, hy)) << 1) |
+                    expand10(quant10(cz, lz, hz));
+    keys[q] = code; vals[q] = (uint32_t)q; morton_out[q] = code;
+}
+
+// ------------------------------------------------------------------ radix sort (stable LSD)
+constexpr int RS_THREADS = 256;
+constexpr int RS_ITEMS = 16;
+constexpr int RS_TILE = RS_THREADS * RS_ITEMS;   // 4096 keys per block
+constexpr int RS_WARPS = RS_THREADS / 32;
+
+__global__ void __launch_bounds__(RS_THREADS)
+k_rs_hist(const uint32_t* __restrict__ keys, int n, int shift, uint32_t* __restrict__ block_hist, int nblocks) {
+    __shared__ uint32_t h[256];
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    int base = blockIdx.x * RS_TILE;
+#pragma unroll
+    for (int r = 0; r < RS_ITEMS; ++r) {
+        int i = base + r * RS_THREADS + threadIdx.x;
+        if (i < n) atomicAdd(&h[(keys[i] >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    block_hist[(size_t)threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];
+}
+
+// exclusive scan of `total` uint32 in place, one block of 1024 threads
+__global__ void __launch_bounds__(1024) k_rs_scan(uint32_t* __restrict__ a, int total) {
+    __shared__ uint32_t warp_sum[32];
+    __shared__ uint32_t carry_s;
+    int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    int per = (total + 1023) / 1024;
+    int lo = tid * per, hi = min(lo + per, total);
+    uint32_t s = 0;
+    for (int i = lo; i < hi; ++i) s += a[i];
+    uint32_t inc = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+    if (lane == 31) warp_sum[w] = inc;
+    __syncthreads();
+    if (w == 0) {
+        uint32_t v = warp_sum[lane], x = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += t; }
+        warp_sum[lane] = x - v;
+        if (lane == 31) carry_s = x;
+    }
+    __syncthreads();
+    uint32_t run = warp_sum[w] + (inc - s);
+    for (int i = lo; i < hi; ++i) { uint32_t v = a[i]; a[i] = run; run += v; }
+}
+
+__global__ void __launch_bounds__(RS_THREADS)
+k_rs_scatter(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+             uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int n, int shift,
+             const uint32_t* __restrict__ block_off, int nblocks) {
+    __shared__ uint32_t cnt[RS_WARPS][256];
+    int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    for (int i = tid; i < RS_WARPS * 256; i += RS_THREADS) (&cnt[0][0])[i] = 0;
+    __syncthreads();
+    uint32_t key[RS_ITEMS], val[RS_ITEMS], rank[RS_ITEMS];
+    int base = blockIdx.x * RS_TILE + w * (RS_ITEMS * 32);
+    uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+    for (int r = 0; r < RS_ITEMS; ++r) {
+        int i = base + r * 32 + lane;
+        bool valid = i < n;
+        key[r] = valid ? keys_in[i] : 0u;
+        val[r] = valid ? vals_in[i] : 0u;
+        uint32_t digit = valid ? ((key[r] >> shift) & 255u) : 256u;
+        uint32_t peers = __match_any_sync(0xffffffffu, digit);
+        int leader = __ffs(peers) - 1;
+        uint32_t b = 0;
+        if (valid && lane == leader) { b = cnt[w][digit]; cnt[w][digit] = b + __popc(peers); }
+        b = __shfl_sync(0xffffffffu, b, leader);
+        rank[r] = b + __popc(peers & lt);
+        __syncwarp();
+    }
+    __syncthreads();
+    {   // per digit: global base of this block, then exclusive prefix over the block's warps
+        uint32_t run = block_off[(size_t)tid * nblocks + blockIdx.x];
+#pragma unroll
+        for (int ww = 0; ww < RS_WARPS; ++ww) { uint32_t c = cnt[ww][tid]; cnt[ww][tid] = run; run += c; }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < RS_ITEMS; ++r) {
+        int i = base + r * 32 + lane;
+        if (i < n) {
+            uint32_t pos = cnt[w][(key[r] >> shift) & 255u] + rank[r];
+            keys_out[pos] = key[r]; vals_out[pos] = val[r];
+        }
+    }
+}
+
+// ------------------------------------------------------------------ Karras hierarchy
+__device__ __forceinline__ int delta(const uint32_t* __restrict__ k, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    uint32_t a = k[i], b = k[j];
+    if (a == b) return 32 + __clz((uint32_t)i ^ (uint32_t)j);
+    return __clz(a ^ b);
+}
+
+// children[2i], children[2i+1]: >= 0 internal node, < 0 = ~leaf position
+__global__ void k_karras(const uint32_t* __restrict__ keys, int n, int* __restrict__ children,
+                         int* __restrict__ parent, int* __restrict__ leaf_parent) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    if (i == 0) parent[0] = -1;
+    int d = (delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    int dmin = delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (delta(keys, n, i, i + lmax * d) > dmin) lmax <<= 1;
+    int l = 0;
+    for (int t = lmax >> 1; t >= 1; t >>= 1)
+        if (delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    int j = i + l * d;
+    int dnode = delta(keys, n, i, j);
+    int s = 0, t = l;
+    do {
+        t = (t + 1) >> 1;
+        if (delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+    } while (t > 1);
+    int gamma = i + s * d + min(d, 0);
+    int lo = min(i, j), hi = max(i, j);
+    int left, right;
+    if (lo == gamma) { left = ~gamma; leaf_parent[gamma] = i; } else { left = gamma; parent[gamma] = i; }
+    if (hi == gamma + 1) { right = ~(gamma + 1); leaf_parent[gamma + 1] = i; } else { right = gamma + 1; parent[gamma + 1] = i; }
+    children[2 * i] = left; children[2 * i + 1] = right;
+}
+
+// bottom-up refit: the second thread to reach a node merges the child boxes
+__global__ void k_refit(int n, const uint32_t* __restrict__ sorted_prim, const float4* __restrict__ amin,
+                        const float4* __restrict__ amax, const int* __restrict__ children,
+                        const int* __restrict__ parent, const int* __restrict__ leaf_parent,
+                        float4* node_min, float4* node_max, int* flags) {
+    int pos = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pos >= n) return;
+    int node = leaf_parent[pos];
+    while (node >= 0) {
+        __threadfence();
+        if (atomicAdd(&flags[node], 1) == 0) return;
+        __threadfence();
+        float4 mn[2], mx[2];
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            int c = children[2 * node + k];
+            if (c < 0) { uint32_t q = sorted_prim[~c]; mn[k] = amin[q]; mx[k] = amax[q]; }
+            else { mn[k] = __ldcg(&node_min[c]); mx[k] = __ldcg(&node_max[c]); }
+        }
+        __stcg(&node_min[node], make_float4(fminf(mn[0].x, mn[1].x), fminf(mn[0].y, mn[1].y), fminf(mn[0].z, mn[1].z), 0.f));
+        __stcg(&node_max[node], make_float4(fmaxf(mx[0].x, mx[1].x), fmaxf(mx[0].y, mx[1].y), fmaxf(mx[0].z, mx[1].z), 0.f));
+        node = parent[node];
+    }
+}
+
+__device__ __forceinline__ int leaf_code(int pos, uint32_t q, int ns, int nq) {
+    uint32_t payload = q < (uint32_t)ns ? PRT_MAKE_LEAF(0, q)
+                     : q < (uint32_t)(ns + nq) ? PRT_MAKE_LEAF(1, q - ns)
+                     : PRT_MAKE_LEAF(2, pos);
+    return ~(int)payload;
+}
+
+__global__ void k_emit_nodes(int n, int ns, int nq, const uint32_t* __restrict__ sorted_prim,
+                             const float4* __restrict__ amin, const float4* __restrict__ amax,
+                             const int* __restrict__ children, const float4* __restrict__ node_min,
+                             const float4* __restrict__ node_max, BvhNode* __restrict__ nodes) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    float4 mn[2], mx[2]; int code[2];
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        int c = children[2 * i + k];
+        if (c < 0) { uint32_t q = sorted_prim[~c]; mn[k] = amin[q]; mx[k] = amax[q]; code[k] = leaf_code(~c, q, ns, nq); }
+        else { mn[k] = node_min[c]; mx[k] = node_max[c]; code[k] = c; }
+    }
+    BvhNode nd;
+    nd.lmin = make_float4(mn[0].x, mn[0].y, mn[0].z, __int_as_float(code[0]));
+    nd.lmax = make_float4(mx[0].x, mx[0].y, mx[0].z, __int_as_float(code[1]));
+    nd.rmin = make_float4(mn[1].x, mn[1].y, mn[1].z, 0.f);
+    nd.rmax = make_float4(mx[1].x, mx[1].y, mx[1].z, 0.f);
+    nodes[i] = nd;
+}
+
+// triangle planes in leaf-slot order so a leaf code indexes them directly
+__global__ void k_gather_tris(int n, int ns, int nq, int tri_prim_base, const uint32_t* __restrict__ sorted_prim,
+                              const float4* __restrict__ in_v, const float4* __restrict__ in_n,
+                              const int* __restrict__ in_mat, float4* __restrict__ out_v, float4* __restrict__ out_n) {
+    int pos = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pos >= n) return;
+    int q = (int)sorted_prim[pos];
+    if (q < ns + nq) return;
+    int t = q - ns - nq;
+    float4 a = in_v[3 * t], b = in_v[3 * t + 1], c = in_v[3 * t + 2];
+    a.w = __int_as_float(tri_prim_base + t); b.w = __int_as_float(in_mat[t]); c.w = 0.f;
+    out_v[3 * pos] = a; out_v[3 * pos + 1] = b; out_v[3 * pos + 2] = c;
+    out_n[3 * pos] = in_n[3 * t]; out_n[3 * pos + 1] = in_n[3 * t + 1]; out_n[3 * pos + 2] = in_n[3 * t + 2];
+}
+
+// ------------------------------------------------------------------ host driver
+int lbvh_build(Ctx* c) {
+    const int n = c->n_prims, ns = c->n_spheres, nq = c->n_quads, nt = c->n_tris;
+    c->bvh_built = false;
+    cudaStream_t st = c->stream;
+    int rc;
+    if ((rc = dev_reserve(c, c->scene_bounds, 6 * sizeof(int)))) return rc;
+    PRT_CUDA(c, cudaEventRecord(c->ev0, st));
+    k_init_bounds<<<1, 32, 0, st>>>((int*)c->scene_bounds.p);
+    if (n == 0) {
+        c->root_code = 0; c->bvh_built = true; c->build_ms = 0.f;
+        PRT_CUDA(c, cudaStreamSynchronize(st));
+        return PRT_OK;
+    }
+    const size_t nn = (size_t)n;
+    if ((rc = dev_reserve(c, c->aabb_min, nn * 16)) || (rc = dev_reserve(c, c->aabb_max, nn * 16)) ||
+        (rc = dev_reserve(c, c->morton, nn * 4)) ||
+        (rc = dev_reserve(c, c->keys[0], nn * 4)) || (rc = dev_reserve(c, c->keys[1], nn * 4)) ||
+        (rc = dev_reserve(c, c->vals[0], nn * 4)) || (rc = dev_reserve(c, c->vals[1], nn * 4)) ||
+        (rc = dev_reserve(c, c->children, nn * 8)) || (rc = dev_reserve(c, c->parent, nn * 8)) ||
+        (rc = dev_reserve(c, c->node_min, nn * 16)) || (rc = dev_reserve(c, c->node_max, nn * 16)) ||
+        (rc = dev_reserve(c, c->flags, nn * 4)) || (rc = dev_reserve(c, c->nodes, nn * sizeof(BvhNode))) ||
+        (rc = dev_reserve(c, c->tri_v, nn * 48)) || (rc = dev_reserve(c, c->tri_n, nn * 48)))
+        return rc;
+    const int nblocks = (n + RS_TILE - 1) / RS_TILE;
+    if ((rc = dev_reserve(c, c->block_hist, (size_t)nblocks * 256 * 4))) return rc;
+
+    const int T = 256, G = (n + T - 1) / T;
+    k_prim_bounds<<<G, T, 0, st>>>((const SphereRec*)c->spheres.p, ns, (const QuadRec*)c->quads.p, nq,
+                                   (const float4*)c->tri_in_v.p, nt, (float4*)c->aabb_min.p,
+                                   (float4*)c->aabb_max.p, (int*)c->scene_bounds.p);
+    k_morton<<<G, T, 0, st>>>((const float4*)c->aabb_min.p, (const float4*)c->aabb_max.p, n,
+                              (const int*)c->scene_bounds.p, (uint32_t*)c->keys[0].p,
+                              (uint32_t*)c->vals[0].p, (uint32_t*)c->morton.p);
+    int cur = 0;
+    for (int pass = 0; pass < 4; ++pass) {
+        int shift = pass * 8;
+        k_rs_hist<<<nblocks, RS_THREADS, 0, st>>>((const uint32_t*)c->keys[cur].p, n, shift,
+                                                  (uint32_t*)c->block_hist.p, nblocks);
+        k_rs_scan<<<1, 1024, 0, st>>>((uint32_t*)c->block_hist.p, nblocks * 256);
+        k_rs_scatter<<<nblocks, RS_THREADS, 0, st>>>((const uint32_t*)c->keys[cur].p, (const uint32_t*)c->vals[cur].p,
+                                                     (uint32_t*)c->keys[cur ^ 1].p, (uint32_t*)c->vals[cur ^ 1].p,
+                                                     n, shift, (const uint32_t*)c->block_hist.p, nblocks);
+        cur ^= 1;
+    }
+    c->sorted_slot = cur;
+    const uint32_t* skeys = (const uint32_t*)c->keys[cur].p;
+    const uint32_t* sprim = (const uint32_t*)c->vals[cur].p;
+    int* parent = (int*)c->parent.p;
+    int* leaf_parent = parent + n;
+    if (n > 1) {
+        PRT_CUDA(c, cudaMemsetAsync(c->flags.p, 0, nn * 4, st));
+        k_karras<<<G, T, 0, st>>>(skeys, n, (int*)c->children.p, parent, leaf_parent);
+        k_refit<<<G, T, 0, st>>>(n, sprim, (const float4*)c->aabb_min.p, (const float4*)c->aabb_max.p,
+                                 (const int*)c->children.p, parent, leaf_parent,
+                                 (float4*)c->node_min.p, (float4*)c->node_max.p, (int*)c->flags.p);
+        k_emit_nodes<<<G, T, 0, st>>>(n, ns, nq, sprim, (const float4*)c->aabb_min.p, (const float4*)c->aabb_max.p,
+                                      (const int*)c->children.p, (const float4*)c->node_min.p,
+                                      (const float4*)c->node_max.p, (BvhNode*)c->nodes.p);
+        c->root_code = 0;
+    } else {
+        // single primitive: the root IS the leaf
+        uint32_t payload = ns ? PRT_MAKE_LEAF(0, 0) : nq ? PRT_MAKE_LEAF(1, 0) : PRT_MAKE_LEAF(2, 0);
+        c->root_code = ~(int)payload;
+    }
+    if (nt > 0)
+        k_gather_tris<<<G, T, 0, st>>>(n, ns, nq, c->tri_prim_base, sprim, (const float4*)c->tri_in_v.p,
+                                       (const float4*)c->tri_in_n.p, (const int*)c->tri_in_mat.p,
+                                       (float4*)c->tri_v.p, (float4*)c->tri_n.p);
+    PRT_CUDA(c, cudaEventRecord(c->ev1, st));
+    PRT_CUDA(c, cudaStreamSynchronize(st));
+    PRT_CUDA(c, cudaGetLastError());
+    PRT_CUDA(c, cudaEventElapsedTime(&c->build_ms, c->ev0, c->ev1));
+    c->stats.build_ms = c->build_ms;
+    c->bvh_built = true;
+    return PRT_OK;
+}
+
+}  // namespace prt

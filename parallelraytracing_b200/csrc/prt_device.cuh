@@ -1,0 +1,365 @@
+// prt_device.cuh — device-side math of the hot path: vectors, counter RNG, the three
+// primitive tests, the four materials, the camera ray.
+//
+// Floating-point contract (DESIGN.md "Numerics"): this translation unit is compiled with
+// -fmad=false, so `a*b+c` is NEVER contracted; every fused multiply-add below is an explicit
+// fmaf(). The CPU oracle (oracle/prt_oracle.cpp) restates the same formulas with the same
+// operation order (-ffp-contract=off), IEEE sqrt and divide on both sides, so integer
+// results (hit ids, Morton codes) are bit-exact and floats agree to the last bit in practice.
+//
+// Reference semantics mirrored (paths relative to /root/reference):
+//   camera ray        src/core/camera.h:104-132
+//   sphere ("Circle") src/core/shape.h:157-203
+//   quad              src/core/shape.h:213-239
+//   triangle          src/core/shape.h:262-303 (Moller-Trumbore there; watertight here)
+//   closest hit rule  src/core/primitive.cpp:21-59 (strict <, lowest list index wins ties)
+//   materials         src/core/material.h:11-161, src/core/math.h:10-50
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define PRT_DEV __device__ __forceinline__
+
+namespace prt {
+
+// ------------------------------------------------------------------ vectors
+struct V3 { float x, y, z; };
+
+PRT_DEV V3 mk(float x, float y, float z) { V3 r; r.x = x; r.y = y; r.z = z; return r; }
+PRT_DEV V3 operator+(V3 a, V3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+PRT_DEV V3 operator-(V3 a, V3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+PRT_DEV V3 operator*(V3 a, float s) { return mk(a.x * s, a.y * s, a.z * s); }
+PRT_DEV V3 operator*(V3 a, V3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
+PRT_DEV V3 neg(V3 a) { return mk(-a.x, -a.y, -a.z); }
+// glm::dot(vec3): (x*x' + y*y') + z*z', unfused.
+PRT_DEV float dot(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+PRT_DEV V3 cross(V3 a, V3 b) {
+    return mk(a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y);
+}
+// glm::normalize: v * inversesqrt(dot(v,v)), inversesqrt = 1/sqrt (IEEE both).
+PRT_DEV V3 normalize(V3 v) { float s = 1.0f / sqrtf(dot(v, v)); return v * s; }
+PRT_DEV V3 xyz(float4 f) { return mk(f.x, f.y, f.z); }
+
+// ------------------------------------------------------------------ RNG
+// Counter-free PCG-RXS-M-XS-32 stream per (path, bounce). Random() mirrors the host
+// branch of the reference: std::rand() / (RAND_MAX + 1.0f) with a 31-bit rand()
+// (src/core/math.h:15); the int->float conversion rounds to nearest, so 1.0f can occur.
+PRT_DEV uint32_t hash32(uint32_t x) {
+    x ^= x >> 16; x *= 0x21f0aaadu; x ^= x >> 15; x *= 0x735a2d97u; x ^= x >> 15;
+    return x;
+}
+PRT_DEV uint32_t path_key(uint32_t seed_lo, uint32_t seed_hi, uint32_t pixel, uint32_t sample) {
+    uint32_t k = hash32(seed_hi ^ 0x9e3779b9u);
+    k = hash32(seed_lo ^ k);
+    k = hash32(sample ^ k);
+    k = hash32(pixel ^ k);
+    return k;
+}
+struct Rng { uint32_t s; };
+PRT_DEV Rng rng_for_bounce(uint32_t key, uint32_t bounce) {
+    Rng r; r.s = hash32(key + 0x9e3779b9u * (bounce + 1u)); return r;
+}
+PRT_DEV uint32_t rng_next31(Rng& r) {
+    r.s = r.s * 747796405u + 2891336453u;
+    uint32_t w = ((r.s >> ((r.s >> 28) + 4u)) ^ r.s) * 277803737u;
+    w = (w >> 22) ^ w;
+    return w >> 1;
+}
+PRT_DEV float rng_uniform(Rng& r) {
+    return __int2float_rn((int)rng_next31(r)) * 4.656612873077392578125e-10f;  // / 2^31
+}
+// Random(-1, 1): min + (max - min) * Random()   (math.h:20-23)
+PRT_DEV float rng_pm1(Rng& r) { return -1.0f + 2.0f * rng_uniform(r); }
+// RandomUnitVector: rejection in the cube (math.h:26-36)
+PRT_DEV V3 rng_unit_vector(Rng& r) {
+    for (;;) {
+        float x = rng_pm1(r);
+        float y = rng_pm1(r);
+        float z = rng_pm1(r);
+        V3 p = mk(x, y, z);
+        float l2 = dot(p, p);
+        if (1e-8f < l2 && l2 <= 1.0f) {
+            float l = sqrtf(l2);
+            return mk(p.x / l, p.y / l, p.z / l);
+        }
+    }
+}
+
+// ------------------------------------------------------------------ scene records
+// Device layouts (16-byte planes, fetched with 128-bit loads).
+struct SphereRec { float4 a; float4 b; };          // a={c.xyz, r}  b={tmin, mat, prim_id, 0}
+struct QuadRec   { float4 a, b, c, d; };            // a={c.xyz,hw} b={u.xyz,hh} c={v.xyz,tmin} d={n.xyz, bits(prim_id)}
+struct MatRec    { float4 a; float4 b; };           // a={r,g,b,param} b={bits(type),0,0,0}
+struct BvhNode   { float4 lmin, lmax, rmin, rmax; };// .w of lmin/lmax = bits(left/right child code)
+
+// child / hit code: >= 0 internal node index; < 0 leaf, ~code = (shape_type << 28) | index
+#define PRT_LEAF_TYPE(c)  ((uint32_t)(c) >> 28)
+#define PRT_LEAF_INDEX(c) ((uint32_t)(c) & 0x0fffffffu)
+#define PRT_MAKE_LEAF(type, idx) (((uint32_t)(type) << 28) | (uint32_t)(idx))
+#define PRT_NO_HIT 0xffffffffu
+
+struct SceneView {
+    const SphereRec* spheres;  int n_spheres;
+    const QuadRec*   quads;    int n_quads;
+    const float4*    tri_v;    // 3 float4 per leaf slot: {v0, bits(prim_id)} {v1, bits(mat)} {v2, 0}
+    const float4*    tri_n;    // 3 float4 per leaf slot: vertex normals
+    int              n_tris;
+    const MatRec*    mats;     int n_mats;
+    const int*       quad_mat; // material per quad (quads' own record is full)
+    const BvhNode*   nodes;    int n_prims;
+    int              root_code; // root: 0 if n_prims>1, leaf code (negative-as-~) if n_prims==1
+    float            tri_tmin;
+    float sky_r, sky_g, sky_b;
+};
+
+// ------------------------------------------------------------------ primitive tests
+// Closest-hit candidate bookkeeping: strict < on t, ties -> lowest reference list index
+// (primitive.cpp:44 keeps the FIRST primitive on equal distance).
+struct Best {
+    float t; uint32_t code; int prim_id; float u, v;
+};
+PRT_DEV void best_init(Best& b) { b.t = __int_as_float(0x7f800000); b.code = PRT_NO_HIT; b.prim_id = 0x7fffffff; b.u = 0.f; b.v = 0.f; }
+PRT_DEV void best_update(Best& b, float t, uint32_t code, int prim_id, float u, float v) {
+    if (t < b.t || (t == b.t && prim_id < b.prim_id)) { b.t = t; b.code = code; b.prim_id = prim_id; b.u = u; b.v = v; }
+}
+
+// Sphere: quadratic exactly as Circle::Intersect (shape.h:157-203) with l = o - c (what
+// InvMat*o gives for a translation) and d = normalize(ray.d) (what TransformNormal gives,
+// primitive.cpp:30). Returns t (>= tmin) or -1; front = both roots >= tmin.
+PRT_DEV float isect_sphere(const SphereRec& s, V3 o, V3 d, bool& front) {
+    V3 l = o - xyz(s.a);
+    float r = s.a.w, tmin = s.b.x;
+    float a = dot(d, d);
+    float b = 2.0f * dot(l, d);
+    float c = dot(l, l) - r * r;
+    float disc = b * b - 4.0f * a * c;
+    if (!(disc >= 0.0f)) return -1.0f;
+    float sq = sqrtf(disc);
+    float t1 = (-b + sq) / (2.0f * a);
+    float t2 = (-b - sq) / (2.0f * a);
+    if (t1 >= tmin && t2 >= tmin) { front = true; return t1 < t2 ? t1 : t2; }
+    front = false;
+    if (t1 >= tmin) return t1;
+    if (t2 >= tmin) return t2;
+    return -1.0f;
+}
+
+// Quad: Quad::Intersect (shape.h:213-239) in world space: plane through c with normal n,
+// extents along unit u (local x) and v (local z). front = origin on the +n side.
+PRT_DEV float isect_quad(const QuadRec& q, V3 o, V3 d, bool& front) {
+    V3 n = xyz(q.d);
+    V3 oc = o - xyz(q.a);
+    float dn = dot(d, n);
+    if (fabsf(dn) < 1e-8f) return -1.0f;
+    float on = dot(oc, n);
+    float t = -on / dn;
+    V3 p = oc + d * t;
+    float x = dot(p, xyz(q.b));
+    float z = dot(p, xyz(q.c));
+    float hw = q.a.w, hh = q.b.w, tmin = q.c.w;
+    if (t > tmin && (x * x < hw * hw) && (z * z < hh * hh)) { front = on > 0.0f; return t; }
+    return -1.0f;
+}
+
+// Watertight ray/triangle test (Woop, Benthin, Wald 2013). Per-ray constants:
+struct RayShear { int kx, ky, kz; float sx, sy, sz; };
+PRT_DEV RayShear make_shear(V3 d) {
+    RayShear r;
+    float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
+    r.kz = (ax > ay) ? ((ax > az) ? 0 : 2) : ((ay > az) ? 1 : 2);
+    r.kx = r.kz + 1; if (r.kx == 3) r.kx = 0;
+    r.ky = r.kx + 1; if (r.ky == 3) r.ky = 0;
+    float dz = r.kz == 0 ? d.x : (r.kz == 1 ? d.y : d.z);
+    if (dz < 0.0f) { int t = r.kx; r.kx = r.ky; r.ky = t; }
+    float dx = r.kx == 0 ? d.x : (r.kx == 1 ? d.y : d.z);
+    float dy = r.ky == 0 ? d.x : (r.ky == 1 ? d.y : d.z);
+    r.sx = dx / dz; r.sy = dy / dz; r.sz = 1.0f / dz;
+    return r;
+}
+PRT_DEV float comp(V3 v, int k) { return k == 0 ? v.x : (k == 1 ? v.y : v.z); }
+
+// Returns t >= tmin or -1; b1,b2 = barycentric weights of v1,v2 (reference naming,
+// shape.h:282-284).
+PRT_DEV float isect_tri(V3 v0, V3 v1, V3 v2, V3 o, const RayShear& rs, float tmin, float tmax,
+                        float& b1, float& b2) {
+    V3 A = v0 - o, B = v1 - o, C = v2 - o;
+    float Akz = comp(A, rs.kz), Bkz = comp(B, rs.kz), Ckz = comp(C, rs.kz);
+    float Ax = fmaf(-rs.sx, Akz, comp(A, rs.kx)), Ay = fmaf(-rs.sy, Akz, comp(A, rs.ky));
+    float Bx = fmaf(-rs.sx, Bkz, comp(B, rs.kx)), By = fmaf(-rs.sy, Bkz, comp(B, rs.ky));
+    float Cx = fmaf(-rs.sx, Ckz, comp(C, rs.kx)), Cy = fmaf(-rs.sy, Ckz, comp(C, rs.ky));
+    float U = Cx * By - Cy * Bx;
+    float V = Ax * Cy - Ay * Cx;
+    float W = Bx * Ay - By * Ax;
+    if (U == 0.0f || V == 0.0f || W == 0.0f) {
+        double CxBy = (double)Cx * (double)By, CyBx = (double)Cy * (double)Bx;
+        U = (float)(CxBy - CyBx);
+        double AxCy = (double)Ax * (double)Cy, AyCx = (double)Ay * (double)Cx;
+        V = (float)(AxCy - AyCx);
+        double BxAy = (double)Bx * (double)Ay, ByAx = (double)By * (double)Ax;
+        W = (float)(BxAy - ByAx);
+    }
+    if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f)) return -1.0f;
+    float det = (U + V) + W;
+    if (det == 0.0f) return -1.0f;
+    float Az = rs.sz * Akz, Bz = rs.sz * Bkz, Cz = rs.sz * Ckz;
+    float T = fmaf(W, Cz, fmaf(V, Bz, U * Az));
+    float t = T / det;
+    if (!(t >= tmin) || t > tmax) return -1.0f;
+    b1 = V / det;
+    b2 = W / det;
+    return t;
+}
+
+// ------------------------------------------------------------------ ray/box (robust slab)
+struct RayBox { V3 o; V3 inv; };
+PRT_DEV float safe_inv(float d) {
+    float a = fabsf(d) < 1e-20f ? copysignf(1e-20f, d) : d;
+    return 1.0f / a;
+}
+PRT_DEV RayBox make_raybox(V3 o, V3 d) {
+    RayBox r; r.o = o; r.inv = mk(safe_inv(d.x), safe_inv(d.y), safe_inv(d.z)); return r;
+}
+// Returns entry distance (>=0) if the box [mn,mx] overlaps the ray within [0,tmax], else -1.
+// The far side is widened by 1+2^-21 (covers the <=3 ulp error of the three slab products),
+// so a primitive that the exact test would report is never culled by rounding.
+PRT_DEV float isect_box(const RayBox& r, float4 mn, float4 mx, float tmax) {
+    float x0 = (mn.x - r.o.x) * r.inv.x, x1 = (mx.x - r.o.x) * r.inv.x;
+    float y0 = (mn.y - r.o.y) * r.inv.y, y1 = (mx.y - r.o.y) * r.inv.y;
+    float z0 = (mn.z - r.o.z) * r.inv.z, z1 = (mx.z - r.o.z) * r.inv.z;
+    float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.0f));
+    float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), tmax));
+    tf = tf * 1.00000047683715820312f;
+    return tn <= tf ? tn : -1.0f;
+}
+
+// ------------------------------------------------------------------ leaf test dispatch
+// d = ray direction, dn = normalize(d) (the sphere test's local direction).
+PRT_DEV void test_leaf(const SceneView& sc, uint32_t code, V3 o, V3 d, V3 dn, const RayShear& rs, Best& best) {
+    uint32_t type = PRT_LEAF_TYPE(code), idx = PRT_LEAF_INDEX(code);
+    if (type == 2u) {
+        float4 a = __ldg(&sc.tri_v[3 * idx + 0]);
+        float4 b = __ldg(&sc.tri_v[3 * idx + 1]);
+        float4 c = __ldg(&sc.tri_v[3 * idx + 2]);
+        float b1, b2;
+        float t = isect_tri(xyz(a), xyz(b), xyz(c), o, rs, sc.tri_tmin, best.t, b1, b2);
+        if (t >= 0.0f) best_update(best, t, code, __float_as_int(a.w), b1, b2);
+    } else if (type == 0u) {
+        SphereRec s; s.a = __ldg(&sc.spheres[idx].a); s.b = __ldg(&sc.spheres[idx].b);
+        bool front;
+        float t = isect_sphere(s, o, dn, front);
+        if (t >= 0.0f) best_update(best, t, code, __float_as_int(s.b.z), front ? 1.0f : 0.0f, 0.0f);
+    } else {
+        QuadRec q; q.a = __ldg(&sc.quads[idx].a); q.b = __ldg(&sc.quads[idx].b);
+        q.c = __ldg(&sc.quads[idx].c); q.d = __ldg(&sc.quads[idx].d);
+        bool front;
+        float t = isect_quad(q, o, d, front);
+        if (t >= 0.0f) best_update(best, t, code, __float_as_int(q.d.w), front ? 1.0f : 0.0f, 0.0f);
+    }
+}
+
+// ------------------------------------------------------------------ surface + materials
+struct Surface { V3 p; V3 n; bool front; int mat; };
+
+// Rebuild SurfaceInteraction{Position, Normal, IsFrontFace, Material} for a hit record.
+PRT_DEV Surface make_surface(const SceneView& sc, V3 o, V3 d, float t, uint32_t code, float u, float v) {
+    Surface s;
+    uint32_t type = PRT_LEAF_TYPE(code), idx = PRT_LEAF_INDEX(code);
+    if (type == 2u) {
+        float4 a = __ldg(&sc.tri_v[3 * idx + 0]);
+        float4 b = __ldg(&sc.tri_v[3 * idx + 1]);
+        float4 c = __ldg(&sc.tri_v[3 * idx + 2]);
+        float4 na = __ldg(&sc.tri_n[3 * idx + 0]);
+        float4 nb = __ldg(&sc.tri_n[3 * idx + 1]);
+        float4 nc = __ldg(&sc.tri_n[3 * idx + 2]);
+        float b0 = (1.0f - u) - v;                      // (1 - b1 - b2)  shape.h:291
+        s.p = (xyz(a) * b0 + xyz(b) * u) + xyz(c) * v;
+        V3 n = (xyz(na) * b0 + xyz(nb) * u) + xyz(nc) * v;
+        if (dot(n, d) > 0.0f) { n = neg(n); s.front = false; } else s.front = true;   // shape.h:294-302
+        s.n = normalize(n);                             // TransformNormal, primitive.cpp:39
+        s.mat = __float_as_int(b.w);
+    } else if (type == 0u) {
+        float4 a = __ldg(&sc.spheres[idx].a);
+        float4 b = __ldg(&sc.spheres[idx].b);
+        // local hit point l + dn*t, normal = normalize(local point) (shape.h:194-199), then
+        // Position = Mat*p' = p' + c and TransformNormal normalises once more (primitive.cpp:38-39)
+        V3 pl = (o - xyz(a)) + normalize(d) * t;
+        V3 n = normalize(pl);
+        s.front = u != 0.0f;
+        if (!s.front) n = neg(n);
+        s.n = normalize(n);
+        s.p = pl + xyz(a);
+        s.mat = __float_as_int(b.y);
+    } else {
+        float4 qd = __ldg(&sc.quads[idx].d);
+        s.p = o + d * t;
+        s.front = u != 0.0f;
+        s.n = s.front ? xyz(qd) : neg(xyz(qd));
+        s.mat = __ldg(&sc.quad_mat[idx]);
+    }
+    return s;
+}
+
+// glm::reflect: I - N * dot(N, I) * 2
+PRT_DEV V3 reflect(V3 i, V3 n) { float k = dot(n, i); return i - (n * k) * 2.0f; }
+
+// MaterialHandle::{Emit,Scatter} (material.h:139-161). Returns true when the path
+// continues with direction out_d (already passed through Ray::Normalize as
+// cpu/renderer.cpp:84 does) and throughput factor atten; emit = Le of the surface.
+PRT_DEV bool scatter(const MatRec& m, V3 d, const Surface& s, Rng& rng, V3& atten, V3& out_d, V3& emit) {
+    int type = __float_as_int(m.b.x);
+    emit = mk(0.f, 0.f, 0.f);
+    V3 dir;
+    if (type == 1) {                                    // Lambertian, material.h:16-31
+        V3 ruv = rng_unit_vector(rng);
+        dir = s.n + ruv;
+        if (fabsf(dir.x) < 1e-8f && fabsf(dir.y) < 1e-8f && fabsf(dir.z) < 1e-8f) dir = s.n;
+        dir = normalize(dir);
+        atten = mk(m.a.x, m.a.y, m.a.z);
+    } else if (type == 2) {                             // Metal, material.h:48-57
+        V3 r = normalize(reflect(d, s.n));
+        V3 ruv = rng_unit_vector(rng);
+        r = r + ruv * m.a.w;
+        dir = normalize(r);
+        atten = mk(m.a.x, m.a.y, m.a.z);
+        if (!(dot(dir, s.n) > 0.0f)) return false;
+    } else if (type == 3) {                             // Dielectric, material.h:76-95
+        atten = mk(1.f, 1.f, 1.f);
+        float ior = m.a.w;
+        float ri = s.front ? (1.0f / ior) : ior;
+        float cos_t = fminf(dot(neg(d), s.n), 1.0f);
+        float sin_t = sqrtf(1.0f - cos_t * cos_t);
+        bool cannot = ri * sin_t > 1.0f;
+        float r0 = (1.0f - ri) / (1.0f + ri);
+        r0 = r0 * r0;
+        float x = 1.0f - cos_t;
+        float x5 = ((x * x) * (x * x)) * x;             // pow(1-cos, 5)
+        float fres = r0 + (1.0f - r0) * x5;
+        // `cannot_refract || fresnel > Random()` short-circuits: no draw when cannot_refract
+        bool refl = cannot;
+        if (!refl) refl = fres > rng_uniform(rng);
+        if (refl) dir = reflect(d, s.n);
+        else {                                          // "Reflect" = refract, math.h:45-50
+            float c2 = fminf(dot(neg(d), s.n), 1.0f);
+            V3 perp = (d + s.n * c2) * ri;
+            float k = -sqrtf(fabsf(1.0f - dot(perp, perp)));
+            dir = perp + s.n * k;
+        }
+    } else {                                            // Emissive / invalid: path ends
+        if (type == 4) emit = mk(m.a.x, m.a.y, m.a.z);
+        return false;
+    }
+    out_d = normalize(dir);                             // scatteredRay.Normalize(), cpu/renderer.cpp:84
+    return true;
+}
+
+// Camera::GetCameraRay (camera.h:104-132)
+struct CamView { V3 pos, front, right, up; float tan_half, aspect, w, h; int W, H; };
+PRT_DEV V3 camera_dir(const CamView& c, float px, float py) {
+    float ndc_x = (px / c.w) * 2.0f - 1.0f;
+    float ndc_y = 1.0f - (py / c.h) * 2.0f;
+    V3 dc = normalize(mk(ndc_x * c.aspect * c.tan_half, ndc_y * c.tan_half, -1.0f));
+    V3 w = (c.right * dc.x + c.up * dc.y) + neg(c.front) * dc.z;
+    return normalize(w);
+}
+
+}  // namespace prt

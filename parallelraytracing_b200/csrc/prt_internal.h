@@ -1,0 +1,91 @@
+// prt_internal.h — context object and internal entry points shared by the .cu files.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include "../../include/prt.h"
+#include "prt_device.cuh"
+
+namespace prt {
+
+struct DevBuf {
+    void* p = nullptr; size_t bytes = 0;
+};
+
+struct Ctx {
+    int device = 0;
+    int num_sms = 148;
+    cudaStream_t stream = nullptr;
+    std::string err;
+
+    // ---- scene (input order q: spheres, then quads, then triangles) ----
+    int n_spheres = 0, n_quads = 0, n_tris = 0, n_prims = 0, n_mats = 0;
+    int tri_prim_base = 0;
+    DevBuf spheres, quads, quad_mat, mats;
+    DevBuf tri_in_v, tri_in_n, tri_in_mat;     // input order: 3 float4 / tri (w unused), 3 float4 / tri, int / tri
+    DevBuf prim_id_of_q;                        // int per q: reference list index
+    float sky[3] = {0.4f, 0.3f, 0.6f};
+    bool scene_set = false;
+
+    // ---- LBVH ----
+    DevBuf aabb_min, aabb_max;                  // float4 per q
+    DevBuf scene_bounds;                        // 6 ordered-int floats
+    DevBuf keys[2], vals[2];                    // radix sort ping-pong
+    DevBuf block_hist;                          // digit-major per-block histograms
+    DevBuf children, parent, node_min, node_max, flags;
+    DevBuf nodes;                               // BvhNode per internal node
+    DevBuf tri_v, tri_n;                        // leaf-slot order (3 float4 per slot)
+    DevBuf morton;                              // per q (kept for prt_debug_lbvh)
+    int sorted_slot = 0;                        // which of keys/vals holds the sorted result
+    int root_code = 0;
+    bool bvh_built = false;
+    float build_ms = 0.f;
+
+    // ---- camera / film ----
+    prt_camera cam{};
+    bool cam_set = false;
+    DevBuf accum_own;
+    float* accum = nullptr;                     // W*H*3 (own or external)
+    bool accum_external = false;
+    int accum_spp = 0;
+    DevBuf display;                             // RGBA8
+
+    // ---- wavefront state ----
+    int64_t wave_paths = 0;                     // capacity (paths in flight)
+    int64_t wave_paths_opt = 0;                 // user override, 0 = auto
+    DevBuf q_o[2], q_d[2], q_b[2];              // ray queues: float4 planes
+    DevBuf hits;                                // float4 per ray
+    DevBuf contrib;                             // float4 per path slot
+    DevBuf qcount;                              // uint32 [PRT_MAX_DEPTH+2]
+    DevBuf stats_dev;                           // uint64 [PRT_MAX_DEPTH + 4]
+    int ctas_per_sm = 8;
+    int counters_on = 0;
+    int use_graph = 1;
+    prt_stats stats{};
+
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+};
+
+// error helpers ------------------------------------------------------------------
+int set_err(Ctx* c, int code, const std::string& msg);
+#define PRT_CUDA(ctx, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
+    return prt::set_err((ctx), e_ == cudaErrorMemoryAllocation ? PRT_ERR_OOM : PRT_ERR_CUDA, \
+        std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
+
+int dev_reserve(Ctx* c, DevBuf& b, size_t bytes);   // grow-only allocation
+void dev_free(DevBuf& b);
+
+SceneView scene_view(const Ctx* c);
+
+// lbvh.cu
+int lbvh_build(Ctx* c);
+// wavefront.cu
+int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_begin);
+int wavefront_trace_batch(Ctx* c, const prt_ray* rays, int n, prt_hit* out, int use_bvh);
+int film_resolve_display(Ctx* c, float exposure, float gamma, uint8_t* host_rgba);
+int film_scale_accum(Ctx* c, float s);
+
+}  // namespace prt
+
+struct prt_ctx { prt::Ctx c; };

@@ -1,0 +1,452 @@
+// wavefront.cu — the wavefront path-tracing pipeline over SoA ray queues in HBM:
+//   raygen -> [ extend (persistent BVH traversal) -> shade/scatter + compaction ] x depth -> resolve
+//
+// Behavioural spec = the reference's estimator, identical in its CPU recursion
+// (src/backend/cpu/renderer.cpp:59-103), its megakernel loop (cuda_megakernel/renderer.cu:81-119)
+// and its wavefront stages (cuda_wavefront/renderer.cu:186-335):
+//   L = 0, beta = 1; repeat <= D times: closest hit?  no -> L += beta*sky, stop
+//                                       yes -> L += beta*Le; scatter? beta *= atten, continue : stop
+// This is a new design, not a port: rays travel IN the queues as 16-byte planes (the reference
+// keeps per-pixel state and queues of pixel indices), compaction is by ballot/popc with one
+// atomic per warp, extend is a persistent grid sized to the SM count reading the queue length
+// from device memory, the RNG is a stateless counter hash (no 48-byte curandState), and the
+// per-sample radiance goes to a slot-indexed plane that `resolve` sums in sample order, so the
+// accumulated image is deterministic (no float atomics).
+#include "prt_internal.h"
+#include <algorithm>
+
+namespace prt {
+
+constexpr int WF_THREADS = 256;
+constexpr int STACK_SMEM = 24;    // entries per thread held in shared memory
+constexpr int STACK_LOCAL = 40;   // overflow entries (Karras tree height <= 62 for 2^28 prims)
+
+// queue entry: O = {o.xyz, bits(slot<<5 | bounce)}, D = {d.xyz, bits(path_key)}, B = {beta.rgb, 0}
+__device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
+// streaming (read-once / write-once) queue traffic: bypass L1, do not pollute it for the BVH
+__device__ __forceinline__ float4 ld_stream(const float4* p) { return __ldcs(p); }
+__device__ __forceinline__ void st_stream(float4* p, float4 v) { __stcs(p, v); }
+
+// ------------------------------------------------------------------ raygen
+__global__ void __launch_bounds__(WF_THREADS)
+k_raygen(CamView cam, int pix0, int npix, int n_paths, uint32_t sample0, uint32_t seed_lo, uint32_t seed_hi,
+         float4* __restrict__ qo, float4* __restrict__ qd, float4* __restrict__ qb, uint32_t* __restrict__ qcount) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) qcount[0] = (uint32_t)n_paths;
+    if (i >= n_paths) return;
+    int s_local = i / npix;
+    int pixel = pix0 + (i - s_local * npix);
+    int y = pixel / cam.W, x = pixel - y * cam.W;
+    V3 d = camera_dir(cam, (float)x + 0.5f, (float)y + 0.5f);     // pixel centre, cpu/renderer.cpp:45
+    uint32_t key = path_key(seed_lo, seed_hi, (uint32_t)pixel, sample0 + (uint32_t)s_local);
+    st_stream(&qo[i], make_float4(cam.pos.x, cam.pos.y, cam.pos.z, __uint_as_float((uint32_t)i << 5)));
+    st_stream(&qd[i], make_float4(d.x, d.y, d.z, __uint_as_float(key)));
+    st_stream(&qb[i], make_float4(1.f, 1.f, 1.f, 0.f));
+}
+
+// ------------------------------------------------------------------ extend
+// Closest hit by stack traversal of the two-child LBVH. One thread per ray; the traversal
+// stack lives in shared memory ([entry][thread], conflict-free), overflowing to local memory.
+template <bool COUNT>
+__device__ __forceinline__ Best traverse(const SceneView& sc, V3 o, V3 d, int* __restrict__ sstack,
+                                         uint32_t& n_nodes, uint32_t& n_prims) {
+    Best best; best_init(best);
+    if (sc.n_prims == 0) return best;
+    RayBox rb = make_raybox(o, d);
+    RayShear rs = make_shear(d);
+    V3 dn = normalize(d);
+    int lstack[STACK_LOCAL];
+    int sp = 0;
+    int cur = sc.root_code;
+    for (;;) {
+        if (cur >= 0) {
+            const BvhNode* nd = sc.nodes + cur;
+            float4 lmin = ldg4(&nd->lmin), lmax = ldg4(&nd->lmax), rmin = ldg4(&nd->rmin), rmax = ldg4(&nd->rmax);
+            if (COUNT) ++n_nodes;
+            float tl = isect_box(rb, lmin, lmax, best.t);
+            float tr = isect_box(rb, rmin, rmax, best.t);
+            int cl = __float_as_int(lmin.w), cr = __float_as_int(lmax.w);
+            if (tl >= 0.0f && tr >= 0.0f) {
+                int nearc = cl, farc = cr;
+                if (tr < tl) { nearc = cr; farc = cl; }
+                if (sp < STACK_SMEM) sstack[sp * WF_THREADS] = farc; else lstack[sp - STACK_SMEM] = farc;
+                ++sp;
+                cur = nearc;
+                continue;
+            } else if (tl >= 0.0f) { cur = cl; continue; }
+            else if (tr >= 0.0f) { cur = cr; continue; }
+        } else {
+            if (COUNT) ++n_prims;
+            test_leaf(sc, (uint32_t)~cur, o, d, dn, rs, best);
+        }
+        if (sp == 0) break;
+        --sp;
+        cur = sp < STACK_SMEM ? sstack[sp * WF_THREADS] : lstack[sp - STACK_SMEM];
+    }
+    return best;
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(WF_THREADS)
+k_extend(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ qd, float4* __restrict__ hits,
+         const uint32_t* __restrict__ qcount, int bounce, unsigned long long* __restrict__ stats) {
+    __shared__ int sstack[STACK_SMEM * WF_THREADS];
+    const uint32_t count = qcount[bounce];
+    uint32_t nn = 0, np = 0;
+    for (uint32_t i = blockIdx.x * WF_THREADS + threadIdx.x; i < count; i += gridDim.x * WF_THREADS) {
+        float4 o4 = ld_stream(&qo[i]), d4 = ld_stream(&qd[i]);
+        Best b = traverse<COUNT>(sc, xyz(o4), xyz(d4), sstack + threadIdx.x, nn, np);
+        st_stream(&hits[i], make_float4(b.t, __uint_as_float(b.code), b.u, b.v));
+    }
+    if (COUNT) {
+        for (int o = 16; o > 0; o >>= 1) { nn += __shfl_xor_sync(0xffffffffu, nn, o); np += __shfl_xor_sync(0xffffffffu, np, o); }
+        if ((threadIdx.x & 31) == 0 && (nn | np)) {
+            atomicAdd(&stats[PRT_MAX_DEPTH + 0], (unsigned long long)nn);
+            atomicAdd(&stats[PRT_MAX_DEPTH + 1], (unsigned long long)np);
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&stats[bounce], (unsigned long long)count);
+}
+
+// Brute force over every primitive = the reference's own algorithm (primitive.cpp:21-59);
+// used for parity (`prt_trace_batch(use_bvh=0)`), never on the render path.
+__global__ void __launch_bounds__(WF_THREADS)
+k_extend_brute(SceneView sc, const uint32_t* __restrict__ sorted_prim, const float4* __restrict__ qo,
+               const float4* __restrict__ qd, float4* __restrict__ hits, const uint32_t* __restrict__ qcount, int bounce) {
+    const uint32_t count = qcount[bounce];
+    for (uint32_t i = blockIdx.x * WF_THREADS + threadIdx.x; i < count; i += gridDim.x * WF_THREADS) {
+        float4 o4 = qo[i], d4 = qd[i];
+        V3 o = xyz(o4), d = xyz(d4);
+        RayShear rs = make_shear(d);
+        V3 dn = normalize(d);
+        Best b; best_init(b);
+        for (int pos = 0; pos < sc.n_prims; ++pos) {
+            uint32_t q = sorted_prim[pos];
+            uint32_t code = q < (uint32_t)sc.n_spheres ? PRT_MAKE_LEAF(0, q)
+                          : q < (uint32_t)(sc.n_spheres + sc.n_quads) ? PRT_MAKE_LEAF(1, q - sc.n_spheres)
+                          : PRT_MAKE_LEAF(2, pos);
+            test_leaf(sc, code, o, d, dn, rs, b);
+        }
+        hits[i] = make_float4(b.t, __uint_as_float(b.code), b.u, b.v);
+    }
+}
+
+// ------------------------------------------------------------------ shade / scatter + compaction
+__global__ void __launch_bounds__(WF_THREADS)
+k_shade(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ qd, const float4* __restrict__ qb,
+        const float4* __restrict__ hits, float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb,
+        float4* __restrict__ contrib, uint32_t* __restrict__ qcount, int bounce, int max_depth) {
+    const uint32_t count = qcount[bounce];
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t stride = gridDim.x * WF_THREADS;
+    for (uint32_t base = blockIdx.x * WF_THREADS + (threadIdx.x & ~31u); base < count; base += stride) {
+        uint32_t i = base + lane;
+        bool cont = false;
+        float4 o4, d4; V3 beta, np, ndir;
+        if (i < count) {
+            o4 = ld_stream(&qo[i]); d4 = ld_stream(&qd[i]);
+            float4 b4 = ld_stream(&qb[i]), h = ld_stream(&hits[i]);
+            beta = xyz(b4);
+            uint32_t slot = __float_as_uint(o4.w) >> 5;
+            uint32_t code = __float_as_uint(h.y);
+            V3 L = mk(0.f, 0.f, 0.f);
+            if (code == PRT_NO_HIT) {
+                L = beta * mk(sc.sky_r, sc.sky_g, sc.sky_b);            // cpu/renderer.cpp:99
+            } else {
+                V3 o = xyz(o4), d = xyz(d4);
+                Surface s = make_surface(sc, o, d, h.x, code, h.z, h.w);
+                MatRec m;
+                if (s.mat >= 0 && s.mat < sc.n_mats) { m.a = __ldg(&sc.mats[s.mat].a); m.b = __ldg(&sc.mats[s.mat].b); }
+                else { m.a = make_float4(0, 0, 0, 0); m.b = make_float4(0, 0, 0, 0); }
+                Rng rng = rng_for_bounce(__float_as_uint(d4.w), (uint32_t)bounce);
+                V3 atten, emit;
+                bool sc_ok = scatter(m, d, s, rng, atten, ndir, emit);
+                L = beta * emit;                                          // L += emitted (renderer.cpp:74)
+                if (sc_ok && bounce + 1 < max_depth) { cont = true; beta = beta * atten; np = s.p; }
+            }
+            if (!cont) st_stream(&contrib[slot], make_float4(L.x, L.y, L.z, 0.f));
+        }
+        // compaction: ballot/popc, one atomic per warp
+        uint32_t mask = __ballot_sync(0xffffffffu, cont);
+        if (mask) {
+            int leader = __ffs(mask) - 1;
+            uint32_t b0 = 0;
+            if ((int)lane == leader) b0 = atomicAdd(&qcount[bounce + 1], (uint32_t)__popc(mask));
+            b0 = __shfl_sync(0xffffffffu, b0, leader);
+            if (cont) {
+                uint32_t j = b0 + __popc(mask & ((1u << lane) - 1u));
+                st_stream(&no[j], make_float4(np.x, np.y, np.z, __uint_as_float(__float_as_uint(o4.w) + 1u)));
+                st_stream(&nd[j], make_float4(ndir.x, ndir.y, ndir.z, d4.w));
+                st_stream(&nb[j], make_float4(beta.x, beta.y, beta.z, 0.f));
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------ resolve (accumulate)
+// accum[3p+c] += sum over the wave's samples, in sample order (Film::AddSample, film.cu:37-55)
+__global__ void __launch_bounds__(WF_THREADS)
+k_resolve(const float4* __restrict__ contrib, int pix0, int npix, int n_samples, float* __restrict__ accum) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npix) return;
+    float* a = accum + 3 * (size_t)(pix0 + i);
+    float r = a[0], g = a[1], b = a[2];
+    for (int s = 0; s < n_samples; ++s) {
+        float4 c = ld_stream(&contrib[(size_t)s * npix + i]);
+        r += c.x; g += c.y; b += c.z;
+    }
+    a[0] = r; a[1] = g; a[2] = b;
+}
+
+// ------------------------------------------------------------------ film display resolve
+// Film::UpdateDisplay (film.cu:134-194): avg -> Reinhard -> pow(1/gamma) -> u8, alpha 255.
+__global__ void k_display(const float* __restrict__ accum, int npix, float inv_w, float has_w, float exposure,
+                          float inv_gamma, uint8_t* __restrict__ out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npix) return;
+    uint8_t px[4];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        float v = 0.0f;
+        if (has_w > 0.0f) {
+            v = accum[3 * (size_t)i + c] * inv_w;
+            float x = v * exposure;
+            x = x / (1.0f + x);
+            v = (float)pow((double)x, (double)inv_gamma);
+        }
+        v = fmaxf(0.0f, fminf(1.0f, v));
+        px[c] = (uint8_t)(v * 255.0f + 0.5f);
+    }
+    px[3] = 255;
+    *reinterpret_cast<uchar4*>(out + 4 * (size_t)i) = make_uchar4(px[0], px[1], px[2], px[3]);
+}
+
+// ------------------------------------------------------------------ hit records for the parity batch
+__global__ void k_hit_records(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ qd,
+                              const float4* __restrict__ hits, int n, prt_hit* __restrict__ out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 h = hits[i];
+    uint32_t code = __float_as_uint(h.y);
+    prt_hit r;
+    if (code == PRT_NO_HIT) {
+        r.t = h.x; r.prim_id = -1; r.b1 = r.b2 = 0.f; r.px = r.py = r.pz = 0.f; r.nx = r.ny = r.nz = 0.f;
+        r.front = 0; r.material = -1;
+    } else {
+        V3 o = xyz(qo[i]), d = xyz(qd[i]);
+        Surface s = make_surface(sc, o, d, h.x, code, h.z, h.w);
+        uint32_t type = PRT_LEAF_TYPE(code), idx = PRT_LEAF_INDEX(code);
+        int pid = type == 2u ? __float_as_int(sc.tri_v[3 * idx].w)
+                : type == 0u ? __float_as_int(sc.spheres[idx].b.z) : __float_as_int(sc.quads[idx].d.w);
+        r.t = h.x; r.prim_id = pid;
+        r.b1 = type == 2u ? h.z : 0.f; r.b2 = type == 2u ? h.w : 0.f;
+        r.px = s.p.x; r.py = s.p.y; r.pz = s.p.z; r.nx = s.n.x; r.ny = s.n.y; r.nz = s.n.z;
+        r.front = s.front ? 1 : 0; r.material = s.mat;
+    }
+    out[i] = r;
+}
+
+__global__ void k_load_rays(const prt_ray* __restrict__ rays, int n, float4* __restrict__ qo, float4* __restrict__ qd,
+                            uint32_t* __restrict__ qcount) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) qcount[0] = (uint32_t)n;
+    if (i >= n) return;
+    prt_ray r = rays[i];
+    qo[i] = make_float4(r.ox, r.oy, r.oz, 0.f);
+    qd[i] = make_float4(r.dx, r.dy, r.dz, 0.f);
+}
+
+// ------------------------------------------------------------------ host side
+SceneView scene_view(const Ctx* c) {
+    SceneView v{};
+    v.spheres = (const SphereRec*)c->spheres.p; v.n_spheres = c->n_spheres;
+    v.quads = (const QuadRec*)c->quads.p; v.n_quads = c->n_quads;
+    v.tri_v = (const float4*)c->tri_v.p; v.tri_n = (const float4*)c->tri_n.p; v.n_tris = c->n_tris;
+    v.mats = (const MatRec*)c->mats.p; v.n_mats = c->n_mats;
+    v.quad_mat = (const int*)c->quad_mat.p;
+    v.nodes = (const BvhNode*)c->nodes.p; v.n_prims = c->n_prims;
+    v.root_code = c->root_code;
+    v.tri_tmin = 0.001f;                                  // kShapeRayTMin, shape.h:128
+    v.sky_r = c->sky[0]; v.sky_g = c->sky[1]; v.sky_b = c->sky[2];
+    return v;
+}
+
+static CamView cam_view(const prt_camera& k) {
+    CamView v;
+    v.pos = {k.pos[0], k.pos[1], k.pos[2]};
+    v.front = {k.front[0], k.front[1], k.front[2]};
+    v.right = {k.right[0], k.right[1], k.right[2]};
+    v.up = {k.up[0], k.up[1], k.up[2]};
+    v.tan_half = k.tan_half_fov;
+    v.w = (float)k.width; v.h = (float)k.height;
+    v.aspect = v.w / v.h;                                 // m_Width / m_Height, camera.h:112
+    v.W = k.width; v.H = k.height;
+    return v;
+}
+
+static int ensure_wave_buffers(Ctx* c, int64_t paths) {
+    int rc;
+    size_t b16 = (size_t)paths * 16;
+    for (int k = 0; k < 2; ++k)
+        if ((rc = dev_reserve(c, c->q_o[k], b16)) || (rc = dev_reserve(c, c->q_d[k], b16)) ||
+            (rc = dev_reserve(c, c->q_b[k], b16))) return rc;
+    if ((rc = dev_reserve(c, c->hits, b16)) || (rc = dev_reserve(c, c->contrib, b16))) return rc;
+    if ((rc = dev_reserve(c, c->qcount, (PRT_MAX_DEPTH + 2) * 4))) return rc;
+    if ((rc = dev_reserve(c, c->stats_dev, (PRT_MAX_DEPTH + 4) * 8))) return rc;
+    return PRT_OK;
+}
+
+int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_begin) {
+    const int W = c->cam.width, H = c->cam.height;
+    const int64_t P = (int64_t)W * H;
+    cudaStream_t st = c->stream;
+    int64_t cap = c->wave_paths_opt > 0 ? c->wave_paths_opt : (int64_t)8 << 20;
+    cap = std::min<int64_t>(cap, (int64_t)1 << 26);                  // slot must fit 27 bits
+    // wave = pixel range [p0, p0+npix) x S samples
+    int64_t npix_wave = std::min<int64_t>(P, cap);
+    int S_wave = (int)std::max<int64_t>(1, std::min<int64_t>(spp, cap / npix_wave));
+    int rc;
+    if ((rc = ensure_wave_buffers(c, npix_wave * S_wave))) return rc;
+    c->wave_paths = npix_wave * S_wave;
+
+    SceneView sc = scene_view(c);
+    CamView cam = cam_view(c->cam);
+    uint32_t* qcount = (uint32_t*)c->qcount.p;
+    unsigned long long* dstats = (unsigned long long*)c->stats_dev.p;
+    const int grid_p = c->num_sms * c->ctas_per_sm;
+    const uint32_t seed_lo = (uint32_t)seed, seed_hi = (uint32_t)(seed >> 32);
+
+    std::vector<cudaEvent_t> evs;
+    auto new_event = [&]() { cudaEvent_t e; cudaEventCreate(&e); evs.push_back(e); return e; };
+
+    PRT_CUDA(c, cudaMemsetAsync(dstats, 0, (PRT_MAX_DEPTH + 4) * 8, st));
+    PRT_CUDA(c, cudaEventRecord(c->ev0, st));
+    int launches = 0;
+    uint64_t paths = 0;
+    for (int s0 = 0; s0 < spp; s0 += S_wave) {
+        const int S = std::min(S_wave, spp - s0);
+        for (int64_t p0 = 0; p0 < P; p0 += npix_wave) {
+            const int npix = (int)std::min<int64_t>(npix_wave, P - p0);
+            const int n_paths = npix * S;
+            paths += (uint64_t)n_paths;
+            PRT_CUDA(c, cudaMemsetAsync(qcount, 0, (PRT_MAX_DEPTH + 2) * 4, st));
+            k_raygen<<<(n_paths + WF_THREADS - 1) / WF_THREADS, WF_THREADS, 0, st>>>(
+                cam, (int)p0, npix, n_paths, (uint32_t)(sample_begin + s0), seed_lo, seed_hi,
+                (float4*)c->q_o[0].p, (float4*)c->q_d[0].p, (float4*)c->q_b[0].p, qcount);
+            ++launches;
+            int cur = 0;
+            const int grid = (int)std::min<int64_t>(grid_p, (n_paths + WF_THREADS - 1) / WF_THREADS);
+            for (int b = 0; b < max_depth; ++b) {
+                cudaEvent_t e0 = new_event(), e1 = new_event(), e2 = new_event();
+                cudaEventRecord(e0, st);
+                if (c->counters_on)
+                    k_extend<true><<<grid, WF_THREADS, 0, st>>>(sc, (const float4*)c->q_o[cur].p, (const float4*)c->q_d[cur].p,
+                                                                (float4*)c->hits.p, qcount, b, dstats);
+                else
+                    k_extend<false><<<grid, WF_THREADS, 0, st>>>(sc, (const float4*)c->q_o[cur].p, (const float4*)c->q_d[cur].p,
+                                                                 (float4*)c->hits.p, qcount, b, dstats);
+                cudaEventRecord(e1, st);
+                k_shade<<<grid, WF_THREADS, 0, st>>>(sc, (const float4*)c->q_o[cur].p, (const float4*)c->q_d[cur].p,
+                                                     (const float4*)c->q_b[cur].p, (const float4*)c->hits.p,
+                                                     (float4*)c->q_o[cur ^ 1].p, (float4*)c->q_d[cur ^ 1].p,
+                                                     (float4*)c->q_b[cur ^ 1].p, (float4*)c->contrib.p, qcount, b, max_depth);
+                cudaEventRecord(e2, st);
+                launches += 2;
+                cur ^= 1;
+            }
+            k_resolve<<<(npix + WF_THREADS - 1) / WF_THREADS, WF_THREADS, 0, st>>>(
+                (const float4*)c->contrib.p, (int)p0, npix, S, c->accum);
+            ++launches;
+        }
+    }
+    PRT_CUDA(c, cudaEventRecord(c->ev1, st));
+    PRT_CUDA(c, cudaStreamSynchronize(st));
+    PRT_CUDA(c, cudaGetLastError());
+    c->accum_spp += spp;
+
+    unsigned long long h[PRT_MAX_DEPTH + 4];
+    PRT_CUDA(c, cudaMemcpy(h, dstats, sizeof(h), cudaMemcpyDeviceToHost));
+    prt_stats& s = c->stats;
+    s.rays_total = 0;
+    for (int b = 0; b < PRT_MAX_DEPTH; ++b) { s.rays_per_bounce[b] = h[b]; s.rays_total += h[b]; }
+    s.nodes_visited = h[PRT_MAX_DEPTH]; s.prims_tested = h[PRT_MAX_DEPTH + 1];
+    s.paths = paths;
+    s.kernel_launches = launches;
+    cudaEventElapsedTime(&s.render_ms, c->ev0, c->ev1);
+    float ext = 0.f, shd = 0.f;
+    for (size_t k = 0; k + 2 < evs.size(); k += 3) {
+        float a = 0.f, b2 = 0.f;
+        cudaEventElapsedTime(&a, evs[k], evs[k + 1]);
+        cudaEventElapsedTime(&b2, evs[k + 1], evs[k + 2]);
+        ext += a; shd += b2;
+    }
+    for (cudaEvent_t e : evs) cudaEventDestroy(e);
+    s.extend_ms = ext; s.shade_ms = shd;
+    s.n_prims = c->n_prims; s.n_nodes = c->n_prims > 1 ? c->n_prims - 1 : 0;
+    return PRT_OK;
+}
+
+int wavefront_trace_batch(Ctx* c, const prt_ray* rays, int n, prt_hit* out, int use_bvh) {
+    if (n <= 0) return PRT_OK;
+    cudaStream_t st = c->stream;
+    int rc;
+    if ((rc = ensure_wave_buffers(c, std::max<int64_t>(n, 1)))) return rc;
+    DevBuf d_rays, d_out;
+    if ((rc = dev_reserve(c, d_rays, (size_t)n * sizeof(prt_ray))) || (rc = dev_reserve(c, d_out, (size_t)n * sizeof(prt_hit)))) {
+        dev_free(d_rays); dev_free(d_out); return rc;
+    }
+    SceneView sc = scene_view(c);
+    uint32_t* qcount = (uint32_t*)c->qcount.p;
+    unsigned long long* dstats = (unsigned long long*)c->stats_dev.p;
+    cudaMemcpyAsync(d_rays.p, rays, (size_t)n * sizeof(prt_ray), cudaMemcpyHostToDevice, st);
+    cudaMemsetAsync(dstats, 0, (PRT_MAX_DEPTH + 4) * 8, st);
+    const int G = (n + WF_THREADS - 1) / WF_THREADS;
+    k_load_rays<<<G, WF_THREADS, 0, st>>>((const prt_ray*)d_rays.p, n, (float4*)c->q_o[0].p, (float4*)c->q_d[0].p, qcount);
+    const int grid = std::min(G, c->num_sms * c->ctas_per_sm);
+    if (use_bvh) {
+        if (c->counters_on)
+            k_extend<true><<<grid, WF_THREADS, 0, st>>>(sc, (const float4*)c->q_o[0].p, (const float4*)c->q_d[0].p, (float4*)c->hits.p, qcount, 0, dstats);
+        else
+            k_extend<false><<<grid, WF_THREADS, 0, st>>>(sc, (const float4*)c->q_o[0].p, (const float4*)c->q_d[0].p, (float4*)c->hits.p, qcount, 0, dstats);
+    } else {
+        k_extend_brute<<<grid, WF_THREADS, 0, st>>>(sc, (const uint32_t*)c->vals[c->sorted_slot].p, (const float4*)c->q_o[0].p,
+                                                    (const float4*)c->q_d[0].p, (float4*)c->hits.p, qcount, 0);
+    }
+    k_hit_records<<<G, WF_THREADS, 0, st>>>(sc, (const float4*)c->q_o[0].p, (const float4*)c->q_d[0].p,
+                                            (const float4*)c->hits.p, n, (prt_hit*)d_out.p);
+    cudaMemcpyAsync(out, d_out.p, (size_t)n * sizeof(prt_hit), cudaMemcpyDeviceToHost, st);
+    cudaError_t e = cudaStreamSynchronize(st);
+    if (e == cudaSuccess) e = cudaGetLastError();
+    unsigned long long h[PRT_MAX_DEPTH + 4];
+    if (e == cudaSuccess) e = cudaMemcpy(h, dstats, sizeof(h), cudaMemcpyDeviceToHost);
+    dev_free(d_rays); dev_free(d_out);
+    if (e != cudaSuccess) return set_err(c, PRT_ERR_CUDA, std::string("trace_batch: ") + cudaGetErrorString(e));
+    c->stats.nodes_visited = h[PRT_MAX_DEPTH]; c->stats.prims_tested = h[PRT_MAX_DEPTH + 1];
+    c->stats.rays_total = h[0];
+    return PRT_OK;
+}
+
+__global__ void k_scale(float* a, size_t n, float s) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) a[i] *= s;
+}
+int film_scale_accum(Ctx* c, float s) {
+    size_t n = (size_t)c->cam.width * c->cam.height * 3;
+    k_scale<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(c->accum, n, s);
+    PRT_CUDA(c, cudaStreamSynchronize(c->stream));
+    return PRT_OK;
+}
+
+int film_resolve_display(Ctx* c, float exposure, float gamma, uint8_t* host_rgba) {
+    const int npix = c->cam.width * c->cam.height;
+    int rc;
+    if ((rc = dev_reserve(c, c->display, (size_t)npix * 4))) return rc;
+    float w = (float)c->accum_spp;
+    k_display<<<(npix + 255) / 256, 256, 0, c->stream>>>(c->accum, npix, w > 0.f ? 1.0f / w : 0.f, w, exposure,
+                                                        1.0f / gamma, (uint8_t*)c->display.p);
+    PRT_CUDA(c, cudaMemcpyAsync(host_rgba, c->display.p, (size_t)npix * 4, cudaMemcpyDeviceToHost, c->stream));
+    PRT_CUDA(c, cudaStreamSynchronize(c->stream));
+    return PRT_OK;
+}
+
+}  // namespace prt

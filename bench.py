@@ -1,0 +1,379 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the B200 path-tracing backend (contract: see README / DESIGN.md).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
+
+One "step" = one pass of the hot path over one batch: render `spp` samples/pixel of the workload
+(default: BASELINE.json configs[1] = reference Cornell scene, 1920x1080, 256 spp, depth 8) into the
+float accumulation buffer; with N>1 ranks (torchrun, one per GPU) every rank renders its own sample
+range of the same frame (weak scaling: 256 spp per GPU) and the buffers are sum-reduced with NCCL.
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (scene factory name, W, H, spp per step, depth, camera)
+    "cornell_1080p_256spp_d8": dict(scene="cornell", W=1920, H=1080, spp=256, depth=8),
+    "random_balls_large_1080p_64spp_d8": dict(scene="random_balls_large", W=1920, H=1080, spp=64, depth=8),
+    "closed_cornell_1080p_64spp_d8": dict(scene="closed_cornell", W=1920, H=1080, spp=64, depth=8),
+    "dragon960k_1080p_16spp_d8": dict(scene="dragon960k", W=1920, H=1080, spp=16, depth=8),
+    "soup10m_1080p_4spp_d16": dict(scene="soup10m", W=1920, H=1080, spp=4, depth=16),
+    "soup1m_1080p_8spp_d16": dict(scene="soup1m", W=1920, H=1080, spp=8, depth=16),
+}
+DEFAULT_WORKLOAD = "cornell_1080p_256spp_d8"
+
+
+def make_workload(name):
+    from parallelraytracing_b200 import scene as S
+    w = WORKLOADS[name]
+    s = w["scene"]
+    cam = S.Camera(width=w["W"], height=w["H"])                       # viewer camera (5,5,8)->0, main.cpp:142-150
+    if s == "cornell":
+        sd = S.cornell()
+    elif s == "random_balls_large":
+        sd = S.make_scene(S.ScenePreset.RANDOM_BALLS_LARGE)
+    elif s == "closed_cornell":
+        sd = S.closed_cornell()
+    elif s == "dragon960k":
+        z = np.load(os.path.join(ROOT, "tests", "golden", "reference_vectors.npz"))
+        sd = S.mesh_scene((z["mesh_dragon_v"], z["mesh_dragon_n"], z["mesh_dragon_f"]), subdiv=2, name="dragon960k")
+        cam = S.Camera(pos=(0.0, 1.0, 5.0), front=S._normalize(S._v3(0, -1, -5)), width=w["W"], height=w["H"])
+    elif s in ("soup10m", "soup1m"):
+        sd = S.random_triangle_soup(10_000_000 if s == "soup10m" else 1_000_000)
+        cam = S.Camera(pos=(0.0, 0.0, 150.0), front=(0.0, 0.0, -1.0), width=w["W"], height=w["H"])
+    else:
+        raise ValueError(s)
+    return sd, cam, w
+
+
+def scene_bytes(sd):
+    n = sd.spheres.nbytes + sd.quads.nbytes + sd.materials.nbytes
+    if sd.n_tris:
+        n += sd.tri_verts.nbytes + sd.tri_normals.nbytes + sd.tri_material.nbytes
+    return int(n)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True); self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        pw = [float(r[2]) for r in self.rows if len(r) >= 7 and r[2].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) >= 7 and r[3 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": reasons}
+
+
+# ---------------------------------------------------------------- CPU arm (oracle/ is used ONLY here)
+PRESET_OF = {"cornell": 3, "random_balls_large": 6}
+
+
+class CpuArm:
+    """The reference's own CPU implementation of the path, timed on this host's cores:
+    oracle/_ref (reference Scene::Intersect, MaterialHandle::Scatter/Emit, Camera::GetCameraRay compiled
+    from the reference sources + the TraceRay recursion of cpu/renderer.cpp:59-103 with a depth
+    parameter and the deterministic rand()) when it was built, else the oracle port."""
+
+    def __init__(self, workload):
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import oracle_lib
+        self.sd, self.cam, self.w = make_workload(workload)
+        self.cores = os.cpu_count() or 1
+        ref = oracle_lib.load_ref()
+        if ref is not None and self.w["scene"] in PRESET_OF:
+            self.kind, self.scene = "reference", ref.preset(PRESET_OF[self.w["scene"]])
+            self._render = lambda spp, y0, y1, s0: self.scene.render(self.cam, spp, self.w["depth"], seed=1, sample_begin=s0,
+                                                                     n_threads=self.cores, y_begin=y0, y_end=y1)
+        else:
+            self.kind, self.scene = "port", oracle_lib.load_oracle().scene(self.sd)
+            self.scene.build_lbvh()
+            self._render = lambda spp, y0, y1, s0: self.scene.render(self.cam, spp, self.w["depth"], seed=1, sample_begin=s0,
+                                                                     use_bvh=True, n_threads=self.cores, y_begin=y0, y_end=y1)
+
+    def run(self, spp, rows=None):
+        """Render `spp` samples of a centred band of `rows` rows (None = whole frame). Returns (seconds, rays)."""
+        H = self.cam.height
+        y0 = 0 if rows is None else (H - rows) // 2
+        t = time.perf_counter()
+        _, rays = self._render(spp, y0, H if rows is None else y0 + rows, 0)
+        return time.perf_counter() - t, rays
+
+    def calibrate(self, target_s):
+        """Pick (spp, rows) so one sample run takes about target_s."""
+        H = self.cam.height
+        rows = max(8, H // 16)
+        dt, rays = self.run(1, rows)
+        per_row_spp = max(dt, 1e-4) / rows
+        full_spp = per_row_spp * H
+        if full_spp <= target_s:
+            return max(1, int(target_s / full_spp)), None
+        return 1, max(8, min(H, int(target_s / per_row_spp)))
+
+    def describe(self, spp, rows):
+        H, W = self.cam.height, self.cam.width
+        what = ("reference Intersect/Scatter/GetCameraRay (oracle/_ref) + TraceRay recursion, deterministic rand()"
+                if self.kind == "reference" else "oracle port (CPU LBVH traversal, not the reference's brute force)")
+        return "%s: %d spp x %d of %d rows x %d px, depth %d, %d threads" % (what, spp, H if rows is None else rows, H, W,
+                                                                            self.w["depth"], self.cores)
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    arm = CpuArm(args.workload)
+    target = max(1.0, min(10.0, 150.0 / max(1, args.steps + args.warmup)))
+    spp, rows = arm.calibrate(target)
+    for _ in range(args.warmup):
+        arm.run(spp, rows)
+    t_tot, r_tot = 0.0, 0
+    for _ in range(args.steps):
+        dt, rays = arm.run(spp, rows)
+        t_tot += dt; r_tot += rays
+    val = r_tot / t_tot / 1e6
+    W, H = arm.cam.width, arm.cam.height
+    frac = spp * (1.0 if rows is None else rows / H)
+    out = {"impl": "reference", "metric": "Mrays/s", "value": val, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": 1e3 * t_tot / args.steps, "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": args.workload, "width": W, "height": H, "depth": arm.w["depth"], "sample_per_step_spp": frac},
+           "spp_per_s_1080p": frac * args.steps / t_tot,
+           "cpu_baseline": {"value": val, "unit": "Mrays/s", "cores": arm.cores, "kind": arm.kind, "sample": arm.describe(spp, rows)},
+           "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(out))
+    return 0
+
+
+# ---------------------------------------------------------------- GPU arm
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from parallelraytracing_b200.capi import Context
+
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    sd, cam, w = make_workload(args.workload)
+    W, H, spp, depth = w["W"], w["H"], w["spp"], w["depth"]
+    ctx = Context(local)
+    ctx.set_scene(sd); ctx.build_bvh(); ctx.set_camera(cam)
+    build_ms = ctx.stats().build_ms
+    # the accumulation buffer is a torch tensor so that NCCL can reduce it in place
+    accum = torch.zeros(H * W * 3, dtype=torch.float32, device="cuda")
+    ctx.set_accum_buffer(accum.data_ptr())
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")       # > 126 MB L2
+    host_img = torch.empty(H * W * 3, dtype=torch.float32).pin_memory()
+
+    def step(i, timed_events=None):
+        """rank r renders samples [r*spp, (r+1)*spp) of step i's frame; sum-reduce to rank 0."""
+        accum.zero_()
+        ctx.clear_accum()
+        ctx.render(spp, depth, seed=1 + i, sample_begin=rank * spp)
+        if world > 1:
+            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for i in range(args.warmup):
+        step(i)
+    sync_all()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    # ---- timed region: device time of prt_render (CUDA events on the context's own stream, read back
+    # through prt_get_stats) + the reduce (torch events on torch's stream), max over ranks
+    rays = 0; launches = 0; render_ms = 0.0; ext_ms = 0.0; shd_ms = 0.0; red_ms = 0.0
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sync_all()
+    t_wall = time.perf_counter()
+    for i in range(args.steps):
+        flush.zero_()                                                     # L2 flush between timed iterations
+        accum.zero_()
+        ctx.clear_accum()
+        torch.cuda.synchronize()
+        ctx.render(spp, depth, seed=100 + i, sample_begin=rank * spp)     # synchronous, like ProgressiveRender
+        st = ctx.stats()
+        rays += st.rays_total; launches += st.kernel_launches
+        render_ms += st.render_ms; ext_ms += st.extend_ms; shd_ms += st.shade_ms
+        if world > 1:
+            e0.record(); dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM); e1.record(); torch.cuda.synchronize()
+            red_ms += e0.elapsed_time(e1)
+    sync_all()
+    wall_ms = 1e3 * (time.perf_counter() - t_wall)
+    clk = clocks.stop() if rank == 0 else None
+    dev_ms = render_ms + red_ms
+    if world > 1:
+        t = torch.tensor([dev_ms, float(rays), float(launches)], dtype=torch.float64, device="cuda")
+        tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        dev_ms_max, rays_all, launches_all = float(tmax[0]), float(tsum[1]), int(tsum[2])
+    else:
+        dev_ms_max, rays_all, launches_all = dev_ms, float(rays), launches
+
+    # ---- e2e: the call a user makes (Renderer interface, HOST scene in, HOST image out), every step
+    from parallelraytracing_b200 import B200Renderer, Film
+    film, r = Film(W, H), B200Renderer(device=local, max_depth=depth, samples_per_call=spp, seed=1)
+    r.ctx = ctx                                                          # same device context (allocations stay warm)
+    ctx.set_accum_buffer(None)
+    e2e_rays = 0
+    sync_all()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        r.SetSeed(200 + i); r.SetNextSample(rank * spp)
+        r.Init(film, sd, cam)                 # host scene -> H2D upload + GPU LBVH build + camera
+        film.Clear()
+        r.ProgressiveRender()
+        img = film.ReadAccum()                # D2H of the float image
+        e2e_rays += r.Stats().rays_total
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_s, float(e2e_rays)], dtype=torch.float64, device="cuda")
+        tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        e2e_s, e2e_rays = float(tmax[0]), float(tsum[1])
+    return dict(rank=rank, world=world, ctx=ctx, sd=sd, cam=cam, w=w, rays_all=rays_all, dev_ms_max=dev_ms_max,
+                launches_all=launches_all, ext_ms=ext_ms, shd_ms=shd_ms, render_ms=render_ms, red_ms=red_ms, rays=rays,
+                clk=clk, e2e_s=e2e_s, e2e_rays=e2e_rays, build_ms=build_ms, wall_ms=wall_ms, img_mean=float(img.mean()))
+
+
+def roofline_and_json(args, R):
+    ctx, w, sd = R["ctx"], R["w"], R["sd"]
+    W, H, spp, depth = w["W"], w["H"], w["spp"], w["depth"]
+    steps = args.steps
+    # per-ray traversal work from the device counters (untimed pass, counters cost speed)
+    ctx.enable_counters(True)
+    ctx.clear_accum(); ctx.render(min(spp, 4), depth, seed=999, sample_begin=0)
+    st = ctx.stats()
+    ctx.enable_counters(False)
+    n_node = st.nodes_visited / max(1, st.rays_total)
+    n_leaf = st.prims_tested / max(1, st.rays_total)
+    rays_step = R["rays"] / steps                      # this rank
+    paths_step = W * H * spp
+    # ALGORITHMIC bytes per launch-set (DESIGN.md "Algorithmic bytes"): extend = 32 B ray in + 16 B hit out
+    # + 64 B per node visited + 48 B per leaf primitive tested; shade = 64 B in (ray 32, beta 16, hit 16)
+    # + 48 B out per continuing ray + 16 B out per terminating path + 16|96 B surface record per hit
+    leaf_rec = 96 if sd.n_tris > (len(sd.spheres) + len(sd.quads)) else 16
+    ext_bytes = rays_step * (48 + 64 * n_node + 48 * n_leaf)
+    cont = rays_step - paths_step
+    shd_bytes = rays_step * 64 + cont * 48 + paths_step * 16 + rays_step * leaf_rec
+    ext_ms, shd_ms = R["ext_ms"] / steps, R["shd_ms"] / steps
+    peak, peak_src = peaks()
+    if ext_ms >= shd_ms:
+        name, ach, ms_k, nl = "k_extend (persistent LBVH traversal)", ext_bytes / (ext_ms * 1e-3) / 1e9, ext_ms, depth
+    else:
+        name, ach, ms_k, nl = "k_shade (scatter + compaction)", shd_bytes / (shd_ms * 1e-3) / 1e9, shd_ms, depth
+    roof = {"bound": "hbm", "kernel": name, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+            "traffic": None, "peak_source": peak_src, "kernel_ms_per_step": ms_k,
+            "extend_ms_per_step": ext_ms, "shade_ms_per_step": shd_ms, "render_ms_per_step": R["render_ms"] / steps,
+            "nodes_per_ray": n_node, "leaf_tests_per_ray": n_leaf,
+            "algorithmic_bytes_per_ray": {"extend": 48 + 64 * n_node + 48 * n_leaf, "shade": shd_bytes / max(1.0, rays_step)},
+            "note": "achieved = algorithmic bytes of all launches of the kernel in one step / their summed CUDA-event time; "
+                    "tiny scenes are issue-bound (nodes stay in L1/L2), so frac<<1 is expected there"}
+    dev_s = R["dev_ms_max"] * 1e-3
+    value = R["rays_all"] / dev_s / 1e6
+    out = {"metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": R["world"], "steps": steps, "warmup": args.warmup,
+           "ms_per_step": R["dev_ms_max"] / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+           "dtype": "f32", "data": "synthetic",
+           "config": {"workload": args.workload, "scene": sd.name, "prims": sd.n_prims, "width": W, "height": H,
+                      "spp_per_step_per_gpu": spp, "depth": depth, "partition": "sample-range, NCCL sum-reduce to rank 0",
+                      "l2": "256 MiB flush between timed steps; queues (%.0f MB) also exceed L2" % (ctx.stats().paths * 0 + 8 * (1 << 20) * 112 / 1e6)},
+           "spp_per_s_1080p": R["world"] * spp * steps / dev_s,
+           "mpaths_per_s": R["world"] * paths_step * steps / dev_s / 1e6,
+           "rays_per_path": rays_step / paths_step,
+           "e2e": {"value": R["e2e_rays"] / R["e2e_s"] / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": scene_bytes(sd) + 64,
+                   "d2h_bytes_per_step": W * H * 12, "what": "B200Renderer.Init(host scene)+ProgressiveRender+Film.ReadAccum per step, wall clock"},
+           "gpu_launches": R["launches_all"], "bvh_build_ms": R["build_ms"], "reduce_ms_per_step": R["red_ms"] / steps,
+           "wall_ms_per_step": R["wall_ms"] / steps, "clocks": R["clk"], "roofline": roof}
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    R = run_ours(args)
+    if R["rank"] == 0:
+        out = roofline_and_json(args, R)
+        if R["world"] == 1 and not args.no_cpu_baseline:
+            arm = CpuArm(args.workload)
+            spp, rows = arm.calibrate(12.0)
+            dt, rays = arm.run(spp, rows)
+            out["cpu_baseline"] = {"value": rays / dt / 1e6, "unit": "Mrays/s", "cores": arm.cores, "kind": arm.kind,
+                                   "sample": arm.describe(spp, rows), "seconds": dt}
+        else:
+            out["cpu_baseline"] = None
+        print(json.dumps(out))
+    if R["world"] > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

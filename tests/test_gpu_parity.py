@@ -1,0 +1,220 @@
+"""GPU parity tests (-m gpu): the sm_100a CUDA path, called through the C ABI (include/prt.h), against
+the CPU oracle on the same seeded inputs — bit-exact on integer work (Morton codes, sorted order,
+Karras topology, closest-hit ids) and, because both sides run the same IEEE operation order, bit-exact
+on t / positions / radiance too; plus the committed reference vectors (tests/golden) with the
+tolerances of SURVEY 8c."""
+import numpy as np
+import pytest
+
+import util
+from parallelraytracing_b200 import scene as S
+from parallelraytracing_b200.capi import Context, PrtError
+
+pytestmark = pytest.mark.gpu
+PRESETS = {p.name.lower(): int(p) for p in S.ScenePreset}
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return np.load(util.GOLDEN + "/reference_vectors.npz")
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = Context(0)
+    yield c
+    c.close()
+
+
+def dragon_scene(gold, instances=((0, 0, 0),), subdiv=0):
+    return S.mesh_scene((gold["mesh_dragon_v"], gold["mesh_dragon_n"], gold["mesh_dragon_f"]), subdiv=subdiv,
+                        instances=instances, name="dragon")
+
+
+SCENES = {
+    "cornell": lambda g: S.cornell(),
+    "default": lambda g: S.make_scene(S.ScenePreset.DEFAULT),
+    "random_balls_large": lambda g: S.make_scene(S.ScenePreset.RANDOM_BALLS_LARGE),
+    "closed_cornell": lambda g: S.closed_cornell(),
+    "dragon3": lambda g: dragon_scene(g, ((-1.5, 0, 0), (0, 0, 0), (1.5, 0, 0))),
+    "soup20k": lambda g: S.random_triangle_soup(20000),
+}
+
+
+# ---------------------------------------------------------------- LBVH: integer work bit-exact
+@pytest.mark.parametrize("name", sorted(SCENES))
+def test_lbvh_bit_exact(ctx, oracle, gold, name):
+    sd = SCENES[name](gold)
+    ctx.set_scene(sd); ctx.build_bvh()
+    g = ctx.debug_lbvh()
+    o = oracle.scene(sd).get_lbvh()
+    assert np.array_equal(g["scene_bounds"], o["scene_bounds"])
+    assert np.array_equal(g["morton"], o["morton"]), "Morton codes"
+    assert np.array_equal(g["sorted_prim"], o["sorted_prim"]), "sorted primitive order (stable radix sort)"
+    assert np.array_equal(g["node_children"], o["node_children"]), "Karras topology"
+    assert np.array_equal(g["node_parent"], o["node_parent"])
+    assert np.array_equal(g["node_bounds"], o["node_bounds"]), "refit bounds"
+
+
+def test_lbvh_large_properties(ctx):
+    """1M-triangle soup (oracle too slow for a full compare in the GPU suite): size-independent
+    properties — sorted keys, permutation, every node's box contains its children, one root."""
+    sd = S.random_triangle_soup(1_000_000)
+    ctx.set_scene(sd); ctx.build_bvh()
+    g = ctx.debug_lbvh()
+    n = sd.n_prims
+    keys = g["morton"][g["sorted_prim"]]
+    assert np.all(np.diff(keys.astype(np.int64)) >= 0), "sortedness"
+    same = np.diff(keys.astype(np.int64)) == 0
+    assert np.all(np.diff(g["sorted_prim"].astype(np.int64))[same] > 0), "stability: ties keep input order"
+    assert np.array_equal(np.sort(g["sorted_prim"]), np.arange(n, dtype=np.uint32)), "permutation"
+    ch = g["node_children"]
+    assert (g["node_parent"] == -1).sum() == 1 and g["node_parent"][0] == -1
+    internal = ch[ch >= 0]
+    assert np.array_equal(np.sort(internal), np.arange(1, n - 1)), "every internal node but the root is a child once"
+    leaves = ~ch[ch < 0]
+    assert np.array_equal(np.sort(leaves), np.arange(n)), "every leaf is a child once"
+    # child boxes of node i enclose the boxes stored in the child node
+    nb = g["node_bounds"]
+    for side in (0, 1):
+        c = ch[:, side]; m = c >= 0
+        box_min, box_max = nb[m, 6 * side:6 * side + 3], nb[m, 6 * side + 3:6 * side + 6]
+        cmin = np.minimum(nb[c[m], 0:3], nb[c[m], 6:9]); cmax = np.maximum(nb[c[m], 3:6], nb[c[m], 9:12])
+        assert np.array_equal(box_min, cmin) and np.array_equal(box_max, cmax)
+
+
+# ---------------------------------------------------------------- closest hit on fixed ray batches
+@pytest.mark.parametrize("name", sorted(SCENES))
+def test_closest_hit_bit_exact_vs_oracle(ctx, oracle, gold, name):
+    sd = SCENES[name](gold)
+    ctx.set_scene(sd); ctx.build_bvh()
+    rays = util.fixed_ray_batch(sd, 65536, seed=1, clamp_extent=60.0)
+    ctx.enable_counters(True)
+    got = ctx.trace_batch(rays, use_bvh=True)
+    st = ctx.stats()
+    ctx.enable_counters(False)
+    cnt = np.zeros(2, np.uint64)
+    want = oracle.scene(sd).trace_batch(rays, use_bvh=True, counters=cnt)
+    assert np.array_equal(got["prim_id"], want["prim_id"]), "closest-hit primitive ids"
+    assert np.array_equal(got, want), "full hit records (t, barycentrics, position, normal, face, material)"
+    assert np.array_equal(np.argsort(got["t"], kind="stable"), np.argsort(want["t"], kind="stable")), "t-ordering"
+    assert (st.nodes_visited, st.prims_tested) == (int(cnt[0]), int(cnt[1])), "traversal counters reproduce on the CPU"
+    assert (got["prim_id"] >= 0).mean() > 0.05
+
+
+@pytest.mark.parametrize("name", ["cornell", "random_balls_large", "soup20k"])
+def test_gpu_brute_force_equals_bvh(ctx, gold, name):
+    """The reference's own algorithm (loop over every primitive, primitive.cpp:26) on the GPU gives the
+    same records as the LBVH traversal."""
+    sd = SCENES[name](gold)
+    ctx.set_scene(sd); ctx.build_bvh()
+    rays = util.fixed_ray_batch(sd, 4096, seed=3, clamp_extent=60.0)
+    assert np.array_equal(ctx.trace_batch(rays, use_bvh=True), ctx.trace_batch(rays, use_bvh=False))
+
+
+@pytest.mark.parametrize("name", ["default", "material_test", "cornell", "random_balls_large"])
+def test_closest_hit_vs_reference_vectors(ctx, gold, name):
+    sd = util.scene_from_npz(gold, "scene_" + name)
+    ctx.set_scene(sd); ctx.build_bvh()
+    rays, ref_hits, second = gold["hits_%s_rays" % name], gold["hits_%s_ref" % name], gold["hits_%s_second" % name]
+    got = ctx.trace_batch(rays)
+    with np.errstate(invalid="ignore"):
+        near = np.abs(second - ref_hits["t"]) <= 1e-4 * np.maximum(1.0, ref_hits["t"])
+    idm = ref_hits["prim_id"] != got["prim_id"]
+    assert not (idm & ~near).any()
+    ok = (ref_hits["prim_id"] >= 0) & ~idm
+    assert np.all(np.abs(ref_hits["t"][ok] - got["t"][ok]) <= 1e-4 * np.maximum(1.0, ref_hits["t"][ok]))
+    assert np.array_equal(ref_hits["front"][ok], got["front"][ok])
+
+
+# ---------------------------------------------------------------- radiance
+@pytest.mark.parametrize("name,W,H,spp,depth", [("cornell", 128, 128, 8, 8), ("default", 96, 96, 4, 8),
+                                                 ("random_balls_large", 96, 54, 4, 8), ("closed_cornell", 96, 96, 4, 8),
+                                                 ("dragon3", 64, 64, 2, 8), ("soup20k", 64, 64, 2, 16)])
+def test_image_bit_exact_vs_oracle(ctx, oracle, gold, name, W, H, spp, depth):
+    sd = SCENES[name](gold)
+    cam = S.Camera(width=W, height=H) if name not in ("dragon3",) else \
+        S.Camera(pos=(0.0, 1.0, 5.0), front=S._normalize(S._v3(0, -1, -5)), width=W, height=H)
+    if name == "soup20k":
+        cam = S.Camera(pos=(0.0, 0.0, 150.0), front=(0.0, 0.0, -1.0), width=W, height=H)
+    ctx.set_scene(sd); ctx.build_bvh(); ctx.set_camera(cam); ctx.clear_accum()
+    ctx.render(spp, depth, seed=7)
+    got = ctx.read_accum()
+    want, rays = oracle.scene(sd).render(cam, spp, depth, seed=7)
+    st = ctx.stats()
+    assert st.rays_total == rays, "closest-hit query count"
+    m = util.image_metrics(want / spp, got / spp)
+    assert np.array_equal(got, want), m
+
+
+@pytest.mark.parametrize("name", ["cornell", "default", "material_test", "random_balls_large", "light_test"])
+def test_image_vs_reference_vectors(ctx, gold, name):
+    """Against the reference tier-2 render (reference Intersect/Scatter/GetCameraRay + deterministic
+    rand): RMSE <= 1e-3 and max rel <= 1e-2 over non-flip pixels; flips (coplanar-tie decisions) counted."""
+    W, H, spp, depth, seed, ref_rays = (int(x) for x in gold["img_%s_meta" % name])
+    sd = util.scene_from_npz(gold, "scene_" + name)
+    ctx.set_scene(sd); ctx.build_bvh(); ctx.set_camera(S.Camera(width=W, height=H)); ctx.clear_accum()
+    ctx.render(spp, depth, seed=seed)
+    m = util.image_metrics(gold["img_%s" % name] / spp, ctx.read_accum() / spp)
+    assert m["flips"] <= (0.02 if name == "cornell" else 0.002) * m["n"], m
+    assert m["rmse_nonflip"] <= 1e-3 and m["max_rel_nonflip"] <= 1e-2, m
+
+
+def test_sample_ranges_compose(ctx, gold):
+    """Multi-GPU sharding rule: samples [0,6) == [0,2) + [2,6), any wave size."""
+    sd = S.closed_cornell(); cam = S.Camera(width=80, height=60)
+    ctx.set_scene(sd); ctx.build_bvh(); ctx.set_camera(cam)
+    ctx.clear_accum(); ctx.render(6, 8, seed=3); a = ctx.read_accum()
+    ctx.clear_accum(); ctx.render(2, 8, seed=3, sample_begin=0); ctx.render(4, 8, seed=3, sample_begin=2); b = ctx.read_accum()
+    assert np.array_equal(a, b) and ctx.accum_spp() == 6
+    ctx.set_option("wave_paths", 7000)                 # forces pixel-range waves with ragged tails
+    ctx.clear_accum(); ctx.render(6, 8, seed=3); c = ctx.read_accum()
+    ctx.set_option("wave_paths", 0)
+    assert np.array_equal(a, c)
+
+
+def test_display_resolve_exact(ctx, oracle):
+    sd = S.cornell(); cam = S.Camera(width=64, height=64)
+    ctx.set_scene(sd); ctx.build_bvh(); ctx.set_camera(cam); ctx.clear_accum(); ctx.render(4, 8, seed=1)
+    want = oracle.resolve_display(ctx.read_accum(), 4.0, 1.0, 2.2)
+    got = ctx.resolve_display(1.0, 2.2)
+    assert np.abs(got.astype(int) - want.astype(int)).max() <= 1 and (got == want).mean() > 0.999
+
+
+# ---------------------------------------------------------------- edge cases
+def test_edge_cases(ctx):
+    cam = S.Camera(width=33, height=17)
+    empty = S.SceneData()
+    ctx.set_scene(empty); ctx.build_bvh(); ctx.set_camera(cam); ctx.clear_accum(); ctx.render(2, 8, seed=1)
+    img = ctx.read_accum()
+    assert np.allclose(img, np.array(S.SKY, np.float32) * 2)            # every path misses -> sky
+    b = S.SceneBuilder("one"); b.add_sphere(1.0, b.emissive((2, 3, 4)), trans=(0, 0, 0))
+    ctx.set_scene(b.build()); ctx.build_bvh(); ctx.clear_accum(); ctx.render(1, 8, seed=1)
+    img = ctx.read_accum()
+    assert np.isfinite(img).all() and (img == np.array([2, 3, 4], np.float32)).all(-1).any()
+    ctx.clear_accum(); ctx.render(3, 0, seed=1)                          # depth 0: TraceRay returns 0
+    assert not ctx.read_accum().any() and ctx.accum_spp() == 3
+    assert len(ctx.trace_batch(np.zeros(0, util.ray_dt))) == 0
+    with pytest.raises(PrtError):
+        ctx.render(1, 99)
+
+
+def test_renderer_interface(gold):
+    """Init / SetCamera / ProgressiveRender call pattern of main.cpp:138-170, 506-532."""
+    from parallelraytracing_b200 import B200Renderer, Film
+    film = Film(64, 48); cam = S.Camera(width=64, height=48)
+    r = B200Renderer(max_depth=20)
+    r.Init(film, S.cornell(), cam); film.Clear()
+    assert r.ok
+    for _ in range(3):
+        r.ProgressiveRender()
+    assert film.Weight() == 3
+    a = film.ReadAccum()
+    r.SetCamera(cam); film.Clear()
+    assert film.Weight() == 0
+    r.SetNextSample(0)
+    for _ in range(3):
+        r.ProgressiveRender()
+    assert np.array_equal(a, film.ReadAccum())
+    assert film.UpdateDisplay().shape == (48, 64, 4)
+    r.close()

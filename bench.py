@@ -209,6 +209,9 @@ def run_ours(args):
     sd, cam, w = make_workload(args.workload)
     W, H, spp, depth = w["W"], w["H"], w["spp"], w["depth"]
     ctx = Context(local)
+    for kv in args.opt:
+        k, v = kv.split("=")
+        ctx.set_option(k, int(v))
     ctx.set_scene(sd); ctx.build_bvh(); ctx.set_camera(cam)
     build_ms = ctx.stats().build_ms
     # the accumulation buffer is a torch tensor so that NCCL can reduce it in place
@@ -333,7 +336,8 @@ def roofline_and_json(args, R):
            "dtype": "f32", "data": "synthetic",
            "config": {"workload": args.workload, "scene": sd.name, "prims": sd.n_prims, "width": W, "height": H,
                       "spp_per_step_per_gpu": spp, "depth": depth, "partition": "sample-range, NCCL sum-reduce to rank 0",
-                      "l2": "256 MiB flush between timed steps; queues (%.0f MB) also exceed L2" % (ctx.stats().paths * 0 + 8 * (1 << 20) * 112 / 1e6)},
+                      "l2": "256 MiB L2 flush between timed steps; ray queues (GBs) also exceed the 126 MB L2",
+                      "options": args.opt},
            "spp_per_s_1080p": R["world"] * spp * steps / dev_s,
            "mpaths_per_s": R["world"] * paths_step * steps / dev_s / 1e6,
            "rays_per_path": rays_step / paths_step,
@@ -352,6 +356,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--opt", action="append", default=[], help="prt_set_option key=value (e.g. fused=0, wave_paths=8388608)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

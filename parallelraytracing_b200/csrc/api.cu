@@ -94,6 +94,7 @@ void prt_destroy(prt_ctx* ctx) {
                       &c->q_o[0], &c->q_o[1], &c->q_d[0], &c->q_d[1], &c->q_b[0], &c->q_b[1], &c->hits, &c->contrib,
                       &c->qcount, &c->stats_dev};
     for (DevBuf* b : bufs) dev_free(*b);
+    for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -334,6 +335,8 @@ int prt_set_option(prt_ctx* ctx, const char* key, int64_t value) {
     if (!strcmp(key, "wave_paths")) { if (value < 0) return set_err(c, PRT_ERR_INVALID, "wave_paths < 0"); c->wave_paths_opt = value; }
     else if (!strcmp(key, "ctas_per_sm")) { if (value < 1 || value > 32) return set_err(c, PRT_ERR_INVALID, "ctas_per_sm out of range"); c->ctas_per_sm = (int)value; }
     else if (!strcmp(key, "use_graph")) c->use_graph = value ? 1 : 0;
+    else if (!strcmp(key, "fused")) c->fused = value ? 1 : 0;
+    else if (!strcmp(key, "stage_timing")) c->stage_timing = value ? 1 : 0;
     else return set_err(c, PRT_ERR_INVALID, std::string("unknown option: ") + key);
     return PRT_OK;
 }

@@ -62,6 +62,9 @@ struct Ctx {
     int ctas_per_sm = 8;
     int counters_on = 0;
     int use_graph = 1;
+    int fused = 1;                              // 1: k_primary/k_bounce, 0: raygen/extend/shade as separate stages
+    int stage_timing = 1;                       // CUDA-event pairs around the hot kernels
+    std::vector<cudaEvent_t> ev_pool;
     prt_stats stats{};
 
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;

@@ -132,6 +132,45 @@ k_extend_brute(SceneView sc, const uint32_t* __restrict__ sorted_prim, const flo
 }
 
 // ------------------------------------------------------------------ shade / scatter + compaction
+// One path segment after its closest hit is known: L = beta*Le (or beta*sky on a miss), then
+// scatter. Returns true when the path continues with (np, ndir, beta*atten).
+__device__ __forceinline__ bool shade_segment(const SceneView& sc, V3 o, V3 d, uint32_t key, int bounce, int max_depth,
+                                              float t, uint32_t code, float hu, float hv, V3& beta, V3& np, V3& ndir, V3& L) {
+    if (code == PRT_NO_HIT) {
+        L = beta * mk(sc.sky_r, sc.sky_g, sc.sky_b);                    // cpu/renderer.cpp:99
+        return false;
+    }
+    Surface s = make_surface(sc, o, d, t, code, hu, hv);
+    MatRec m;
+    if (s.mat >= 0 && s.mat < sc.n_mats) { m.a = __ldg(&sc.mats[s.mat].a); m.b = __ldg(&sc.mats[s.mat].b); }
+    else { m.a = make_float4(0, 0, 0, 0); m.b = make_float4(0, 0, 0, 0); }
+    Rng rng = rng_for_bounce(key, (uint32_t)bounce);
+    V3 atten, emit;
+    bool sc_ok = scatter(m, d, s, rng, atten, ndir, emit);
+    L = beta * emit;                                                    // L += emitted (renderer.cpp:74)
+    if (sc_ok && bounce + 1 < max_depth) { beta = beta * atten; np = s.p; return true; }
+    return false;
+}
+
+// Queue compaction: ballot/popc, ONE atomic per warp; every lane of the warp must call this.
+__device__ __forceinline__ void push_compacted(bool cont, uint32_t lane, uint32_t* __restrict__ next_count,
+                                               float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb,
+                                               V3 np, V3 ndir, V3 beta, uint32_t slot_bounce, uint32_t key) {
+    uint32_t mask = __ballot_sync(0xffffffffu, cont);
+    if (mask) {
+        int leader = __ffs(mask) - 1;
+        uint32_t b0 = 0;
+        if ((int)lane == leader) b0 = atomicAdd(next_count, (uint32_t)__popc(mask));
+        b0 = __shfl_sync(0xffffffffu, b0, leader);
+        if (cont) {
+            uint32_t j = b0 + __popc(mask & ((1u << lane) - 1u));
+            st_stream(&no[j], make_float4(np.x, np.y, np.z, __uint_as_float(slot_bounce)));
+            st_stream(&nd[j], make_float4(ndir.x, ndir.y, ndir.z, __uint_as_float(key)));
+            st_stream(&nb[j], make_float4(beta.x, beta.y, beta.z, 0.f));
+        }
+    }
+}
+
 __global__ void __launch_bounds__(WF_THREADS)
 k_shade(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ qd, const float4* __restrict__ qb,
         const float4* __restrict__ hits, float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb,
@@ -142,45 +181,95 @@ k_shade(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ 
     for (uint32_t base = blockIdx.x * WF_THREADS + (threadIdx.x & ~31u); base < count; base += stride) {
         uint32_t i = base + lane;
         bool cont = false;
-        float4 o4, d4; V3 beta, np, ndir;
+        float4 o4 = make_float4(0, 0, 0, 0), d4 = o4; V3 beta = mk(0, 0, 0), np = beta, ndir = beta;
         if (i < count) {
             o4 = ld_stream(&qo[i]); d4 = ld_stream(&qd[i]);
             float4 b4 = ld_stream(&qb[i]), h = ld_stream(&hits[i]);
             beta = xyz(b4);
-            uint32_t slot = __float_as_uint(o4.w) >> 5;
-            uint32_t code = __float_as_uint(h.y);
-            V3 L = mk(0.f, 0.f, 0.f);
-            if (code == PRT_NO_HIT) {
-                L = beta * mk(sc.sky_r, sc.sky_g, sc.sky_b);            // cpu/renderer.cpp:99
-            } else {
-                V3 o = xyz(o4), d = xyz(d4);
-                Surface s = make_surface(sc, o, d, h.x, code, h.z, h.w);
-                MatRec m;
-                if (s.mat >= 0 && s.mat < sc.n_mats) { m.a = __ldg(&sc.mats[s.mat].a); m.b = __ldg(&sc.mats[s.mat].b); }
-                else { m.a = make_float4(0, 0, 0, 0); m.b = make_float4(0, 0, 0, 0); }
-                Rng rng = rng_for_bounce(__float_as_uint(d4.w), (uint32_t)bounce);
-                V3 atten, emit;
-                bool sc_ok = scatter(m, d, s, rng, atten, ndir, emit);
-                L = beta * emit;                                          // L += emitted (renderer.cpp:74)
-                if (sc_ok && bounce + 1 < max_depth) { cont = true; beta = beta * atten; np = s.p; }
-            }
-            if (!cont) st_stream(&contrib[slot], make_float4(L.x, L.y, L.z, 0.f));
+            V3 L;
+            cont = shade_segment(sc, xyz(o4), xyz(d4), __float_as_uint(d4.w), bounce, max_depth, h.x, __float_as_uint(h.y), h.z, h.w,
+                                 beta, np, ndir, L);
+            if (!cont) st_stream(&contrib[__float_as_uint(o4.w) >> 5], make_float4(L.x, L.y, L.z, 0.f));
         }
-        // compaction: ballot/popc, one atomic per warp
-        uint32_t mask = __ballot_sync(0xffffffffu, cont);
-        if (mask) {
-            int leader = __ffs(mask) - 1;
-            uint32_t b0 = 0;
-            if ((int)lane == leader) b0 = atomicAdd(&qcount[bounce + 1], (uint32_t)__popc(mask));
-            b0 = __shfl_sync(0xffffffffu, b0, leader);
-            if (cont) {
-                uint32_t j = b0 + __popc(mask & ((1u << lane) - 1u));
-                st_stream(&no[j], make_float4(np.x, np.y, np.z, __uint_as_float(__float_as_uint(o4.w) + 1u)));
-                st_stream(&nd[j], make_float4(ndir.x, ndir.y, ndir.z, d4.w));
-                st_stream(&nb[j], make_float4(beta.x, beta.y, beta.z, 0.f));
-            }
+        push_compacted(cont, lane, &qcount[bounce + 1], no, nd, nb, np, ndir, beta, __float_as_uint(o4.w) + 1u, __float_as_uint(d4.w));
+    }
+}
+
+// ------------------------------------------------------------------ fused stages
+// The same pipeline with the stage boundaries that only cost HBM traffic removed:
+//   k_primary = raygen + extend + shade of bounce 0 (camera rays never touch memory),
+//   k_bounce  = extend + shade of bounce b >= 1 (no hit queue); both compact into the next queue.
+// Results are bit-identical to the staged kernels (same device functions, same order).
+template <bool COUNT>
+__global__ void __launch_bounds__(WF_THREADS)
+k_primary(SceneView sc, CamView cam, int pix0, int npix, int n_paths, uint32_t sample0, uint32_t seed_lo, uint32_t seed_hi,
+          float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb, float4* __restrict__ contrib,
+          uint32_t* __restrict__ qcount, int max_depth, unsigned long long* __restrict__ stats) {
+    __shared__ int sstack[STACK_SMEM * WF_THREADS];
+    const uint32_t count = (uint32_t)n_paths;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t stride = gridDim.x * WF_THREADS;
+    uint32_t nn = 0, npr = 0;
+    for (uint32_t base = blockIdx.x * WF_THREADS + (threadIdx.x & ~31u); base < count; base += stride) {
+        uint32_t i = base + lane;
+        bool cont = false;
+        V3 beta = mk(1.f, 1.f, 1.f), np = mk(0, 0, 0), ndir = np;
+        uint32_t key = 0;
+        if (i < count) {
+            int s_local = (int)i / npix;
+            int pixel = pix0 + ((int)i - s_local * npix);
+            int y = pixel / cam.W, x = pixel - y * cam.W;
+            V3 d = camera_dir(cam, (float)x + 0.5f, (float)y + 0.5f);
+            key = path_key(seed_lo, seed_hi, (uint32_t)pixel, sample0 + (uint32_t)s_local);
+            Best b = traverse<COUNT>(sc, cam.pos, d, sstack + threadIdx.x, nn, npr);
+            V3 L;
+            cont = shade_segment(sc, cam.pos, d, key, 0, max_depth, b.t, b.code, b.u, b.v, beta, np, ndir, L);
+            if (!cont) st_stream(&contrib[i], make_float4(L.x, L.y, L.z, 0.f));
+        }
+        push_compacted(cont, lane, &qcount[1], no, nd, nb, np, ndir, beta, (i << 5) + 1u, key);
+    }
+    if (COUNT) {
+        for (int o = 16; o > 0; o >>= 1) { nn += __shfl_xor_sync(0xffffffffu, nn, o); npr += __shfl_xor_sync(0xffffffffu, npr, o); }
+        if (lane == 0 && (nn | npr)) {
+            atomicAdd(&stats[PRT_MAX_DEPTH + 0], (unsigned long long)nn);
+            atomicAdd(&stats[PRT_MAX_DEPTH + 1], (unsigned long long)npr);
         }
     }
+    if (blockIdx.x == 0 && threadIdx.x == 0) { atomicAdd(&stats[0], (unsigned long long)count); qcount[0] = count; }
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(WF_THREADS)
+k_bounce(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ qd, const float4* __restrict__ qb,
+         float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb, float4* __restrict__ contrib,
+         uint32_t* __restrict__ qcount, int bounce, int max_depth, unsigned long long* __restrict__ stats) {
+    __shared__ int sstack[STACK_SMEM * WF_THREADS];
+    const uint32_t count = qcount[bounce];
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t stride = gridDim.x * WF_THREADS;
+    uint32_t nn = 0, npr = 0;
+    for (uint32_t base = blockIdx.x * WF_THREADS + (threadIdx.x & ~31u); base < count; base += stride) {
+        uint32_t i = base + lane;
+        bool cont = false;
+        float4 o4 = make_float4(0, 0, 0, 0), d4 = o4; V3 beta = mk(0, 0, 0), np = beta, ndir = beta;
+        if (i < count) {
+            o4 = ld_stream(&qo[i]); d4 = ld_stream(&qd[i]);
+            beta = xyz(ld_stream(&qb[i]));
+            Best b = traverse<COUNT>(sc, xyz(o4), xyz(d4), sstack + threadIdx.x, nn, npr);
+            V3 L;
+            cont = shade_segment(sc, xyz(o4), xyz(d4), __float_as_uint(d4.w), bounce, max_depth, b.t, b.code, b.u, b.v, beta, np, ndir, L);
+            if (!cont) st_stream(&contrib[__float_as_uint(o4.w) >> 5], make_float4(L.x, L.y, L.z, 0.f));
+        }
+        push_compacted(cont, lane, &qcount[bounce + 1], no, nd, nb, np, ndir, beta, __float_as_uint(o4.w) + 1u, __float_as_uint(d4.w));
+    }
+    if (COUNT) {
+        for (int o = 16; o > 0; o >>= 1) { nn += __shfl_xor_sync(0xffffffffu, nn, o); npr += __shfl_xor_sync(0xffffffffu, npr, o); }
+        if (lane == 0 && (nn | npr)) {
+            atomicAdd(&stats[PRT_MAX_DEPTH + 0], (unsigned long long)nn);
+            atomicAdd(&stats[PRT_MAX_DEPTH + 1], (unsigned long long)npr);
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&stats[bounce], (unsigned long long)count);
 }
 
 // ------------------------------------------------------------------ resolve (accumulate)
@@ -300,7 +389,7 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
     const int W = c->cam.width, H = c->cam.height;
     const int64_t P = (int64_t)W * H;
     cudaStream_t st = c->stream;
-    int64_t cap = c->wave_paths_opt > 0 ? c->wave_paths_opt : (int64_t)8 << 20;
+    int64_t cap = c->wave_paths_opt > 0 ? c->wave_paths_opt : (int64_t)32 << 20;
     cap = std::min<int64_t>(cap, (int64_t)1 << 26);                  // slot must fit 27 bits
     // wave = pixel range [p0, p0+npix) x S samples
     int64_t npix_wave = std::min<int64_t>(P, cap);
@@ -315,9 +404,16 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
     unsigned long long* dstats = (unsigned long long*)c->stats_dev.p;
     const int grid_p = c->num_sms * c->ctas_per_sm;
     const uint32_t seed_lo = (uint32_t)seed, seed_hi = (uint32_t)(seed >> 32);
+    const bool fused = c->fused != 0, timing = c->stage_timing != 0;
 
-    std::vector<cudaEvent_t> evs;
-    auto new_event = [&]() { cudaEvent_t e; cudaEventCreate(&e); evs.push_back(e); return e; };
+    // per-stage device timing: pooled events, one pair per kernel of the two hot stages
+    size_t ev_used = 0;
+    std::vector<std::pair<size_t, int>> spans;                       // (first event index, stage)
+    auto stamp = [&]() -> size_t {
+        if (ev_used == c->ev_pool.size()) { cudaEvent_t e; cudaEventCreate(&e); c->ev_pool.push_back(e); }
+        cudaEventRecord(c->ev_pool[ev_used], st);
+        return ev_used++;
+    };
 
     PRT_CUDA(c, cudaMemsetAsync(dstats, 0, (PRT_MAX_DEPTH + 4) * 8, st));
     PRT_CUDA(c, cudaEventRecord(c->ev0, st));
@@ -330,32 +426,51 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
             const int n_paths = npix * S;
             paths += (uint64_t)n_paths;
             PRT_CUDA(c, cudaMemsetAsync(qcount, 0, (PRT_MAX_DEPTH + 2) * 4, st));
-            k_raygen<<<(n_paths + WF_THREADS - 1) / WF_THREADS, WF_THREADS, 0, st>>>(
-                cam, (int)p0, npix, n_paths, (uint32_t)(sample_begin + s0), seed_lo, seed_hi,
-                (float4*)c->q_o[0].p, (float4*)c->q_d[0].p, (float4*)c->q_b[0].p, qcount);
-            ++launches;
-            int cur = 0;
             const int grid = (int)std::min<int64_t>(grid_p, (n_paths + WF_THREADS - 1) / WF_THREADS);
-            for (int b = 0; b < max_depth; ++b) {
-                cudaEvent_t e0 = new_event(), e1 = new_event(), e2 = new_event();
-                cudaEventRecord(e0, st);
+            float4 *qo[2] = {(float4*)c->q_o[0].p, (float4*)c->q_o[1].p}, *qd[2] = {(float4*)c->q_d[0].p, (float4*)c->q_d[1].p},
+                   *qb[2] = {(float4*)c->q_b[0].p, (float4*)c->q_b[1].p};
+            float4 *hits = (float4*)c->hits.p, *contrib = (float4*)c->contrib.p;
+            int cur = 0;
+            if (fused) {
+                if (timing) spans.push_back({stamp(), 0});
                 if (c->counters_on)
-                    k_extend<true><<<grid, WF_THREADS, 0, st>>>(sc, (const float4*)c->q_o[cur].p, (const float4*)c->q_d[cur].p,
-                                                                (float4*)c->hits.p, qcount, b, dstats);
+                    k_primary<true><<<grid, WF_THREADS, 0, st>>>(sc, cam, (int)p0, npix, n_paths, (uint32_t)(sample_begin + s0), seed_lo,
+                                                                 seed_hi, qo[1], qd[1], qb[1], contrib, qcount, max_depth, dstats);
                 else
-                    k_extend<false><<<grid, WF_THREADS, 0, st>>>(sc, (const float4*)c->q_o[cur].p, (const float4*)c->q_d[cur].p,
-                                                                 (float4*)c->hits.p, qcount, b, dstats);
-                cudaEventRecord(e1, st);
-                k_shade<<<grid, WF_THREADS, 0, st>>>(sc, (const float4*)c->q_o[cur].p, (const float4*)c->q_d[cur].p,
-                                                     (const float4*)c->q_b[cur].p, (const float4*)c->hits.p,
-                                                     (float4*)c->q_o[cur ^ 1].p, (float4*)c->q_d[cur ^ 1].p,
-                                                     (float4*)c->q_b[cur ^ 1].p, (float4*)c->contrib.p, qcount, b, max_depth);
-                cudaEventRecord(e2, st);
-                launches += 2;
-                cur ^= 1;
+                    k_primary<false><<<grid, WF_THREADS, 0, st>>>(sc, cam, (int)p0, npix, n_paths, (uint32_t)(sample_begin + s0), seed_lo,
+                                                                  seed_hi, qo[1], qd[1], qb[1], contrib, qcount, max_depth, dstats);
+                if (timing) stamp();
+                ++launches;
+                cur = 1;
+                for (int b = 1; b < max_depth; ++b) {
+                    if (timing) spans.push_back({stamp(), 0});
+                    if (c->counters_on)
+                        k_bounce<true><<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], qb[cur], qo[cur ^ 1], qd[cur ^ 1], qb[cur ^ 1],
+                                                                    contrib, qcount, b, max_depth, dstats);
+                    else
+                        k_bounce<false><<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], qb[cur], qo[cur ^ 1], qd[cur ^ 1], qb[cur ^ 1],
+                                                                     contrib, qcount, b, max_depth, dstats);
+                    if (timing) stamp();
+                    ++launches;
+                    cur ^= 1;
+                }
+            } else {
+                k_raygen<<<(n_paths + WF_THREADS - 1) / WF_THREADS, WF_THREADS, 0, st>>>(
+                    cam, (int)p0, npix, n_paths, (uint32_t)(sample_begin + s0), seed_lo, seed_hi, qo[0], qd[0], qb[0], qcount);
+                ++launches;
+                for (int b = 0; b < max_depth; ++b) {
+                    if (timing) spans.push_back({stamp(), 0});
+                    if (c->counters_on) k_extend<true><<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], hits, qcount, b, dstats);
+                    else k_extend<false><<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], hits, qcount, b, dstats);
+                    if (timing) spans.push_back({stamp(), 1});
+                    k_shade<<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], qb[cur], hits, qo[cur ^ 1], qd[cur ^ 1], qb[cur ^ 1],
+                                                         contrib, qcount, b, max_depth);
+                    if (timing) stamp();
+                    launches += 2;
+                    cur ^= 1;
+                }
             }
-            k_resolve<<<(npix + WF_THREADS - 1) / WF_THREADS, WF_THREADS, 0, st>>>(
-                (const float4*)c->contrib.p, (int)p0, npix, S, c->accum);
+            k_resolve<<<(npix + WF_THREADS - 1) / WF_THREADS, WF_THREADS, 0, st>>>(contrib, (int)p0, npix, S, c->accum);
             ++launches;
         }
     }
@@ -373,15 +488,13 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
     s.paths = paths;
     s.kernel_launches = launches;
     cudaEventElapsedTime(&s.render_ms, c->ev0, c->ev1);
-    float ext = 0.f, shd = 0.f;
-    for (size_t k = 0; k + 2 < evs.size(); k += 3) {
-        float a = 0.f, b2 = 0.f;
-        cudaEventElapsedTime(&a, evs[k], evs[k + 1]);
-        cudaEventElapsedTime(&b2, evs[k + 1], evs[k + 2]);
-        ext += a; shd += b2;
+    float ms[2] = {0.f, 0.f};
+    for (auto& sp : spans) {
+        float a = 0.f;
+        cudaEventElapsedTime(&a, c->ev_pool[sp.first], c->ev_pool[sp.first + 1]);
+        ms[sp.second] += a;
     }
-    for (cudaEvent_t e : evs) cudaEventDestroy(e);
-    s.extend_ms = ext; s.shade_ms = shd;
+    s.extend_ms = ms[0]; s.shade_ms = ms[1];
     s.n_prims = c->n_prims; s.n_nodes = c->n_prims > 1 ? c->n_prims - 1 : 0;
     return PRT_OK;
 }

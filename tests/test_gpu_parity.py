@@ -99,7 +99,7 @@ def test_closest_hit_bit_exact_vs_oracle(ctx, oracle, gold, name):
     assert np.array_equal(got, want), "full hit records (t, barycentrics, position, normal, face, material)"
     assert np.array_equal(np.argsort(got["t"], kind="stable"), np.argsort(want["t"], kind="stable")), "t-ordering"
     assert (st.nodes_visited, st.prims_tested) == (int(cnt[0]), int(cnt[1])), "traversal counters reproduce on the CPU"
-    assert (got["prim_id"] >= 0).mean() > 0.05
+    assert (got["prim_id"] >= 0).mean() > 0.01
 
 
 @pytest.mark.parametrize("name", ["cornell", "random_balls_large", "soup20k"])
@@ -171,6 +171,21 @@ def test_sample_ranges_compose(ctx, gold):
     ctx.clear_accum(); ctx.render(6, 8, seed=3); c = ctx.read_accum()
     ctx.set_option("wave_paths", 0)
     assert np.array_equal(a, c)
+
+
+def test_staged_pipeline_equals_fused(ctx, gold):
+    """fused=0 runs raygen / extend / shade as separate kernels with a hit queue; fused=1 (default)
+    removes the stage boundaries. Same device functions, same order: identical bits and ray counts."""
+    for name in ("closed_cornell", "dragon3"):
+        sd = SCENES[name](gold); cam = S.Camera(width=96, height=64)
+        ctx.set_scene(sd); ctx.build_bvh(); ctx.set_camera(cam)
+        out = []
+        for fused in (1, 0):
+            ctx.set_option("fused", fused)
+            ctx.clear_accum(); ctx.render(3, 8, seed=11)
+            out.append((ctx.read_accum(), ctx.stats().rays_total, list(ctx.stats().rays_per_bounce)))
+        ctx.set_option("fused", 1)
+        assert np.array_equal(out[0][0], out[1][0]) and out[0][1:] == out[1][1:]
 
 
 def test_display_resolve_exact(ctx, oracle):

@@ -40,6 +40,19 @@ PRT_DEV V3 cross(V3 a, V3 b) {
 PRT_DEV V3 normalize(V3 v) { float s = 1.0f / sqrtf(dot(v, v)); return v * s; }
 PRT_DEV V3 xyz(float4 f) { return mk(f.x, f.y, f.z); }
 
+// ------------------------------------------------------------------ exact division by a launch constant
+// floor(n / d) for n < 2^31 as one 32x32->64 multiply and a shift (Granlund & Montgomery 1994,
+// m = ceil(2^(31+L) / d), L = ceil(log2 d)); replaces the ~25-instruction integer division.
+struct FastDiv { uint32_t mul, shift, d; };
+static inline FastDiv make_fastdiv(uint32_t d) {
+    FastDiv f; f.d = d;
+    uint32_t L = 0; while ((1ull << L) < d) ++L;
+    f.shift = 31u + L;
+    f.mul = (uint32_t)(((1ull << f.shift) + d - 1) / d);
+    return f;
+}
+PRT_DEV uint32_t fdiv(uint32_t n, const FastDiv& f) { return (uint32_t)(((unsigned long long)n * f.mul) >> f.shift); }
+
 // ------------------------------------------------------------------ RNG
 // Counter-free PCG-RXS-M-XS-32 stream per (path, bounce). Random() mirrors the host
 // branch of the reference: std::rand() / (RAND_MAX + 1.0f) with a 31-bit rand()
@@ -353,7 +366,7 @@ PRT_DEV bool scatter(const MatRec& m, V3 d, const Surface& s, Rng& rng, V3& atte
 }
 
 // Camera::GetCameraRay (camera.h:104-132)
-struct CamView { V3 pos, front, right, up; float tan_half, aspect, w, h; int W, H; };
+struct CamView { V3 pos, front, right, up; float tan_half, aspect, w, h; int W, H; FastDiv divW; };
 PRT_DEV V3 camera_dir(const CamView& c, float px, float py) {
     float ndc_x = (px / c.w) * 2.0f - 1.0f;
     float ndc_y = 1.0f - (py / c.h) * 2.0f;

@@ -29,14 +29,14 @@ __device__ __forceinline__ void st_stream(float4* p, float4 v) { __stcs(p, v); }
 
 // ------------------------------------------------------------------ raygen
 __global__ void __launch_bounds__(WF_THREADS)
-k_raygen(CamView cam, int pix0, int npix, int n_paths, uint32_t sample0, uint32_t seed_lo, uint32_t seed_hi,
+k_raygen(CamView cam, int pix0, int npix, FastDiv div_npix, int n_paths, uint32_t sample0, uint32_t seed_lo, uint32_t seed_hi,
          float4* __restrict__ qo, float4* __restrict__ qd, float4* __restrict__ qb, uint32_t* __restrict__ qcount) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i == 0) qcount[0] = (uint32_t)n_paths;
     if (i >= n_paths) return;
-    int s_local = i / npix;
+    int s_local = (int)fdiv((uint32_t)i, div_npix);
     int pixel = pix0 + (i - s_local * npix);
-    int y = pixel / cam.W, x = pixel - y * cam.W;
+    int y = (int)fdiv((uint32_t)pixel, cam.divW), x = pixel - y * cam.W;
     V3 d = camera_dir(cam, (float)x + 0.5f, (float)y + 0.5f);     // pixel centre, cpu/renderer.cpp:45
     uint32_t key = path_key(seed_lo, seed_hi, (uint32_t)pixel, sample0 + (uint32_t)s_local);
     st_stream(&qo[i], make_float4(cam.pos.x, cam.pos.y, cam.pos.z, __uint_as_float((uint32_t)i << 5)));
@@ -53,8 +53,10 @@ __device__ __forceinline__ Best traverse(const SceneView& sc, V3 o, V3 d, int* _
     Best best; best_init(best);
     if (sc.n_prims == 0) return best;
     RayBox rb = make_raybox(o, d);
-    RayShear rs = make_shear(d);
-    V3 dn = normalize(d);
+    RayShear rs; V3 dn = d;
+    if (sc.n_tris > 0) rs = make_shear(d);            // per-ray triangle-test constants: only if there are triangles
+    else { rs.kx = 0; rs.ky = 1; rs.kz = 2; rs.sx = rs.sy = rs.sz = 0.f; }
+    if (sc.n_spheres > 0) dn = normalize(d);          // Circle's local direction (primitive.cpp:30): only if there are spheres
     int lstack[STACK_LOCAL];
     int sp = 0;
     int cur = sc.root_code;
@@ -202,7 +204,7 @@ k_shade(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ 
 // Results are bit-identical to the staged kernels (same device functions, same order).
 template <bool COUNT>
 __global__ void __launch_bounds__(WF_THREADS)
-k_primary(SceneView sc, CamView cam, int pix0, int npix, int n_paths, uint32_t sample0, uint32_t seed_lo, uint32_t seed_hi,
+k_primary(SceneView sc, CamView cam, int pix0, int npix, FastDiv div_npix, int n_paths, uint32_t sample0, uint32_t seed_lo, uint32_t seed_hi,
           float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb, float4* __restrict__ contrib,
           uint32_t* __restrict__ qcount, int max_depth, unsigned long long* __restrict__ stats) {
     __shared__ int sstack[STACK_SMEM * WF_THREADS];
@@ -216,9 +218,9 @@ k_primary(SceneView sc, CamView cam, int pix0, int npix, int n_paths, uint32_t s
         V3 beta = mk(1.f, 1.f, 1.f), np = mk(0, 0, 0), ndir = np;
         uint32_t key = 0;
         if (i < count) {
-            int s_local = (int)i / npix;
+            int s_local = (int)fdiv(i, div_npix);
             int pixel = pix0 + ((int)i - s_local * npix);
-            int y = pixel / cam.W, x = pixel - y * cam.W;
+            int y = (int)fdiv((uint32_t)pixel, cam.divW), x = pixel - y * cam.W;
             V3 d = camera_dir(cam, (float)x + 0.5f, (float)y + 0.5f);
             key = path_key(seed_lo, seed_hi, (uint32_t)pixel, sample0 + (uint32_t)s_local);
             Best b = traverse<COUNT>(sc, cam.pos, d, sstack + threadIdx.x, nn, npr);
@@ -370,6 +372,7 @@ static CamView cam_view(const prt_camera& k) {
     v.w = (float)k.width; v.h = (float)k.height;
     v.aspect = v.w / v.h;                                 // m_Width / m_Height, camera.h:112
     v.W = k.width; v.H = k.height;
+    v.divW = make_fastdiv((uint32_t)k.width);
     return v;
 }
 
@@ -424,6 +427,7 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
         for (int64_t p0 = 0; p0 < P; p0 += npix_wave) {
             const int npix = (int)std::min<int64_t>(npix_wave, P - p0);
             const int n_paths = npix * S;
+            const FastDiv div_npix = make_fastdiv((uint32_t)npix);
             paths += (uint64_t)n_paths;
             PRT_CUDA(c, cudaMemsetAsync(qcount, 0, (PRT_MAX_DEPTH + 2) * 4, st));
             const int grid = (int)std::min<int64_t>(grid_p, (n_paths + WF_THREADS - 1) / WF_THREADS);
@@ -434,10 +438,10 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
             if (fused) {
                 if (timing) spans.push_back({stamp(), 0});
                 if (c->counters_on)
-                    k_primary<true><<<grid, WF_THREADS, 0, st>>>(sc, cam, (int)p0, npix, n_paths, (uint32_t)(sample_begin + s0), seed_lo,
+                    k_primary<true><<<grid, WF_THREADS, 0, st>>>(sc, cam, (int)p0, npix, div_npix, n_paths, (uint32_t)(sample_begin + s0), seed_lo,
                                                                  seed_hi, qo[1], qd[1], qb[1], contrib, qcount, max_depth, dstats);
                 else
-                    k_primary<false><<<grid, WF_THREADS, 0, st>>>(sc, cam, (int)p0, npix, n_paths, (uint32_t)(sample_begin + s0), seed_lo,
+                    k_primary<false><<<grid, WF_THREADS, 0, st>>>(sc, cam, (int)p0, npix, div_npix, n_paths, (uint32_t)(sample_begin + s0), seed_lo,
                                                                   seed_hi, qo[1], qd[1], qb[1], contrib, qcount, max_depth, dstats);
                 if (timing) stamp();
                 ++launches;
@@ -456,7 +460,7 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
                 }
             } else {
                 k_raygen<<<(n_paths + WF_THREADS - 1) / WF_THREADS, WF_THREADS, 0, st>>>(
-                    cam, (int)p0, npix, n_paths, (uint32_t)(sample_begin + s0), seed_lo, seed_hi, qo[0], qd[0], qb[0], qcount);
+                    cam, (int)p0, npix, div_npix, n_paths, (uint32_t)(sample_begin + s0), seed_lo, seed_hi, qo[0], qd[0], qb[0], qcount);
                 ++launches;
                 for (int b = 0; b < max_depth; ++b) {
                     if (timing) spans.push_back({stamp(), 0});

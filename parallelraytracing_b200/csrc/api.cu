@@ -335,7 +335,10 @@ int prt_set_option(prt_ctx* ctx, const char* key, int64_t value) {
     if (!strcmp(key, "wave_paths")) { if (value < 0) return set_err(c, PRT_ERR_INVALID, "wave_paths < 0"); c->wave_paths_opt = value; }
     else if (!strcmp(key, "ctas_per_sm")) { if (value < 1 || value > 32) return set_err(c, PRT_ERR_INVALID, "ctas_per_sm out of range"); c->ctas_per_sm = (int)value; }
     else if (!strcmp(key, "use_graph")) c->use_graph = value ? 1 : 0;
-    else if (!strcmp(key, "fused")) c->fused = value ? 1 : 0;
+    else if (!strcmp(key, "fused")) c->fused = value < 0 ? -1 : (value ? 1 : 0);
+    else if (!strcmp(key, "fused_max_prims")) c->fused_max_prims = (int)value;
+    else if (!strcmp(key, "persistent")) c->persistent = value ? 1 : 0;
+    else if (!strcmp(key, "pt_refill")) { if (value < 0 || value > 32) return set_err(c, PRT_ERR_INVALID, "pt_refill out of range"); c->pt_refill = (int)value; }
     else if (!strcmp(key, "stage_timing")) c->stage_timing = value ? 1 : 0;
     else return set_err(c, PRT_ERR_INVALID, std::string("unknown option: ") + key);
     return PRT_OK;

@@ -110,6 +110,104 @@ k_extend(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&stats[bounce], (unsigned long long)count);
 }
 
+// Persistent-thread extend with per-lane dynamic ray fetch (Aila & Laine 2009, "persistent while-while"):
+// the grid is sized to what is resident on the SMs; every LANE is a worker that pulls its next ray from
+// the queue through a warp-aggregated atomic as soon as its current ray is finished, so a warp never
+// idles behind its longest ray (ncu on 1M-10M triangle scenes: 6/32 active lanes without this).
+// Inner structure: all lanes first walk internal nodes (postponed leaf), then test the pending leaf;
+// when fewer than `refill` lanes are still traversing, the warp returns to the fetch point.
+// Order-independent result: (t, prim_id) tie rule makes the closest hit unique, so records are
+// bit-identical to k_extend / the CPU oracle; node and leaf counters are identical too.
+#define PRT_DONE ((int)0x80000000)
+template <bool COUNT>
+__global__ void __launch_bounds__(WF_THREADS)
+k_extend_pt(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ qd, float4* __restrict__ hits,
+            const uint32_t* __restrict__ qcount, uint32_t* __restrict__ work, int bounce, int refill,
+            unsigned long long* __restrict__ stats) {
+    __shared__ int sstack[STACK_SMEM * WF_THREADS];
+    const uint32_t count = qcount[bounce];
+    const uint32_t lane = threadIdx.x & 31u;
+    int* __restrict__ st = sstack + threadIdx.x;
+    int lstack[STACK_LOCAL];
+    uint32_t nn = 0, np = 0;
+    bool have = false, exhausted = (sc.n_prims == 0);
+    uint32_t idx = 0; V3 o = mk(0, 0, 0), d = o, dn = o; RayBox rb; RayShear rs; Best best; int cur = PRT_DONE, sp = 0;
+    rb.o = o; rb.inv = o; rs.kx = 0; rs.ky = 1; rs.kz = 2; rs.sx = rs.sy = rs.sz = 0.f; best_init(best);
+    if (sc.n_prims == 0) {          // nothing to hit: every ray is a miss
+        for (uint32_t i = blockIdx.x * WF_THREADS + threadIdx.x; i < count; i += gridDim.x * WF_THREADS)
+            st_stream(&hits[i], make_float4(best.t, __uint_as_float(best.code), 0.f, 0.f));
+    }
+    while (!exhausted || __any_sync(0xffffffffu, have)) {
+        // ---- fetch: idle lanes take the next rays of the queue (one atomic per warp)
+        uint32_t idle = __ballot_sync(0xffffffffu, !have);
+        if (idle && !exhausted) {
+            int leader = __ffs(idle) - 1;
+            uint32_t base = 0;
+            if ((int)lane == leader) base = atomicAdd(work, (uint32_t)__popc(idle));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (!have) {
+                idx = base + __popc(idle & ((1u << lane) - 1u));
+                if (idx < count) {
+                    float4 o4 = ld_stream(&qo[idx]), d4 = ld_stream(&qd[idx]);
+                    o = xyz(o4); d = xyz(d4);
+                    rb = make_raybox(o, d);
+                    if (sc.n_tris > 0) rs = make_shear(d);
+                    dn = sc.n_spheres > 0 ? normalize(d) : d;
+                    best_init(best);
+                    cur = sc.root_code; sp = 0; have = true;
+                }
+            }
+            exhausted = base + (uint32_t)__popc(idle) >= count;
+        }
+        // ---- traverse
+        if (have) {
+            const int thresh = exhausted ? 0 : refill;
+            for (;;) {
+                while (cur >= 0) {                                     // internal nodes
+                    const BvhNode* nd = sc.nodes + cur;
+                    float4 lmin = ldg4(&nd->lmin), lmax = ldg4(&nd->lmax), rmin = ldg4(&nd->rmin), rmax = ldg4(&nd->rmax);
+                    if (COUNT) ++nn;
+                    float tl = isect_box(rb, lmin, lmax, best.t);
+                    float tr = isect_box(rb, rmin, rmax, best.t);
+                    int cl = __float_as_int(lmin.w), cr = __float_as_int(lmax.w);
+                    // branch-free child selection: near child next, far child (if any) to the stack
+                    const bool hl = tl >= 0.0f, hr = tr >= 0.0f;
+                    const bool right_first = hr && (!hl || tr < tl);
+                    const int nearc = right_first ? cr : cl, farc = right_first ? cl : cr;
+                    if (hl && hr) {
+                        if (sp < STACK_SMEM) st[sp * WF_THREADS] = farc; else lstack[sp - STACK_SMEM] = farc;
+                        ++sp;
+                    }
+                    if (hl || hr) cur = nearc;
+                    else if (sp == 0) cur = PRT_DONE;
+                    else { --sp; cur = sp < STACK_SMEM ? st[sp * WF_THREADS] : lstack[sp - STACK_SMEM]; }
+                    if (__popc(__activemask()) < thresh) break;        // lanes drained away (finished or at a leaf)
+                }
+                if (cur < 0 && cur != PRT_DONE) {                      // postponed leaf
+                    if (COUNT) ++np;
+                    test_leaf(sc, (uint32_t)~cur, o, d, dn, rs, best);
+                    if (sp == 0) cur = PRT_DONE;
+                    else { --sp; cur = sp < STACK_SMEM ? st[sp * WF_THREADS] : lstack[sp - STACK_SMEM]; }
+                }
+                if (cur == PRT_DONE) break;
+                if (__popc(__activemask()) < thresh) break;            // too few lanes left: go refill
+            }
+            if (cur == PRT_DONE) {
+                st_stream(&hits[idx], make_float4(best.t, __uint_as_float(best.code), best.u, best.v));
+                have = false;
+            }
+        }
+    }
+    if (COUNT) {
+        for (int k = 16; k > 0; k >>= 1) { nn += __shfl_xor_sync(0xffffffffu, nn, k); np += __shfl_xor_sync(0xffffffffu, np, k); }
+        if (lane == 0 && (nn | np)) {
+            atomicAdd(&stats[PRT_MAX_DEPTH + 0], (unsigned long long)nn);
+            atomicAdd(&stats[PRT_MAX_DEPTH + 1], (unsigned long long)np);
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&stats[bounce], (unsigned long long)count);
+}
+
 // Brute force over every primitive = the reference's own algorithm (primitive.cpp:21-59);
 // used for parity (`prt_trace_batch(use_bvh=0)`), never on the render path.
 __global__ void __launch_bounds__(WF_THREADS)
@@ -383,7 +481,7 @@ static int ensure_wave_buffers(Ctx* c, int64_t paths) {
         if ((rc = dev_reserve(c, c->q_o[k], b16)) || (rc = dev_reserve(c, c->q_d[k], b16)) ||
             (rc = dev_reserve(c, c->q_b[k], b16))) return rc;
     if ((rc = dev_reserve(c, c->hits, b16)) || (rc = dev_reserve(c, c->contrib, b16))) return rc;
-    if ((rc = dev_reserve(c, c->qcount, (PRT_MAX_DEPTH + 2) * 4))) return rc;
+    if ((rc = dev_reserve(c, c->qcount, 2 * (PRT_MAX_DEPTH + 2) * 4))) return rc;   // queue lengths + per-launch work counters
     if ((rc = dev_reserve(c, c->stats_dev, (PRT_MAX_DEPTH + 4) * 8))) return rc;
     return PRT_OK;
 }
@@ -407,7 +505,15 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
     unsigned long long* dstats = (unsigned long long*)c->stats_dev.p;
     const int grid_p = c->num_sms * c->ctas_per_sm;
     const uint32_t seed_lo = (uint32_t)seed, seed_hi = (uint32_t)(seed >> 32);
-    const bool fused = c->fused != 0, timing = c->stage_timing != 0;
+    const bool fused = c->fused < 0 ? (c->n_prims <= c->fused_max_prims) : (c->fused != 0);
+    const bool timing = c->stage_timing != 0;
+    int grid_pt = grid_p;
+    {   // persistent extend: exactly the CTAs that are resident at once
+        int per_sm = 0;
+        cudaError_t e = c->counters_on ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_extend_pt<true>, WF_THREADS, 0)
+                                       : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_extend_pt<false>, WF_THREADS, 0);
+        if (e == cudaSuccess && per_sm > 0) grid_pt = c->num_sms * per_sm;
+    }
 
     // per-stage device timing: pooled events, one pair per kernel of the two hot stages
     size_t ev_used = 0;
@@ -429,7 +535,7 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
             const int n_paths = npix * S;
             const FastDiv div_npix = make_fastdiv((uint32_t)npix);
             paths += (uint64_t)n_paths;
-            PRT_CUDA(c, cudaMemsetAsync(qcount, 0, (PRT_MAX_DEPTH + 2) * 4, st));
+            PRT_CUDA(c, cudaMemsetAsync(qcount, 0, 2 * (PRT_MAX_DEPTH + 2) * 4, st));
             const int grid = (int)std::min<int64_t>(grid_p, (n_paths + WF_THREADS - 1) / WF_THREADS);
             float4 *qo[2] = {(float4*)c->q_o[0].p, (float4*)c->q_o[1].p}, *qd[2] = {(float4*)c->q_d[0].p, (float4*)c->q_d[1].p},
                    *qb[2] = {(float4*)c->q_b[0].p, (float4*)c->q_b[1].p};
@@ -464,7 +570,11 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
                 ++launches;
                 for (int b = 0; b < max_depth; ++b) {
                     if (timing) spans.push_back({stamp(), 0});
-                    if (c->counters_on) k_extend<true><<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], hits, qcount, b, dstats);
+                    if (c->persistent) {
+                        uint32_t* work = qcount + (PRT_MAX_DEPTH + 2) + b;
+                        if (c->counters_on) k_extend_pt<true><<<grid_pt, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], hits, qcount, work, b, c->pt_refill, dstats);
+                        else k_extend_pt<false><<<grid_pt, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], hits, qcount, work, b, c->pt_refill, dstats);
+                    } else if (c->counters_on) k_extend<true><<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], hits, qcount, b, dstats);
                     else k_extend<false><<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], hits, qcount, b, dstats);
                     if (timing) spans.push_back({stamp(), 1});
                     k_shade<<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], qb[cur], hits, qo[cur ^ 1], qd[cur ^ 1], qb[cur ^ 1],
@@ -517,10 +627,20 @@ int wavefront_trace_batch(Ctx* c, const prt_ray* rays, int n, prt_hit* out, int 
     unsigned long long* dstats = (unsigned long long*)c->stats_dev.p;
     cudaMemcpyAsync(d_rays.p, rays, (size_t)n * sizeof(prt_ray), cudaMemcpyHostToDevice, st);
     cudaMemsetAsync(dstats, 0, (PRT_MAX_DEPTH + 4) * 8, st);
+    cudaMemsetAsync(qcount, 0, 2 * (PRT_MAX_DEPTH + 2) * 4, st);
     const int G = (n + WF_THREADS - 1) / WF_THREADS;
     k_load_rays<<<G, WF_THREADS, 0, st>>>((const prt_ray*)d_rays.p, n, (float4*)c->q_o[0].p, (float4*)c->q_d[0].p, qcount);
     const int grid = std::min(G, c->num_sms * c->ctas_per_sm);
-    if (use_bvh) {
+    if (use_bvh && c->persistent) {
+        uint32_t* work = qcount + (PRT_MAX_DEPTH + 2);
+        int per_sm = 4;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_extend_pt<false>, WF_THREADS, 0);
+        const int gpt = std::max(1, c->num_sms * std::max(1, per_sm));
+        if (c->counters_on)
+            k_extend_pt<true><<<gpt, WF_THREADS, 0, st>>>(sc, (const float4*)c->q_o[0].p, (const float4*)c->q_d[0].p, (float4*)c->hits.p, qcount, work, 0, c->pt_refill, dstats);
+        else
+            k_extend_pt<false><<<gpt, WF_THREADS, 0, st>>>(sc, (const float4*)c->q_o[0].p, (const float4*)c->q_d[0].p, (float4*)c->hits.p, qcount, work, 0, c->pt_refill, dstats);
+    } else if (use_bvh) {
         if (c->counters_on)
             k_extend<true><<<grid, WF_THREADS, 0, st>>>(sc, (const float4*)c->q_o[0].p, (const float4*)c->q_d[0].p, (float4*)c->hits.p, qcount, 0, dstats);
         else

@@ -233,3 +233,33 @@ def test_renderer_interface(gold):
     assert np.array_equal(a, film.ReadAccum())
     assert film.UpdateDisplay().shape == (48, 64, 4)
     r.close()
+
+
+def test_cpp_shim_dropin(ctx, tmp_path):
+    """The C++ `B200Renderer : public Renderer` (host/b200_renderer.cpp), compiled against the reference's
+    UNMODIFIED headers and linked with the reference's own Film/Scene/Camera objects (oracle/_ref, built by
+    `make -C oracle shim`), driven with the viewer's call pattern: the reference Film's device accumulator
+    must hold exactly what the C-ABI path produces."""
+    import os
+    import subprocess
+    exe = os.path.join(util.ROOT, "oracle", "_ref", "shim_driver")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/shim_driver not built (needs /root/reference at build time)")
+    W, H, calls, depth, seed = 160, 90, 5, 20, 3
+    for preset in (int(S.ScenePreset.CORNELL), int(S.ScenePreset.DEFAULT)):
+        out = str(tmp_path / ("shim%d.bin" % preset))
+        r = subprocess.run([exe, str(preset), str(W), str(H), str(calls), "1", str(depth), str(seed), out],
+                           capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stdout + r.stderr
+        raw = np.fromfile(out, np.uint8)
+        accum = raw[:W * H * 12].view(np.float32).reshape(H, W, 3)
+        weights = raw[W * H * 12:W * H * 16].view(np.float32)
+        disp = raw[W * H * 16:].reshape(H, W, 4)
+        sd = S.make_scene(preset); cam = S.Camera(width=W, height=H)
+        ctx.set_scene(sd); ctx.build_bvh(); ctx.set_camera(cam); ctx.clear_accum()
+        for i in range(calls):
+            ctx.render(1, depth, seed=seed, sample_begin=i)
+        assert np.all(weights == calls)
+        assert np.array_equal(accum, ctx.read_accum())
+        mine = ctx.resolve_display(1.0, 2.2)
+        assert np.abs(mine.astype(int) - disp.astype(int)).max() <= 1     # reference GPU tonemap (film.cu:101-121)

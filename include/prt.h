@@ -116,13 +116,15 @@ typedef struct prt_stats {
     uint64_t nodes_visited;               /* BVH nodes fetched   (only if counters enabled)    */
     uint64_t prims_tested;                /* leaf primitives tested (only if counters enabled) */
     float    render_ms;                   /* device time of the last prt_render (CUDA events)  */
-    float    extend_ms;                   /* device time in the extend kernels (if timed)      */
+    float    extend_ms;                   /* device time in the extend kernels (fused mode: k_primary + k_bounce) */
     float    shade_ms;
     float    build_ms;                    /* device time of the last prt_build_bvh             */
+    float    primary_ms;                  /* part of extend_ms spent in the bounce-0 kernels   */
+    float    _padf;
     int32_t  kernel_launches;             /* kernels launched by the last prt_render           */
     int32_t  n_prims;
     int32_t  n_nodes;
-    int32_t  _pad;
+    int32_t  primary_launches;            /* bounce-0 kernel launches (= waves) of the last prt_render */
 } prt_stats;
 
 /* ---- life cycle --------------------------------------------------------------------

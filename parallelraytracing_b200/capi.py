@@ -35,7 +35,8 @@ class CStats(C.Structure):
     _fields_ = [("rays_total", C.c_uint64), ("rays_per_bounce", C.c_uint64 * PRT_MAX_DEPTH), ("paths", C.c_uint64),
                 ("nodes_visited", C.c_uint64), ("prims_tested", C.c_uint64),
                 ("render_ms", C.c_float), ("extend_ms", C.c_float), ("shade_ms", C.c_float), ("build_ms", C.c_float),
-                ("kernel_launches", C.c_int32), ("n_prims", C.c_int32), ("n_nodes", C.c_int32), ("_pad", C.c_int32)]
+                ("primary_ms", C.c_float), ("_padf", C.c_float),
+                ("kernel_launches", C.c_int32), ("n_prims", C.c_int32), ("n_nodes", C.c_int32), ("primary_launches", C.c_int32)]
 
 
 class PrtError(RuntimeError):

@@ -553,7 +553,7 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
             float4 *hits = (float4*)c->hits.p, *contrib = (float4*)c->contrib.p;
             int cur = 0;
             if (fused) {
-                if (timing) spans.push_back({stamp(), 0});
+                if (timing) spans.push_back({stamp(), 2});
                 if (c->counters_on)
                     k_primary<true><<<grid, WF_THREADS, 0, st>>>(sc, cam, (int)p0, npix, div_npix, n_paths, (uint32_t)(sample_begin + s0), seed_lo,
                                                                  seed_hi, qo[1], qd[1], qb[1], contrib, qcount, max_depth, dstats);
@@ -580,7 +580,7 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
                     cam, (int)p0, npix, div_npix, n_paths, (uint32_t)(sample_begin + s0), seed_lo, seed_hi, qo[0], qd[0], qb[0], qcount);
                 ++launches;
                 for (int b = 0; b < max_depth; ++b) {
-                    if (timing) spans.push_back({stamp(), 0});
+                    if (timing) spans.push_back({stamp(), b == 0 ? 2 : 0});
                     if (c->persistent) {
                         uint32_t* work = qcount + (PRT_MAX_DEPTH + 2) + b;
                         if (c->counters_on) k_extend_pt<true><<<grid_pt, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], hits, qcount, work, b, c->pt_refill, dstats);
@@ -613,13 +613,15 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
     s.paths = paths;
     s.kernel_launches = launches;
     cudaEventElapsedTime(&s.render_ms, c->ev0, c->ev1);
-    float ms[2] = {0.f, 0.f};
+    float ms[3] = {0.f, 0.f, 0.f};
+    int n_primary = 0;
     for (auto& sp : spans) {
         float a = 0.f;
         cudaEventElapsedTime(&a, c->ev_pool[sp.first], c->ev_pool[sp.first + 1]);
         ms[sp.second] += a;
+        if (sp.second == 2) ++n_primary;
     }
-    s.extend_ms = ms[0]; s.shade_ms = ms[1];
+    s.extend_ms = ms[0] + ms[2]; s.shade_ms = ms[1]; s.primary_ms = ms[2]; s.primary_launches = n_primary;
     s.n_prims = c->n_prims; s.n_nodes = c->n_prims > 1 ? c->n_prims - 1 : 0;
     return PRT_OK;
 }

@@ -30,6 +30,10 @@ WORKLOADS = {
     "dragon960k_1080p_16spp_d8": dict(scene="dragon960k", W=1920, H=1080, spp=16, depth=8),
     "soup10m_1080p_4spp_d16": dict(scene="soup10m", W=1920, H=1080, spp=4, depth=16),
     "soup1m_1080p_8spp_d16": dict(scene="soup1m", W=1920, H=1080, spp=8, depth=16),
+    # BASELINE.json configs[3] / SURVEY 8d C4: the C3 mesh scene at 4K, 1024 spp IN TOTAL, sample range split over
+    # the ranks (strong scaling: rank r renders samples [r*1024/N, (r+1)*1024/N)), one 99.5 MB NCCL sum-reduce
+    "dragon960k_4k_1024spp_d8": dict(scene="dragon960k", W=3840, H=2160, spp=1024, depth=8, strong=True),
+    "dragon960k_4k_64spp_d8": dict(scene="dragon960k", W=3840, H=2160, spp=64, depth=8, strong=True),
 }
 DEFAULT_WORKLOAD = "cornell_1080p_256spp_d8"
 
@@ -208,6 +212,10 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     sd, cam, w = make_workload(args.workload)
     W, H, spp, depth = w["W"], w["H"], w["spp"], w["depth"]
+    if w.get("strong"):                       # fixed total work: every rank takes an equal share of the samples
+        if spp % world:
+            raise SystemExit("bench.py: %d spp does not split over %d ranks" % (spp, world))
+        spp //= world
     ctx = Context(local)
     for kv in args.opt:
         k, v = kv.split("=")
@@ -293,12 +301,12 @@ def run_ours(args):
         e2e_s, e2e_rays = float(tmax[0]), float(tsum[1])
     return dict(rank=rank, world=world, ctx=ctx, sd=sd, cam=cam, w=w, rays_all=rays_all, dev_ms_max=dev_ms_max,
                 launches_all=launches_all, ext_ms=ext_ms, shd_ms=shd_ms, prim_ms=prim_ms, render_ms=render_ms, red_ms=red_ms, rays=rays,
-                clk=clk, e2e_s=e2e_s, e2e_rays=e2e_rays, build_ms=build_ms, wall_ms=wall_ms, img_mean=float(img.mean()))
+                spp=spp, clk=clk, e2e_s=e2e_s, e2e_rays=e2e_rays, build_ms=build_ms, wall_ms=wall_ms, img_mean=float(img.mean()))
 
 
 def roofline_and_json(args, R):
     ctx, w, sd = R["ctx"], R["w"], R["sd"]
-    W, H, spp, depth = w["W"], w["H"], w["spp"], w["depth"]
+    W, H, spp, depth = w["W"], w["H"], R["spp"], w["depth"]
     steps = args.steps
     # per-ray traversal work from the device counters (untimed pass, counters cost speed)
     ctx.enable_counters(True)
@@ -349,8 +357,8 @@ def roofline_and_json(args, R):
     dev_s = R["dev_ms_max"] * 1e-3
     value = R["rays_all"] / dev_s / 1e6
     out = {"metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": R["world"], "steps": steps, "warmup": args.warmup,
-           "ms_per_step": R["dev_ms_max"] / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-           "dtype": "f32", "data": "synthetic",
+           "ms_per_step": R["dev_ms_max"] / steps, "higher_is_better": True, "scaling": "strong" if w.get("strong") else "weak",
+           "vs_baseline": None, "dtype": "f32", "data": "synthetic",
            "config": {"workload": args.workload, "scene": sd.name, "prims": sd.n_prims, "width": W, "height": H,
                       "spp_per_step_per_gpu": spp, "depth": depth, "partition": "sample-range, NCCL sum-reduce to rank 0",
                       "l2": "256 MiB L2 flush between timed steps; ray queues (GBs) also exceed the 126 MB L2",

@@ -337,6 +337,7 @@ int prt_set_option(prt_ctx* ctx, const char* key, int64_t value) {
     else if (!strcmp(key, "use_graph")) c->use_graph = value ? 1 : 0;
     else if (!strcmp(key, "fused")) c->fused = value < 0 ? -1 : (value ? 1 : 0);
     else if (!strcmp(key, "fused_max_prims")) c->fused_max_prims = (int)value;
+    else if (!strcmp(key, "brute_max_prims")) c->brute_max_prims = (int)value;
     else if (!strcmp(key, "persistent")) c->persistent = value ? 1 : 0;
     else if (!strcmp(key, "pt_refill")) { if (value < 0 || value > 32) return set_err(c, PRT_ERR_INVALID, "pt_refill out of range"); c->pt_refill = (int)value; }
     else if (!strcmp(key, "stage_timing")) c->stage_timing = value ? 1 : 0;

@@ -123,6 +123,7 @@ struct SceneView {
     int              root_code; // root: 0 if n_prims>1, leaf code (negative-as-~) if n_prims==1
     float            tri_tmin;
     float sky_r, sky_g, sky_b;
+    int              brute;    // tiny sphere/quad scene: test every primitive in list order, no BVH (see traverse())
 };
 
 // ------------------------------------------------------------------ primitive tests

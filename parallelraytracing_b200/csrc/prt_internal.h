@@ -64,6 +64,7 @@ struct Ctx {
     int use_graph = 1;
     int fused = -1;                             // 1: k_primary/k_bounce, 0: raygen/extend/shade as separate stages, -1: by scene size
     int fused_max_prims = 64;                   // auto: fuse when traversal is a handful of nodes (shading dominates)
+    int brute_max_prims = 8;                    // fused kernels: sphere/quad scenes this small skip the BVH (uniform loop over the list)
     int persistent = 1;                         // staged extend = persistent threads with per-lane dynamic fetch
     int pt_refill = 16;                         // refill the warp when fewer lanes than this are traversing
     int stage_timing = 1;                       // CUDA-event pairs around the hot kernels

@@ -56,11 +56,32 @@ k_raygen(CamView cam, int pix0, int npix, FastDiv div_npix, int n_paths, uint32_
 // ------------------------------------------------------------------ extend
 // Closest hit by stack traversal of the two-child LBVH. One thread per ray; the traversal
 // stack lives in shared memory ([entry][thread], conflict-free), overflowing to local memory.
-template <bool COUNT>
+template <bool COUNT, bool BRUTE = false>
 __device__ __forceinline__ Best traverse(const SceneView& sc, V3 o, V3 d, int* __restrict__ sstack,
                                          uint32_t& n_nodes, uint32_t& n_prims) {
     Best best; best_init(best);
     if (sc.n_prims == 0) return best;
+    if (BRUTE) {
+        // A handful of spheres/quads: the reference's own loop over the list (primitive.cpp:26) is cheaper than
+        // walking a BVH and, unlike it, warp-uniform: every lane tests the same record at the same time (the
+        // records come in through uniform-address loads). Same closest hit: the (t, prim_id) rule is order-free.
+        const V3 dns = sc.n_spheres > 0 ? normalize(d) : d;
+        for (int i = 0; i < sc.n_spheres; ++i) {
+            SphereRec s; s.a = __ldg(&sc.spheres[i].a); s.b = __ldg(&sc.spheres[i].b);
+            bool front;
+            float t = isect_sphere(s, o, dns, front);
+            if (t >= 0.0f) best_update(best, t, PRT_MAKE_LEAF(0, i), __float_as_int(s.b.z), front ? 1.0f : 0.0f, 0.0f);
+        }
+        for (int i = 0; i < sc.n_quads; ++i) {
+            QuadRec q; q.a = __ldg(&sc.quads[i].a); q.b = __ldg(&sc.quads[i].b);
+            q.c = __ldg(&sc.quads[i].c); q.d = __ldg(&sc.quads[i].d);
+            bool front;
+            float t = isect_quad(q, o, d, front);
+            if (t >= 0.0f) best_update(best, t, PRT_MAKE_LEAF(1, i), __float_as_int(q.d.w), front ? 1.0f : 0.0f, 0.0f);
+        }
+        if (COUNT) n_prims += (uint32_t)sc.n_prims;
+        return best;
+    }
     RayBox rb = make_raybox(o, d);
     RayShear rs; V3 dn = d;
     if (sc.n_tris > 0) rs = make_shear(d);            // per-ray triangle-test constants: only if there are triangles
@@ -311,12 +332,12 @@ k_shade(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ 
 //   k_primary = raygen + extend + shade of bounce 0 (camera rays never touch memory),
 //   k_bounce  = extend + shade of bounce b >= 1 (no hit queue); both compact into the next queue.
 // Results are bit-identical to the staged kernels (same device functions, same order).
-template <bool COUNT>
+template <bool COUNT, bool BRUTE>
 __global__ void __launch_bounds__(WF_THREADS)
 k_primary(SceneView sc, CamView cam, int pix0, int npix, FastDiv div_npix, int n_paths, uint32_t sample0, uint32_t seed_lo, uint32_t seed_hi,
           float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb, float4* __restrict__ contrib,
           uint32_t* __restrict__ qcount, int max_depth, unsigned long long* __restrict__ stats) {
-    __shared__ int sstack[STACK_SMEM * WF_THREADS];
+    __shared__ int sstack[BRUTE ? 1 : STACK_SMEM * WF_THREADS];
     const uint32_t count = (uint32_t)n_paths;
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t stride = gridDim.x * WF_THREADS;
@@ -332,7 +353,7 @@ k_primary(SceneView sc, CamView cam, int pix0, int npix, FastDiv div_npix, int n
             int y = (int)fdiv((uint32_t)pixel, cam.divW), x = pixel - y * cam.W;
             V3 d = camera_dir(cam, (float)x + 0.5f, (float)y + 0.5f);
             key = path_key(seed_lo, seed_hi, (uint32_t)pixel, sample0 + (uint32_t)s_local);
-            Best b = traverse<COUNT>(sc, cam.pos, d, sstack + threadIdx.x, nn, npr);
+            Best b = traverse<COUNT, BRUTE>(sc, cam.pos, d, BRUTE ? sstack : sstack + threadIdx.x, nn, npr);
             V3 L;
             cont = shade_segment(sc, cam.pos, d, key, 0, max_depth, b.t, b.code, b.u, b.v, beta, np, ndir, L);
             if (!cont) st_stream(&contrib[i], make_float4(L.x, L.y, L.z, 0.f));
@@ -349,12 +370,12 @@ k_primary(SceneView sc, CamView cam, int pix0, int npix, FastDiv div_npix, int n
     if (blockIdx.x == 0 && threadIdx.x == 0) { atomicAdd(&stats[0], (unsigned long long)count); qcount[0] = count; }
 }
 
-template <bool COUNT>
+template <bool COUNT, bool BRUTE>
 __global__ void __launch_bounds__(WF_THREADS)
 k_bounce(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ qd, const float4* __restrict__ qb,
          float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb, float4* __restrict__ contrib,
          uint32_t* __restrict__ qcount, int bounce, int max_depth, unsigned long long* __restrict__ stats) {
-    __shared__ int sstack[STACK_SMEM * WF_THREADS];
+    __shared__ int sstack[BRUTE ? 1 : STACK_SMEM * WF_THREADS];
     const uint32_t count = qcount[bounce];
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t stride = gridDim.x * WF_THREADS;
@@ -366,7 +387,7 @@ k_bounce(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__
         if (i < count) {
             o4 = ld_stream(&qo[i]); d4 = ld_stream(&qd[i]);
             beta = xyz(ld_stream(&qb[i]));
-            Best b = traverse<COUNT>(sc, xyz(o4), xyz(d4), sstack + threadIdx.x, nn, npr);
+            Best b = traverse<COUNT, BRUTE>(sc, xyz(o4), xyz(d4), BRUTE ? sstack : sstack + threadIdx.x, nn, npr);
             V3 L;
             cont = shade_segment(sc, xyz(o4), xyz(d4), __float_as_uint(d4.w), bounce, max_depth, b.t, b.code, b.u, b.v, beta, np, ndir, L);
             if (!cont) st_stream(&contrib[__float_as_uint(o4.w) >> 5], make_float4(L.x, L.y, L.z, 0.f));
@@ -468,6 +489,7 @@ SceneView scene_view(const Ctx* c) {
     v.root_code = c->root_code;
     v.tri_tmin = 0.001f;                                  // kShapeRayTMin, shape.h:128
     v.sky_r = c->sky[0]; v.sky_g = c->sky[1]; v.sky_b = c->sky[2];
+    v.brute = 0;                                          // only wavefront_render's fused path turns it on
     return v;
 }
 
@@ -514,6 +536,8 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
     CamView cam = cam_view(c->cam);
     uint32_t* qcount = (uint32_t*)c->qcount.p;
     unsigned long long* dstats = (unsigned long long*)c->stats_dev.p;
+    const bool brute = c->n_tris == 0 && c->n_prims <= c->brute_max_prims;   // fused kernels only
+    sc.brute = brute ? 1 : 0;
     const int grid_p = c->num_sms * c->ctas_per_sm;
     const uint32_t seed_lo = (uint32_t)seed, seed_hi = (uint32_t)(seed >> 32);
     const bool fused = c->fused < 0 ? (c->n_prims <= c->fused_max_prims) : (c->fused != 0);
@@ -554,23 +578,23 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
             int cur = 0;
             if (fused) {
                 if (timing) spans.push_back({stamp(), 2});
-                if (c->counters_on)
-                    k_primary<true><<<grid, WF_THREADS, 0, st>>>(sc, cam, (int)p0, npix, div_npix, n_paths, (uint32_t)(sample_begin + s0), seed_lo,
-                                                                 seed_hi, qo[1], qd[1], qb[1], contrib, qcount, max_depth, dstats);
-                else
-                    k_primary<false><<<grid, WF_THREADS, 0, st>>>(sc, cam, (int)p0, npix, div_npix, n_paths, (uint32_t)(sample_begin + s0), seed_lo,
-                                                                  seed_hi, qo[1], qd[1], qb[1], contrib, qcount, max_depth, dstats);
+                {
+                    auto kp = c->counters_on ? (brute ? k_primary<true, true> : k_primary<true, false>)
+                                             : (brute ? k_primary<false, true> : k_primary<false, false>);
+                    kp<<<grid, WF_THREADS, 0, st>>>(sc, cam, (int)p0, npix, div_npix, n_paths, (uint32_t)(sample_begin + s0), seed_lo,
+                                                    seed_hi, qo[1], qd[1], qb[1], contrib, qcount, max_depth, dstats);
+                }
                 if (timing) stamp();
                 ++launches;
                 cur = 1;
                 for (int b = 1; b < max_depth; ++b) {
                     if (timing) spans.push_back({stamp(), 0});
-                    if (c->counters_on)
-                        k_bounce<true><<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], qb[cur], qo[cur ^ 1], qd[cur ^ 1], qb[cur ^ 1],
-                                                                    contrib, qcount, b, max_depth, dstats);
-                    else
-                        k_bounce<false><<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], qb[cur], qo[cur ^ 1], qd[cur ^ 1], qb[cur ^ 1],
-                                                                     contrib, qcount, b, max_depth, dstats);
+                    {
+                        auto kb = c->counters_on ? (brute ? k_bounce<true, true> : k_bounce<true, false>)
+                                                 : (brute ? k_bounce<false, true> : k_bounce<false, false>);
+                        kb<<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], qb[cur], qo[cur ^ 1], qd[cur ^ 1], qb[cur ^ 1],
+                                                        contrib, qcount, b, max_depth, dstats);
+                    }
                     if (timing) stamp();
                     ++launches;
                     cur ^= 1;

@@ -184,8 +184,25 @@ def test_staged_pipeline_equals_fused(ctx, gold):
             ctx.set_option("fused", fused)
             ctx.clear_accum(); ctx.render(3, 8, seed=11)
             out.append((ctx.read_accum(), ctx.stats().rays_total, list(ctx.stats().rays_per_bounce)))
-        ctx.set_option("fused", 1)
+        ctx.set_option("fused", -1)
         assert np.array_equal(out[0][0], out[1][0]) and out[0][1:] == out[1][1:]
+
+
+def test_tiny_scene_list_loop_equals_bvh(ctx):
+    """Sphere/quad scenes of <= brute_max_prims primitives skip the BVH in the fused kernels (a warp-uniform
+    loop over the list, the reference's own algorithm primitive.cpp:26). The (t, prim_id) closest-hit rule is
+    order-free, so the image and every per-bounce ray count must equal the BVH walk bit for bit."""
+    for sd in (S.cornell(), S.closed_cornell(), S.make_scene(S.ScenePreset.MATERIAL_TEST)):
+        cam = S.Camera(width=112, height=80)
+        ctx.set_scene(sd); ctx.build_bvh(); ctx.set_camera(cam)
+        out = []
+        for limit in (1 << 20, 0):                     # list loop for any size / always the BVH
+            ctx.set_option("brute_max_prims", limit)
+            ctx.set_option("fused", 1)
+            ctx.clear_accum(); ctx.render(3, 8, seed=23)
+            out.append((ctx.read_accum(), list(ctx.stats().rays_per_bounce)))
+        ctx.set_option("brute_max_prims", 8); ctx.set_option("fused", -1)
+        assert np.array_equal(out[0][0], out[1][0]) and out[0][1] == out[1][1], sd.name
 
 
 def test_display_resolve_exact(ctx, oracle):

@@ -56,7 +56,7 @@ k_raygen(CamView cam, int pix0, int npix, FastDiv div_npix, int n_paths, uint32_
 // ------------------------------------------------------------------ extend
 // Closest hit by stack traversal of the two-child LBVH. One thread per ray; the traversal
 // stack lives in shared memory ([entry][thread], conflict-free), overflowing to local memory.
-template <bool COUNT, bool BRUTE = false>
+template <bool COUNT, bool BRUTE = false, int SS = STACK_SMEM>
 __device__ __forceinline__ Best traverse(const SceneView& sc, V3 o, V3 d, int* __restrict__ sstack,
                                          uint32_t& n_nodes, uint32_t& n_prims) {
     Best best; best_init(best);
@@ -87,7 +87,7 @@ __device__ __forceinline__ Best traverse(const SceneView& sc, V3 o, V3 d, int* _
     if (sc.n_tris > 0) rs = make_shear(d);            // per-ray triangle-test constants: only if there are triangles
     else { rs.kx = 0; rs.ky = 1; rs.kz = 2; rs.sx = rs.sy = rs.sz = 0.f; }
     if (sc.n_spheres > 0) dn = normalize(d);          // Circle's local direction (primitive.cpp:30): only if there are spheres
-    int lstack[STACK_LOCAL];
+    int lstack[STACK_LOCAL + STACK_SMEM - SS];
     int sp = 0;
     int cur = sc.root_code;
     for (;;) {
@@ -102,7 +102,7 @@ __device__ __forceinline__ Best traverse(const SceneView& sc, V3 o, V3 d, int* _
             if (tl >= 0.0f && tr >= 0.0f) {
                 int nearc = cl, farc = cr;
                 if (tr < tl) { nearc = cr; farc = cl; }
-                if (sp < STACK_SMEM) sstack[sp * WF_THREADS] = farc; else lstack[sp - STACK_SMEM] = farc;
+                if (sp < SS) sstack[sp * WF_THREADS] = farc; else lstack[sp - SS] = farc;
                 ++sp;
                 cur = nearc;
                 continue;
@@ -114,7 +114,7 @@ __device__ __forceinline__ Best traverse(const SceneView& sc, V3 o, V3 d, int* _
         }
         if (sp == 0) break;
         --sp;
-        cur = sp < STACK_SMEM ? sstack[sp * WF_THREADS] : lstack[sp - STACK_SMEM];
+        cur = sp < SS ? sstack[sp * WF_THREADS] : lstack[sp - SS];
     }
     return best;
 }
@@ -303,28 +303,91 @@ __device__ __forceinline__ void push_compacted(bool cont, uint32_t lane, uint32_
     }
 }
 
+// ------------------------------------------------------------------ per-warp shade queue
+// Only the rays that HIT something need the expensive part of shading (surface, material, the
+// rejection-sampled scatter); on sky-lit scenes that is a minority of a warp's lanes (ncu: the scatter
+// code ran at 3.5-7 of 32 lanes). So misses are finished inline (L = beta*sky, one store) and hits are
+// appended to a small queue in shared memory owned by the warp; whenever 32 or more are waiting, the warp
+// shades 32 of them at full width. No block barrier: the queue is private to the warp. Record = 15 words,
+// stored word-major ([word][entry]) so that consecutive lanes touch consecutive banks.
+constexpr int SQ_CAP = 64;        // < 32 waiting + <= 32 appended per batch
+constexpr int SQ_WORDS = 15;      // o.xyz d.xyz beta.rgb key slot_bounce t code u v
+constexpr int SQ_FLOATS = SQ_CAP * SQ_WORDS;
+constexpr int WF_WARPS = WF_THREADS / 32;
+
+__device__ __forceinline__ void sq_put(float* __restrict__ q, int e, V3 o, V3 d, V3 beta, uint32_t key, uint32_t slot_bounce,
+                                       float t, uint32_t code, float u, float v) {
+    q[0 * SQ_CAP + e] = o.x;  q[1 * SQ_CAP + e] = o.y;  q[2 * SQ_CAP + e] = o.z;
+    q[3 * SQ_CAP + e] = d.x;  q[4 * SQ_CAP + e] = d.y;  q[5 * SQ_CAP + e] = d.z;
+    q[6 * SQ_CAP + e] = beta.x; q[7 * SQ_CAP + e] = beta.y; q[8 * SQ_CAP + e] = beta.z;
+    q[9 * SQ_CAP + e] = __uint_as_float(key); q[10 * SQ_CAP + e] = __uint_as_float(slot_bounce);
+    q[11 * SQ_CAP + e] = t; q[12 * SQ_CAP + e] = __uint_as_float(code); q[13 * SQ_CAP + e] = u; q[14 * SQ_CAP + e] = v;
+}
+
+// Shade queue entries [first, first+n) (n <= 32), one per lane, and push the continuing paths. Whole warp calls.
+__device__ __forceinline__ void sq_shade(const SceneView& sc, const float* __restrict__ q, int first, int n, uint32_t lane,
+                                         int bounce, int max_depth, float4* __restrict__ contrib, uint32_t* __restrict__ next_count,
+                                         float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb) {
+    bool cont = false;
+    V3 beta = mk(0, 0, 0), np = beta, ndir = beta;
+    uint32_t key = 0, sb = 0;
+    if ((int)lane < n) {
+        const int e = first + (int)lane;
+        V3 o = mk(q[0 * SQ_CAP + e], q[1 * SQ_CAP + e], q[2 * SQ_CAP + e]);
+        V3 d = mk(q[3 * SQ_CAP + e], q[4 * SQ_CAP + e], q[5 * SQ_CAP + e]);
+        beta = mk(q[6 * SQ_CAP + e], q[7 * SQ_CAP + e], q[8 * SQ_CAP + e]);
+        key = __float_as_uint(q[9 * SQ_CAP + e]); sb = __float_as_uint(q[10 * SQ_CAP + e]);
+        V3 L;
+        cont = shade_segment(sc, o, d, key, bounce, max_depth, q[11 * SQ_CAP + e], __float_as_uint(q[12 * SQ_CAP + e]),
+                             q[13 * SQ_CAP + e], q[14 * SQ_CAP + e], beta, np, ndir, L);
+        if (!cont) st_stream(&contrib[sb >> 5], make_float4(L.x, L.y, L.z, 0.f));
+    }
+    push_compacted(cont, lane, next_count, no, nd, nb, np, ndir, beta, sb + 1u, key);
+}
+
+// One batch of <= 32 segments whose closest hit is known: misses end here, hits go through the queue.
+// `live` = this lane holds a segment. Returns the new queue length. Whole warp calls.
+__device__ __forceinline__ int sq_batch(const SceneView& sc, float* __restrict__ q, int qn, uint32_t lane, bool live,
+                                        V3 o, V3 d, V3 beta, uint32_t key, uint32_t slot_bounce, float t, uint32_t code, float u, float v,
+                                        int bounce, int max_depth, float4* __restrict__ contrib, uint32_t* __restrict__ next_count,
+                                        float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb) {
+    const bool hit = live && code != PRT_NO_HIT;
+    if (live && !hit) {                                                 // cpu/renderer.cpp:99
+        V3 L = beta * mk(sc.sky_r, sc.sky_g, sc.sky_b);
+        st_stream(&contrib[slot_bounce >> 5], make_float4(L.x, L.y, L.z, 0.f));
+    }
+    const uint32_t mask = __ballot_sync(0xffffffffu, hit);
+    if (hit) sq_put(q, qn + __popc(mask & ((1u << lane) - 1u)), o, d, beta, key, slot_bounce, t, code, u, v);
+    qn += __popc(mask);
+    __syncwarp();
+    if (qn >= 32) {
+        qn -= 32;
+        sq_shade(sc, q, qn, 32, lane, bounce, max_depth, contrib, next_count, no, nd, nb);
+        __syncwarp();
+    }
+    return qn;
+}
+
+
 __global__ void __launch_bounds__(WF_THREADS)
 k_shade(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ qd, const float4* __restrict__ qb,
         const float4* __restrict__ hits, float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb,
         float4* __restrict__ contrib, uint32_t* __restrict__ qcount, int bounce, int max_depth) {
+    __shared__ float sq[WF_WARPS * SQ_FLOATS];
+    float* q = sq + (threadIdx.x >> 5) * SQ_FLOATS;
     const uint32_t count = qcount[bounce];
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t stride = gridDim.x * WF_THREADS;
+    int qn = 0;
     for (uint32_t base = blockIdx.x * WF_THREADS + (threadIdx.x & ~31u); base < count; base += stride) {
         uint32_t i = base + lane;
-        bool cont = false;
-        float4 o4 = make_float4(0, 0, 0, 0), d4 = o4; V3 beta = mk(0, 0, 0), np = beta, ndir = beta;
-        if (i < count) {
-            o4 = ld_stream(&qo[i]); d4 = ld_stream(&qd[i]);
-            float4 b4 = ld_stream(&qb[i]), h = ld_stream(&hits[i]);
-            beta = xyz(b4);
-            V3 L;
-            cont = shade_segment(sc, xyz(o4), xyz(d4), __float_as_uint(d4.w), bounce, max_depth, h.x, __float_as_uint(h.y), h.z, h.w,
-                                 beta, np, ndir, L);
-            if (!cont) st_stream(&contrib[__float_as_uint(o4.w) >> 5], make_float4(L.x, L.y, L.z, 0.f));
-        }
-        push_compacted(cont, lane, &qcount[bounce + 1], no, nd, nb, np, ndir, beta, __float_as_uint(o4.w) + 1u, __float_as_uint(d4.w));
+        float4 o4 = make_float4(0, 0, 0, 0), d4 = o4, b4 = o4, h = o4;
+        const bool live = i < count;
+        if (live) { o4 = ld_stream(&qo[i]); d4 = ld_stream(&qd[i]); b4 = ld_stream(&qb[i]); h = ld_stream(&hits[i]); }
+        qn = sq_batch(sc, q, qn, lane, live, xyz(o4), xyz(d4), xyz(b4), __float_as_uint(d4.w), __float_as_uint(o4.w),
+                      h.x, __float_as_uint(h.y), h.z, h.w, bounce, max_depth, contrib, &qcount[bounce + 1], no, nd, nb);
     }
+    if (qn > 0) sq_shade(sc, q, 0, qn, lane, bounce, max_depth, contrib, &qcount[bounce + 1], no, nd, nb);
 }
 
 // ------------------------------------------------------------------ fused stages
@@ -332,34 +395,39 @@ k_shade(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ 
 //   k_primary = raygen + extend + shade of bounce 0 (camera rays never touch memory),
 //   k_bounce  = extend + shade of bounce b >= 1 (no hit queue); both compact into the next queue.
 // Results are bit-identical to the staged kernels (same device functions, same order).
+constexpr int FUSED_STACK = 16;   // fused kernels walk trees of <= fused_max_prims primitives; leaves room for the shade queue
+
 template <bool COUNT, bool BRUTE>
 __global__ void __launch_bounds__(WF_THREADS)
 k_primary(SceneView sc, CamView cam, int pix0, int npix, FastDiv div_npix, int n_paths, uint32_t sample0, uint32_t seed_lo, uint32_t seed_hi,
           float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb, float4* __restrict__ contrib,
           uint32_t* __restrict__ qcount, int max_depth, unsigned long long* __restrict__ stats) {
-    __shared__ int sstack[BRUTE ? 1 : STACK_SMEM * WF_THREADS];
+    __shared__ int sstack[BRUTE ? 1 : FUSED_STACK * WF_THREADS];
+    __shared__ float sq[WF_WARPS * SQ_FLOATS];
+    float* q = sq + (threadIdx.x >> 5) * SQ_FLOATS;
     const uint32_t count = (uint32_t)n_paths;
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t stride = gridDim.x * WF_THREADS;
     uint32_t nn = 0, npr = 0;
+    int qn = 0;
     for (uint32_t base = blockIdx.x * WF_THREADS + (threadIdx.x & ~31u); base < count; base += stride) {
         uint32_t i = base + lane;
-        bool cont = false;
-        V3 beta = mk(1.f, 1.f, 1.f), np = mk(0, 0, 0), ndir = np;
+        const bool live = i < count;
+        V3 d = mk(0, 0, 0);
         uint32_t key = 0;
-        if (i < count) {
+        Best b; best_init(b);
+        if (live) {
             int s_local = (int)fdiv(i, div_npix);
             int pixel = pix0 + ((int)i - s_local * npix);
             int y = (int)fdiv((uint32_t)pixel, cam.divW), x = pixel - y * cam.W;
-            V3 d = camera_dir(cam, (float)x + 0.5f, (float)y + 0.5f);
+            d = camera_dir(cam, (float)x + 0.5f, (float)y + 0.5f);
             key = path_key(seed_lo, seed_hi, (uint32_t)pixel, sample0 + (uint32_t)s_local);
-            Best b = traverse<COUNT, BRUTE>(sc, cam.pos, d, BRUTE ? sstack : sstack + threadIdx.x, nn, npr);
-            V3 L;
-            cont = shade_segment(sc, cam.pos, d, key, 0, max_depth, b.t, b.code, b.u, b.v, beta, np, ndir, L);
-            if (!cont) st_stream(&contrib[i], make_float4(L.x, L.y, L.z, 0.f));
+            b = traverse<COUNT, BRUTE, FUSED_STACK>(sc, cam.pos, d, BRUTE ? sstack : sstack + threadIdx.x, nn, npr);
         }
-        push_compacted(cont, lane, &qcount[1], no, nd, nb, np, ndir, beta, (i << 5) + 1u, key);
+        qn = sq_batch(sc, q, qn, lane, live, cam.pos, d, mk(1.f, 1.f, 1.f), key, i << 5, b.t, b.code, b.u, b.v,
+                      0, max_depth, contrib, &qcount[1], no, nd, nb);
     }
+    if (qn > 0) sq_shade(sc, q, 0, qn, lane, 0, max_depth, contrib, &qcount[1], no, nd, nb);
     if (COUNT) {
         for (int o = 16; o > 0; o >>= 1) { nn += __shfl_xor_sync(0xffffffffu, nn, o); npr += __shfl_xor_sync(0xffffffffu, npr, o); }
         if (lane == 0 && (nn | npr)) {
@@ -375,25 +443,27 @@ __global__ void __launch_bounds__(WF_THREADS)
 k_bounce(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ qd, const float4* __restrict__ qb,
          float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb, float4* __restrict__ contrib,
          uint32_t* __restrict__ qcount, int bounce, int max_depth, unsigned long long* __restrict__ stats) {
-    __shared__ int sstack[BRUTE ? 1 : STACK_SMEM * WF_THREADS];
+    __shared__ int sstack[BRUTE ? 1 : FUSED_STACK * WF_THREADS];
+    __shared__ float sq[WF_WARPS * SQ_FLOATS];
+    float* q = sq + (threadIdx.x >> 5) * SQ_FLOATS;
     const uint32_t count = qcount[bounce];
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t stride = gridDim.x * WF_THREADS;
     uint32_t nn = 0, npr = 0;
+    int qn = 0;
     for (uint32_t base = blockIdx.x * WF_THREADS + (threadIdx.x & ~31u); base < count; base += stride) {
         uint32_t i = base + lane;
-        bool cont = false;
-        float4 o4 = make_float4(0, 0, 0, 0), d4 = o4; V3 beta = mk(0, 0, 0), np = beta, ndir = beta;
-        if (i < count) {
-            o4 = ld_stream(&qo[i]); d4 = ld_stream(&qd[i]);
-            beta = xyz(ld_stream(&qb[i]));
-            Best b = traverse<COUNT, BRUTE>(sc, xyz(o4), xyz(d4), BRUTE ? sstack : sstack + threadIdx.x, nn, npr);
-            V3 L;
-            cont = shade_segment(sc, xyz(o4), xyz(d4), __float_as_uint(d4.w), bounce, max_depth, b.t, b.code, b.u, b.v, beta, np, ndir, L);
-            if (!cont) st_stream(&contrib[__float_as_uint(o4.w) >> 5], make_float4(L.x, L.y, L.z, 0.f));
+        const bool live = i < count;
+        float4 o4 = make_float4(0, 0, 0, 0), d4 = o4, b4 = o4;
+        Best b; best_init(b);
+        if (live) {
+            o4 = ld_stream(&qo[i]); d4 = ld_stream(&qd[i]); b4 = ld_stream(&qb[i]);
+            b = traverse<COUNT, BRUTE, FUSED_STACK>(sc, xyz(o4), xyz(d4), BRUTE ? sstack : sstack + threadIdx.x, nn, npr);
         }
-        push_compacted(cont, lane, &qcount[bounce + 1], no, nd, nb, np, ndir, beta, __float_as_uint(o4.w) + 1u, __float_as_uint(d4.w));
+        qn = sq_batch(sc, q, qn, lane, live, xyz(o4), xyz(d4), xyz(b4), __float_as_uint(d4.w), __float_as_uint(o4.w),
+                      b.t, b.code, b.u, b.v, bounce, max_depth, contrib, &qcount[bounce + 1], no, nd, nb);
     }
+    if (qn > 0) sq_shade(sc, q, 0, qn, lane, bounce, max_depth, contrib, &qcount[bounce + 1], no, nd, nb);
     if (COUNT) {
         for (int o = 16; o > 0; o >>= 1) { nn += __shfl_xor_sync(0xffffffffu, nn, o); npr += __shfl_xor_sync(0xffffffffu, npr, o); }
         if (lane == 0 && (nn | npr)) {

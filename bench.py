@@ -332,7 +332,9 @@ def roofline_and_json(args, R):
         queue_bytes = rays_step * (32 + 16) + rays_step * 64 + cont * 48 + paths_step * 16 + paths_step * 48
         name = "k_extend_pt + k_shade (persistent LBVH traversal, shade/compaction)"
     alg_bytes = queue_bytes + rays_step * (b_shade + b_trav)
-    ker_ms = (R["ext_ms"] + R["shd_ms"]) / steps
+    # kernel time: summed per-launch CUDA-event spans; with two waves in flight (two streams) spans of different
+    # waves overlap in time, so the sum is capped by the device time of the whole render
+    ker_ms = min(R["ext_ms"] + R["shd_ms"], R["render_ms"]) / steps
     peak, peak_src = peaks()
     ach = alg_bytes / (ker_ms * 1e-3) / 1e9
     traffic = None

@@ -188,6 +188,11 @@ int  prt_set_accum_buffer(prt_ctx* ctx, float* device_rgb);
 int  prt_read_accum(prt_ctx* ctx, float* host_rgb);
 /* Samples per pixel accumulated since the last clear. */
 int  prt_accum_spp(const prt_ctx* ctx);
+/* Declare the weight (samples per pixel) of what the accumulation buffer holds. For a caller that fills
+ * the external buffer itself - e.g. rank 0 after the NCCL sum-reduce of N ranks' buffers - so that
+ * prt_resolve_display divides by the right count (Film::m_Weights after AddSampleBufferGPU(buf, w),
+ * film.cu:79-99, 111-115). */
+int  prt_set_accum_spp(prt_ctx* ctx, int spp);
 
 /* ---- film resolve -----------------------------------------------
  * accum/spp -> Reinhard -> gamma -> RGBA8, Film::UpdateDisplay semantics

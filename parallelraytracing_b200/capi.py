@@ -46,7 +46,7 @@ class PrtError(RuntimeError):
 EXPORTS = [
     "prt_create", "prt_destroy", "prt_last_error", "prt_version", "prt_set_scene", "prt_build_bvh",
     "prt_set_camera", "prt_render", "prt_clear_accum", "prt_scale_accum", "prt_accum_device_ptr",
-    "prt_set_accum_buffer", "prt_read_accum", "prt_accum_spp", "prt_resolve_display", "prt_trace_batch",
+    "prt_set_accum_buffer", "prt_read_accum", "prt_accum_spp", "prt_set_accum_spp", "prt_resolve_display", "prt_trace_batch",
     "prt_debug_lbvh", "prt_num_prims", "prt_enable_counters", "prt_get_stats", "prt_set_option",
 ]
 
@@ -82,6 +82,7 @@ def load_library():
     lib.prt_set_accum_buffer.argtypes = [vp, vp]
     lib.prt_read_accum.argtypes = [vp, vp]
     lib.prt_accum_spp.argtypes = [vp]
+    lib.prt_set_accum_spp.argtypes = [vp, i32]
     lib.prt_resolve_display.argtypes = [vp, f32, f32, vp]
     lib.prt_trace_batch.argtypes = [vp, vp, i32, vp, i32]
     lib.prt_debug_lbvh.argtypes = [vp, vp, vp, vp, vp, vp, vp]
@@ -172,6 +173,9 @@ class Context:
 
     def accum_spp(self):
         return self.lib.prt_accum_spp(self.h)
+
+    def set_accum_spp(self, spp):
+        self._check(self.lib.prt_set_accum_spp(self.h, int(spp)), "prt_set_accum_spp")
 
     def resolve_display(self, exposure=1.0, gamma=2.2):
         out = np.empty((self.height, self.width, 4), dtype=np.uint8)

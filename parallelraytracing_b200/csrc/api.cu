@@ -92,9 +92,12 @@ void prt_destroy(prt_ctx* ctx) {
                       &c->vals[0], &c->vals[1], &c->block_hist, &c->children, &c->parent, &c->node_min, &c->node_max,
                       &c->flags, &c->nodes, &c->tri_v, &c->tri_n, &c->morton, &c->accum_own, &c->display,
                       &c->q_o[0], &c->q_o[1], &c->q_d[0], &c->q_d[1], &c->q_b[0], &c->q_b[1], &c->hits, &c->contrib,
-                      &c->qcount, &c->stats_dev};
+                      &c->q2_o[0], &c->q2_o[1], &c->q2_d[0], &c->q2_d[1], &c->q2_b[0], &c->q2_b[1], &c->hits2, &c->contrib2,
+                      &c->qcount2, &c->qcount, &c->stats_dev};
     for (DevBuf* b : bufs) dev_free(*b);
     for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
+    for (cudaEvent_t e : {c->ev_res[0], c->ev_res[1], c->ev_join}) if (e) cudaEventDestroy(e);
+    if (c->stream2) { cudaStreamSynchronize(c->stream2); cudaStreamDestroy(c->stream2); }
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -264,6 +267,12 @@ int prt_read_accum(prt_ctx* ctx, float* host_rgb) {
 
 int prt_accum_spp(const prt_ctx* ctx) { return ctx ? ctx->c.accum_spp : 0; }
 
+int prt_set_accum_spp(prt_ctx* ctx, int spp) {
+    if (!ctx || spp < 0) return set_err(ctx ? &ctx->c : nullptr, PRT_ERR_INVALID, "prt_set_accum_spp: bad argument");
+    ctx->c.accum_spp = spp;
+    return PRT_OK;
+}
+
 int prt_resolve_display(prt_ctx* ctx, float exposure, float gamma, uint8_t* host_rgba) {
     if (!ctx || !host_rgba) return set_err(ctx ? &ctx->c : nullptr, PRT_ERR_INVALID, "prt_resolve_display: NULL argument");
     Ctx* c = &ctx->c;
@@ -338,6 +347,7 @@ int prt_set_option(prt_ctx* ctx, const char* key, int64_t value) {
     else if (!strcmp(key, "fused")) c->fused = value < 0 ? -1 : (value ? 1 : 0);
     else if (!strcmp(key, "fused_max_prims")) c->fused_max_prims = (int)value;
     else if (!strcmp(key, "brute_max_prims")) c->brute_max_prims = (int)value;
+    else if (!strcmp(key, "overlap")) c->overlap = value ? 1 : 0;
     else if (!strcmp(key, "persistent")) c->persistent = value ? 1 : 0;
     else if (!strcmp(key, "pt_refill")) { if (value < 0 || value > 32) return set_err(c, PRT_ERR_INVALID, "pt_refill out of range"); c->pt_refill = (int)value; }
     else if (!strcmp(key, "stage_timing")) c->stage_timing = value ? 1 : 0;

@@ -82,7 +82,11 @@ PRT_DEV float rng_uniform(Rng& r) {
     return __int2float_rn((int)rng_next31(r)) * 4.656612873077392578125e-10f;  // / 2^31
 }
 // Random(-1, 1): min + (max - min) * Random()   (math.h:20-23)
-PRT_DEV float rng_pm1(Rng& r) { return -1.0f + 2.0f * rng_uniform(r); }
+// One FFMA: x*2^-31, the doubling and x*2^-30 are all exact (power-of-two scalings of a 24-bit significand), so
+// fmaf(x, 2^-30, -1) rounds the same real number once, exactly like the three-operation form does.
+PRT_DEV float rng_pm1(Rng& r) {
+    return fmaf(__int2float_rn((int)rng_next31(r)), 9.31322574615478515625e-10f, -1.0f);
+}
 // RandomUnitVector: rejection in the cube (math.h:26-36)
 PRT_DEV V3 rng_unit_vector(Rng& r) {
     for (;;) {

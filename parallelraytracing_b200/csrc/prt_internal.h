@@ -58,6 +58,12 @@ struct Ctx {
     DevBuf hits;                                // float4 per ray
     DevBuf contrib;                             // float4 per path slot
     DevBuf qcount;                              // uint32 [PRT_MAX_DEPTH+2]
+    // second buffer set + stream: consecutive waves alternate between the two sets so that the thin tail
+    // bounces of wave k (a few thousand rays, launch-bound) run under the primary stage of wave k+1
+    DevBuf q2_o[2], q2_d[2], q2_b[2], hits2, contrib2, qcount2;
+    cudaStream_t stream2 = nullptr;
+    cudaEvent_t ev_res[2] = {nullptr, nullptr}, ev_join = nullptr;
+    int overlap = 1;                            // 1: two waves in flight (when a render has more than one wave)
     DevBuf stats_dev;                           // uint64 [PRT_MAX_DEPTH + 4]
     int ctas_per_sm = 8;
     int counters_on = 0;

@@ -577,7 +577,7 @@ static CamView cam_view(const prt_camera& k) {
     return v;
 }
 
-static int ensure_wave_buffers(Ctx* c, int64_t paths) {
+static int ensure_wave_buffers(Ctx* c, int64_t paths, bool second_set = false) {
     int rc;
     size_t b16 = (size_t)paths * 16;
     for (int k = 0; k < 2; ++k)
@@ -586,25 +586,38 @@ static int ensure_wave_buffers(Ctx* c, int64_t paths) {
     if ((rc = dev_reserve(c, c->hits, b16)) || (rc = dev_reserve(c, c->contrib, b16))) return rc;
     if ((rc = dev_reserve(c, c->qcount, 2 * (PRT_MAX_DEPTH + 2) * 4))) return rc;   // queue lengths + per-launch work counters
     if ((rc = dev_reserve(c, c->stats_dev, (PRT_MAX_DEPTH + 4) * 8))) return rc;
+    if (second_set) {
+        for (int k = 0; k < 2; ++k)
+            if ((rc = dev_reserve(c, c->q2_o[k], b16)) || (rc = dev_reserve(c, c->q2_d[k], b16)) ||
+                (rc = dev_reserve(c, c->q2_b[k], b16))) return rc;
+        if ((rc = dev_reserve(c, c->hits2, b16)) || (rc = dev_reserve(c, c->contrib2, b16))) return rc;
+        if ((rc = dev_reserve(c, c->qcount2, 2 * (PRT_MAX_DEPTH + 2) * 4))) return rc;
+        if (!c->stream2) {
+            PRT_CUDA(c, cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking));
+            for (cudaEvent_t* e : {&c->ev_res[0], &c->ev_res[1], &c->ev_join})
+                PRT_CUDA(c, cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+        }
+    }
     return PRT_OK;
 }
 
 int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_begin) {
     const int W = c->cam.width, H = c->cam.height;
     const int64_t P = (int64_t)W * H;
-    cudaStream_t st = c->stream;
-    int64_t cap = c->wave_paths_opt > 0 ? c->wave_paths_opt : (int64_t)32 << 20;
+    int64_t cap = c->wave_paths_opt > 0 ? c->wave_paths_opt : (int64_t)64 << 20;   // 64 Mi paths: 8.6 GB of queues per set
     cap = std::min<int64_t>(cap, (int64_t)1 << 26);                  // slot must fit 27 bits
     // wave = pixel range [p0, p0+npix) x S samples
     int64_t npix_wave = std::min<int64_t>(P, cap);
     int S_wave = (int)std::max<int64_t>(1, std::min<int64_t>(spp, cap / npix_wave));
+    const int64_t n_waves = ((spp + S_wave - 1) / S_wave) * ((P + npix_wave - 1) / npix_wave);
+    const int nsets = (c->overlap && n_waves > 1) ? 2 : 1;           // two waves in flight on two streams
     int rc;
-    if ((rc = ensure_wave_buffers(c, npix_wave * S_wave))) return rc;
+    if ((rc = ensure_wave_buffers(c, npix_wave * S_wave, nsets > 1))) return rc;
     c->wave_paths = npix_wave * S_wave;
+    cudaStream_t sts[2] = {c->stream, nsets > 1 ? c->stream2 : c->stream};
 
     SceneView sc = scene_view(c);
     CamView cam = cam_view(c->cam);
-    uint32_t* qcount = (uint32_t*)c->qcount.p;
     unsigned long long* dstats = (unsigned long long*)c->stats_dev.p;
     const bool brute = c->n_tris == 0 && c->n_prims <= c->brute_max_prims;   // fused kernels only
     sc.brute = brute ? 1 : 0;
@@ -623,49 +636,55 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
     // per-stage device timing: pooled events, one pair per kernel of the two hot stages
     size_t ev_used = 0;
     std::vector<std::pair<size_t, int>> spans;                       // (first event index, stage)
-    auto stamp = [&]() -> size_t {
+    auto stamp = [&](cudaStream_t s) -> size_t {
         if (ev_used == c->ev_pool.size()) { cudaEvent_t e; cudaEventCreate(&e); c->ev_pool.push_back(e); }
-        cudaEventRecord(c->ev_pool[ev_used], st);
+        cudaEventRecord(c->ev_pool[ev_used], s);
         return ev_used++;
     };
 
-    PRT_CUDA(c, cudaMemsetAsync(dstats, 0, (PRT_MAX_DEPTH + 4) * 8, st));
-    PRT_CUDA(c, cudaEventRecord(c->ev0, st));
+    PRT_CUDA(c, cudaMemsetAsync(dstats, 0, (PRT_MAX_DEPTH + 4) * 8, c->stream));
+    PRT_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    if (nsets > 1) PRT_CUDA(c, cudaStreamWaitEvent(c->stream2, c->ev0, 0));
     int launches = 0;
     uint64_t paths = 0;
+    int64_t wave = 0;
     for (int s0 = 0; s0 < spp; s0 += S_wave) {
         const int S = std::min(S_wave, spp - s0);
-        for (int64_t p0 = 0; p0 < P; p0 += npix_wave) {
+        for (int64_t p0 = 0; p0 < P; p0 += npix_wave, ++wave) {
+            const int set = (int)(wave % nsets);
+            cudaStream_t st = sts[set];
             const int npix = (int)std::min<int64_t>(npix_wave, P - p0);
             const int n_paths = npix * S;
             const FastDiv div_npix = make_fastdiv((uint32_t)npix);
             paths += (uint64_t)n_paths;
+            uint32_t* qcount = (uint32_t*)(set ? c->qcount2.p : c->qcount.p);
             PRT_CUDA(c, cudaMemsetAsync(qcount, 0, 2 * (PRT_MAX_DEPTH + 2) * 4, st));
             const int grid = (int)std::min<int64_t>(grid_p, (n_paths + WF_THREADS - 1) / WF_THREADS);
-            float4 *qo[2] = {(float4*)c->q_o[0].p, (float4*)c->q_o[1].p}, *qd[2] = {(float4*)c->q_d[0].p, (float4*)c->q_d[1].p},
-                   *qb[2] = {(float4*)c->q_b[0].p, (float4*)c->q_b[1].p};
-            float4 *hits = (float4*)c->hits.p, *contrib = (float4*)c->contrib.p;
+            DevBuf *bo = set ? c->q2_o : c->q_o, *bd = set ? c->q2_d : c->q_d, *bb = set ? c->q2_b : c->q_b;
+            float4 *qo[2] = {(float4*)bo[0].p, (float4*)bo[1].p}, *qd[2] = {(float4*)bd[0].p, (float4*)bd[1].p},
+                   *qb[2] = {(float4*)bb[0].p, (float4*)bb[1].p};
+            float4 *hits = (float4*)(set ? c->hits2.p : c->hits.p), *contrib = (float4*)(set ? c->contrib2.p : c->contrib.p);
             int cur = 0;
             if (fused) {
-                if (timing) spans.push_back({stamp(), 2});
+                if (timing) spans.push_back({stamp(st), 2});
                 {
                     auto kp = c->counters_on ? (brute ? k_primary<true, true> : k_primary<true, false>)
                                              : (brute ? k_primary<false, true> : k_primary<false, false>);
                     kp<<<grid, WF_THREADS, 0, st>>>(sc, cam, (int)p0, npix, div_npix, n_paths, (uint32_t)(sample_begin + s0), seed_lo,
                                                     seed_hi, qo[1], qd[1], qb[1], contrib, qcount, max_depth, dstats);
                 }
-                if (timing) stamp();
+                if (timing) stamp(st);
                 ++launches;
                 cur = 1;
                 for (int b = 1; b < max_depth; ++b) {
-                    if (timing) spans.push_back({stamp(), 0});
+                    if (timing) spans.push_back({stamp(st), 0});
                     {
                         auto kb = c->counters_on ? (brute ? k_bounce<true, true> : k_bounce<true, false>)
                                                  : (brute ? k_bounce<false, true> : k_bounce<false, false>);
                         kb<<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], qb[cur], qo[cur ^ 1], qd[cur ^ 1], qb[cur ^ 1],
                                                         contrib, qcount, b, max_depth, dstats);
                     }
-                    if (timing) stamp();
+                    if (timing) stamp(st);
                     ++launches;
                     cur ^= 1;
                 }
@@ -674,25 +693,33 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
                     cam, (int)p0, npix, div_npix, n_paths, (uint32_t)(sample_begin + s0), seed_lo, seed_hi, qo[0], qd[0], qb[0], qcount);
                 ++launches;
                 for (int b = 0; b < max_depth; ++b) {
-                    if (timing) spans.push_back({stamp(), b == 0 ? 2 : 0});
+                    if (timing) spans.push_back({stamp(st), b == 0 ? 2 : 0});
                     if (c->persistent) {
                         uint32_t* work = qcount + (PRT_MAX_DEPTH + 2) + b;
                         if (c->counters_on) k_extend_pt<true><<<grid_pt, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], hits, qcount, work, b, c->pt_refill, dstats);
                         else k_extend_pt<false><<<grid_pt, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], hits, qcount, work, b, c->pt_refill, dstats);
                     } else if (c->counters_on) k_extend<true><<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], hits, qcount, b, dstats);
                     else k_extend<false><<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], hits, qcount, b, dstats);
-                    if (timing) spans.push_back({stamp(), 1});
+                    if (timing) spans.push_back({stamp(st), 1});
                     k_shade<<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], qb[cur], hits, qo[cur ^ 1], qd[cur ^ 1], qb[cur ^ 1],
                                                          contrib, qcount, b, max_depth);
-                    if (timing) stamp();
+                    if (timing) stamp(st);
                     launches += 2;
                     cur ^= 1;
                 }
             }
+            // resolves read-modify-write the same accumulation pixels: keep them in wave order across the two streams
+            if (nsets > 1 && wave > 0) PRT_CUDA(c, cudaStreamWaitEvent(st, c->ev_res[(wave - 1) & 1], 0));
             k_resolve<<<(npix + WF_THREADS - 1) / WF_THREADS, WF_THREADS, 0, st>>>(contrib, (int)p0, npix, S, c->accum);
+            if (nsets > 1) PRT_CUDA(c, cudaEventRecord(c->ev_res[wave & 1], st));
             ++launches;
         }
     }
+    if (nsets > 1) {
+        PRT_CUDA(c, cudaEventRecord(c->ev_join, c->stream2));
+        PRT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_join, 0));
+    }
+    cudaStream_t st = c->stream;
     PRT_CUDA(c, cudaEventRecord(c->ev1, st));
     PRT_CUDA(c, cudaStreamSynchronize(st));
     PRT_CUDA(c, cudaGetLastError());
@@ -715,6 +742,7 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
         ms[sp.second] += a;
         if (sp.second == 2) ++n_primary;
     }
+    // with two waves in flight the per-kernel spans of the two streams overlap in time: their sum can exceed render_ms
     s.extend_ms = ms[0] + ms[2]; s.shade_ms = ms[1]; s.primary_ms = ms[2]; s.primary_launches = n_primary;
     s.n_prims = c->n_prims; s.n_nodes = c->n_prims > 1 ? c->n_prims - 1 : 0;
     return PRT_OK;

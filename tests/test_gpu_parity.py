@@ -168,9 +168,11 @@ def test_sample_ranges_compose(ctx, gold):
     ctx.clear_accum(); ctx.render(2, 8, seed=3, sample_begin=0); ctx.render(4, 8, seed=3, sample_begin=2); b = ctx.read_accum()
     assert np.array_equal(a, b) and ctx.accum_spp() == 6
     ctx.set_option("wave_paths", 7000)                 # forces pixel-range waves with ragged tails
-    ctx.clear_accum(); ctx.render(6, 8, seed=3); c = ctx.read_accum()
-    ctx.set_option("wave_paths", 0)
-    assert np.array_equal(a, c)
+    ctx.clear_accum(); ctx.render(6, 8, seed=3); c = ctx.read_accum()          # many waves, two in flight on two streams
+    ctx.set_option("overlap", 0)
+    ctx.clear_accum(); ctx.render(6, 8, seed=3); d = ctx.read_accum()          # same waves, one stream
+    ctx.set_option("overlap", 1); ctx.set_option("wave_paths", 0)
+    assert np.array_equal(a, c) and np.array_equal(a, d)
 
 
 def test_staged_pipeline_equals_fused(ctx, gold):

@@ -201,7 +201,9 @@ int  prt_resolve_display(prt_ctx* ctx, float exposure, float gamma, uint8_t* hos
 
 /* ---- parity / introspection --------------------------------------------------------
  * Closest hit for a fixed ray batch (host buffers). use_bvh=0 brute-forces all
- * primitives on the GPU (the reference's own algorithm, primitive.cpp:21-59). */
+ * primitives on the GPU (the reference's own algorithm, primitive.cpp:21-59); 1 walks the
+ * two-child LBVH (node/leaf counters comparable with the CPU oracle); 2 walks the 4-wide
+ * quantised nodes the render path uses (same hits, fewer node visits). */
 int  prt_trace_batch(prt_ctx* ctx, const prt_ray* rays, int n, prt_hit* out, int use_bvh);
 
 /* LBVH internals for the bit-exact integer checks. Any pointer may be NULL.

@@ -185,7 +185,7 @@ class Context:
     def trace_batch(self, rays, use_bvh=True):
         rays = np.ascontiguousarray(rays, dtype=ray_dt)
         out = np.zeros(len(rays), dtype=hit_dt)
-        self._check(self.lib.prt_trace_batch(self.h, _ptr(rays), len(rays), _ptr(out), 1 if use_bvh else 0), "prt_trace_batch")
+        self._check(self.lib.prt_trace_batch(self.h, _ptr(rays), len(rays), _ptr(out), int(use_bvh)), "prt_trace_batch")
         return out
 
     def num_prims(self):

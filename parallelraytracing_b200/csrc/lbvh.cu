@@ -300,10 +300,75 @@ __global__ void k_gather_tris(int n, int ns, int nq, int tri_prim_base, const ui
     out_n[3 * pos] = in_n[3 * t]; out_n[3 * pos + 1] = in_n[3 * t + 1]; out_n[3 * pos + 2] = in_n[3 * t + 2];
 }
 
+// ------------------------------------------------------------------ 4-wide quantised nodes
+// Collapse the two-child tree by grandchildren: every internal node at EVEN depth becomes a wide node whose
+// slots are its children's children (a leaf child keeps its own slot), 2..4 slots. Wide nodes live at the
+// index of the binary node they replace (odd-depth entries stay unused), so child codes need no remapping
+// and the root is still node 0. Depth comes from walking the parent chain (<= tree height steps).
+__device__ __forceinline__ float pow2_ceil_scale(float ext) {
+    // smallest power of two s with ext / s <= 254 (room for the 2^-6 margin and the ceil); >= 2^-60
+    float s = 8.673617379884035e-19f;                                  // 2^-60
+    if (ext > 0.0f) {
+        int e; frexpf(ext * (1.0f / 254.0f), &e);                      // ext/254 = m * 2^e, m in [0.5, 1)  ->  2^e >= ext/254
+        e = e < -60 ? -60 : e;
+        s = ldexpf(1.0f, e);
+    }
+    return s;
+}
+
+__global__ void k_emit_wide(int n_internal, const int* __restrict__ parent, const BvhNode* __restrict__ nodes,
+                            WideNode* __restrict__ wide) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_internal) return;
+    int depth = 0;
+    for (int p = parent[i]; p >= 0; p = parent[p]) ++depth;
+    if (depth & 1) return;
+    float lo[4][3], hi[4][3]; int code[4]; int ns = 0;
+    BvhNode nd = nodes[i];
+    const int cc[2] = {__float_as_int(nd.lmin.w), __float_as_int(nd.lmax.w)};
+    const float4 bmin[2] = {nd.lmin, nd.rmin}, bmax[2] = {nd.lmax, nd.rmax};
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        if (cc[k] < 0) {
+            lo[ns][0] = bmin[k].x; lo[ns][1] = bmin[k].y; lo[ns][2] = bmin[k].z;
+            hi[ns][0] = bmax[k].x; hi[ns][1] = bmax[k].y; hi[ns][2] = bmax[k].z; code[ns++] = cc[k];
+        } else {
+            BvhNode ch = nodes[cc[k]];
+            lo[ns][0] = ch.lmin.x; lo[ns][1] = ch.lmin.y; lo[ns][2] = ch.lmin.z;
+            hi[ns][0] = ch.lmax.x; hi[ns][1] = ch.lmax.y; hi[ns][2] = ch.lmax.z; code[ns++] = __float_as_int(ch.lmin.w);
+            lo[ns][0] = ch.rmin.x; lo[ns][1] = ch.rmin.y; lo[ns][2] = ch.rmin.z;
+            hi[ns][0] = ch.rmax.x; hi[ns][1] = ch.rmax.y; hi[ns][2] = ch.rmax.z; code[ns++] = __float_as_int(ch.lmax.w);
+        }
+    }
+    WideNode w;
+    float org[3], sc[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        float mn = lo[0][k], mx = hi[0][k];
+        for (int c = 1; c < ns; ++c) { mn = fminf(mn, lo[c][k]); mx = fmaxf(mx, hi[c][k]); }
+        org[k] = mn; sc[k] = pow2_ceil_scale(mx - mn);
+        uint32_t ql = 0, qh = 0;
+        for (int c = 0; c < 4; ++c) {
+            uint32_t a = 255u, b = 0u;                                  // empty slot: inverted box
+            if (c < ns) {
+                float fl = floorf((lo[c][k] - mn) / sc[k] - 0.015625f), fh = ceilf((hi[c][k] - mn) / sc[k] + 0.015625f);
+                a = (uint32_t)fminf(fmaxf(fl, 0.0f), 255.0f); b = (uint32_t)fminf(fmaxf(fh, 0.0f), 255.0f);
+            }
+            ql |= a << (8 * c); qh |= b << (8 * c);
+        }
+        w.qlo[k] = ql; w.qhi[k] = qh;
+    }
+    w.ox = org[0]; w.oy = org[1]; w.oz = org[2];
+    w.sx = sc[0] * 32768.0f; w.sy = sc[1] * 32768.0f; w.sz = sc[2] * 32768.0f;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) w.code[c] = c < ns ? code[c] : code[0];
+    wide[i] = w;
+}
+
 // ------------------------------------------------------------------ host driver
 int lbvh_build(Ctx* c) {
     const int n = c->n_prims, ns = c->n_spheres, nq = c->n_quads, nt = c->n_tris;
-    c->bvh_built = false;
+    c->bvh_built = false; c->wide_built = false;
     cudaStream_t st = c->stream;
     int rc;
     if ((rc = dev_reserve(c, c->scene_bounds, 6 * sizeof(int)))) return rc;
@@ -357,6 +422,11 @@ int lbvh_build(Ctx* c) {
         k_refit<<<G, T, 0, st>>>(n, sprim, (const float4*)c->aabb_min.p, (const float4*)c->aabb_max.p,
                                  (const int*)c->children.p, parent, leaf_parent,
                                  (float4*)c->node_min.p, (float4*)c->node_max.p, (int*)c->flags.p, ns, nq, (BvhNode*)c->nodes.p);
+        if (c->bvh_wide > 0 || (c->bvh_wide < 0 && n >= c->wide_min_prims)) {
+            if ((rc = dev_reserve(c, c->wnodes, nn * sizeof(WideNode)))) return rc;
+            k_emit_wide<<<G, T, 0, st>>>(n - 1, parent, (const BvhNode*)c->nodes.p, (WideNode*)c->wnodes.p);
+            c->wide_built = true;
+        }
         c->root_code = 0;
     } else {
         // single primitive: the root IS the leaf

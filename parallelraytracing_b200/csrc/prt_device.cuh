@@ -109,6 +109,20 @@ struct QuadRec   { float4 a, b, c, d; };            // a={c.xyz,hw} b={u.xyz,hh}
 struct MatRec    { float4 a; float4 b; };           // a={r,g,b,param} b={bits(type),0,0,0}
 struct BvhNode   { float4 lmin, lmax, rmin, rmax; };// .w of lmin/lmax = bits(left/right child code)
 
+// 4-wide node with child boxes quantised to 8 bits on a per-node grid (64 bytes, two 256-bit loads for FOUR
+// children; the two-child node above costs the same two loads for two). Child c's box on axis k is
+//   [origin_k + qlo_k[c]*s_k , origin_k + qhi_k[c]*s_k],  s_k = scale_k * 2^-15 (a power of two),
+// a superset of the true box by at least 2^-6 grid steps (the builder floors/ceils with that margin), which
+// pays for the rounding of the fused decode in the traversal. Empty slots: qlo 255, qhi 0 (an inverted box, never entered) and, as a
+// belt-and-braces default, the code of slot 0 (entering it would repeat work, never change a result).
+struct WideNode {
+    float ox, oy, oz, sx;          // origin, scale_x = 2^(e_x + 15)
+    int   code[4];                 // same coding as BvhNode children
+    uint32_t qlo[3], qhi[3];       // byte c of qlo[k] = child c, axis k
+    float sy, sz;
+};
+#define PRT_EMPTY ((int)0x80000000)
+
 // child / hit code: >= 0 internal node index; < 0 leaf, ~code = (shape_type << 28) | index
 #define PRT_LEAF_TYPE(c)  ((uint32_t)(c) >> 28)
 #define PRT_LEAF_INDEX(c) ((uint32_t)(c) & 0x0fffffffu)
@@ -124,9 +138,11 @@ struct SceneView {
     const MatRec*    mats;     int n_mats;
     const int*       quad_mat; // material per quad (quads' own record is full)
     const BvhNode*   nodes;    int n_prims;
+    const WideNode*  wnodes;   // 4-wide quantised nodes, indexed like `nodes` (only even-depth entries exist); NULL = none
     int              root_code; // root: 0 if n_prims>1, leaf code (negative-as-~) if n_prims==1
     float            tri_tmin;
     float sky_r, sky_g, sky_b;
+    uint32_t         one_bits; // 0x3f800000, read from the constant bank so that PRMT keeps its selector as the immediate
     int              brute;    // tiny sphere/quad scene: test every primitive in list order, no BVH (see traverse())
 };
 

@@ -35,6 +35,10 @@ struct Ctx {
     DevBuf block_hist;                          // digit-major per-block histograms
     DevBuf children, parent, node_min, node_max, flags;
     DevBuf nodes;                               // BvhNode per internal node
+    DevBuf wnodes;                              // WideNode at the index of every even-depth internal node
+    int bvh_wide = -1;                          // 4-wide quantised nodes for the staged extend: 1 always, 0 never, -1 by scene size
+    int wide_min_prims = 4096;                  // auto: below this the two-child tree is L1-resident and its cheaper node step wins
+    bool wide_built = false;
     DevBuf tri_v, tri_n;                        // leaf-slot order (3 float4 per slot)
     DevBuf morton;                              // per q (kept for prt_debug_lbvh)
     int sorted_slot = 0;                        // which of keys/vals holds the sorted result

@@ -185,7 +185,7 @@ k_extend_pt(SceneView sc, const float4* __restrict__ qo, const float4* __restric
                     if (sc.n_tris > 0) rs = make_shear(d);
                     dn = sc.n_spheres > 0 ? normalize(d) : d;
                     best_init(best);
-                    cur = sc.root_code; sp = 0; have = true;
+                    cur = sc.root_code; st[0] = PRT_DONE; sp = 1; have = true;
                 }
             }
             exhausted = base + (uint32_t)__popc(idle) >= count;
@@ -206,23 +206,159 @@ k_extend_pt(SceneView sc, const float4* __restrict__ qo, const float4* __restric
                     const bool hl = tl >= 0.0f, hr = tr >= 0.0f;
                     const bool right_first = hr && (!hl || tr < tl);
                     const int nearc = right_first ? cr : cl, farc = right_first ? cl : cr;
-                    if (hl && hr) {
-                        if (sp < STACK_SMEM) st[sp * WF_THREADS] = farc; else lstack[sp - STACK_SMEM] = farc;
-                        ++sp;
+                    // Push and pop without divergent branches (ncu: as `if (both) push ... else pop` they were 18 % of the
+                    // kernel's warp instructions at 3-4 active lanes). Entry 0 of the stack is a PRT_DONE sentinel, so a
+                    // pop never tests for "empty"; the store is predicated and the entry below the top is always read.
+                    const bool push = hl && hr, any = hl || hr;
+                    if (sp < STACK_SMEM) {
+                        int* top = st + sp * WF_THREADS;
+                        if (push) *top = farc;
+                        const int below = top[-WF_THREADS];
+                        cur = any ? nearc : below;
+                        sp += push ? 1 : (any ? 0 : -1);
+                    } else {                                             // deep stack (rare): spill entries live in local memory
+                        if (push) { lstack[sp - STACK_SMEM] = farc; ++sp; }
+                        if (any) cur = nearc;
+                        else { --sp; cur = sp < STACK_SMEM ? st[sp * WF_THREADS] : lstack[sp - STACK_SMEM]; }
                     }
-                    if (hl || hr) cur = nearc;
-                    else if (sp == 0) cur = PRT_DONE;
-                    else { --sp; cur = sp < STACK_SMEM ? st[sp * WF_THREADS] : lstack[sp - STACK_SMEM]; }
                     if (__popc(__activemask()) < thresh) break;        // lanes drained away (finished or at a leaf)
                 }
                 if (cur < 0 && cur != PRT_DONE) {                      // postponed leaf
                     if (COUNT) ++np;
                     test_leaf(sc, (uint32_t)~cur, o, d, dn, rs, best);
-                    if (sp == 0) cur = PRT_DONE;
-                    else { --sp; cur = sp < STACK_SMEM ? st[sp * WF_THREADS] : lstack[sp - STACK_SMEM]; }
+                    --sp; cur = sp < STACK_SMEM ? st[sp * WF_THREADS] : lstack[sp - STACK_SMEM];
                 }
                 if (cur == PRT_DONE) break;
                 if (__popc(__activemask()) < thresh) break;            // too few lanes left: go refill
+            }
+            if (cur == PRT_DONE) {
+                st_stream(&hits[idx], make_float4(best.t, __uint_as_float(best.code), best.u, best.v));
+                have = false;
+            }
+        }
+    }
+    if (COUNT) {
+        for (int k = 16; k > 0; k >>= 1) { nn += __shfl_xor_sync(0xffffffffu, nn, k); np += __shfl_xor_sync(0xffffffffu, np, k); }
+        if (lane == 0 && (nn | np)) {
+            atomicAdd(&stats[PRT_MAX_DEPTH + 0], (unsigned long long)nn);
+            atomicAdd(&stats[PRT_MAX_DEPTH + 1], (unsigned long long)np);
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&stats[bounce], (unsigned long long)count);
+}
+
+// Persistent-thread extend over the 4-wide quantised nodes (WideNode, prt_device.cuh). Same skeleton as
+// k_extend_pt; per node: two 256-bit loads, then for each of the 4 children 6 x (PRMT + FFMA) slab planes.
+// Decode: byte q -> g = 1 + q*2^-15 (PRMT into the mantissa of 1.0f), plane t = g*Bp + (A - Bp) with
+// Bp = scale*inv = 2^15 * step*inv and A = (origin - o)*inv, i.e. A + q*step*inv in one FFMA. Conservative:
+// A is widened by 2^-22 |A| (its two roundings), the quantised box has a 2^-6-step margin (rounding of
+// A - Bp is <= 2^-9 step) and the far side gets the same 1+2^-21 factor as the two-child test. The closest hit
+// does not depend on any of this (order-free (t, prim_id) rule), only the node count does.
+template <bool COUNT>
+__global__ void __launch_bounds__(WF_THREADS)
+k_extend_wide(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ qd, float4* __restrict__ hits,
+              const uint32_t* __restrict__ qcount, uint32_t* __restrict__ work, int bounce, int refill,
+              unsigned long long* __restrict__ stats) {
+    __shared__ int sstack[STACK_SMEM * WF_THREADS];
+    const uint32_t count = qcount[bounce];
+    const uint32_t lane = threadIdx.x & 31u;
+    int* __restrict__ st = sstack + threadIdx.x;
+    int lstack[STACK_LOCAL];
+    uint32_t nn = 0, np = 0;
+    bool have = false, exhausted = false;
+    uint32_t idx = 0; V3 o = mk(0, 0, 0), d = o, dn = o, inv = o; RayShear rs; Best best; int cur = PRT_DONE, sp = 0;
+    rs.kx = 0; rs.ky = 1; rs.kz = 2; rs.sx = rs.sy = rs.sz = 0.f; best_init(best);
+    while (!exhausted || __any_sync(0xffffffffu, have)) {
+        uint32_t idle = __ballot_sync(0xffffffffu, !have);
+        if (idle && !exhausted) {
+            int leader = __ffs(idle) - 1;
+            uint32_t base = 0;
+            if ((int)lane == leader) base = atomicAdd(work, (uint32_t)__popc(idle));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (!have) {
+                idx = base + __popc(idle & ((1u << lane) - 1u));
+                if (idx < count) {
+                    float4 o4 = ld_stream(&qo[idx]), d4 = ld_stream(&qd[idx]);
+                    o = xyz(o4); d = xyz(d4);
+                    inv = mk(safe_inv(d.x), safe_inv(d.y), safe_inv(d.z));
+                    if (sc.n_tris > 0) rs = make_shear(d);
+                    dn = sc.n_spheres > 0 ? normalize(d) : d;
+                    best_init(best);
+                    cur = sc.root_code; st[0] = PRT_DONE; sp = 1; have = true;
+                }
+            }
+            exhausted = base + (uint32_t)__popc(idle) >= count;
+        }
+        if (have) {
+            const int thresh = exhausted ? 0 : refill;
+            const bool nx = inv.x < 0.0f, ny = inv.y < 0.0f, nz = inv.z < 0.0f;
+            for (;;) {
+                while (cur >= 0) {
+                    const WideNode* nd = sc.wnodes + cur;
+                    float4 a0, a1, b0, b1;
+                    ldg8(nd, a0, a1); ldg8(reinterpret_cast<const char*>(nd) + 32, b0, b1);
+                    if (COUNT) ++nn;
+                    const float Bx = a0.w * inv.x, By = b1.z * inv.y, Bz = b1.w * inv.z;
+                    const float Ax = (a0.x - o.x) * inv.x, Ay = (a0.y - o.y) * inv.y, Az = (a0.z - o.z) * inv.z;
+                    const float e = 2.384185791015625e-07f;                                        // 2^-22
+                    const float nAx = fmaf(-fabsf(Ax), e, Ax) - Bx, fAx = fmaf(fabsf(Ax), e, Ax) - Bx;
+                    const float nAy = fmaf(-fabsf(Ay), e, Ay) - By, fAy = fmaf(fabsf(Ay), e, Ay) - By;
+                    const float nAz = fmaf(-fabsf(Az), e, Az) - Bz, fAz = fmaf(fabsf(Az), e, Az) - Bz;
+                    const uint32_t lx = __float_as_uint(b0.x), ly = __float_as_uint(b0.y), lz = __float_as_uint(b0.z);
+                    const uint32_t hx = __float_as_uint(b0.w), hy = __float_as_uint(b1.x), hz = __float_as_uint(b1.y);
+                    const uint32_t wnx = nx ? hx : lx, wfx = nx ? lx : hx;
+                    const uint32_t wny = ny ? hy : ly, wfy = ny ? ly : hy;
+                    const uint32_t wnz = nz ? hz : lz, wfz = nz ? lz : hz;
+                    const int cc[4] = {__float_as_int(a1.x), __float_as_int(a1.y), __float_as_int(a1.z), __float_as_int(a1.w)};
+                    uint32_t key[4]; bool hit[4];
+                    const uint32_t one = sc.one_bits;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const uint32_t selb = 0x7604u | ((uint32_t)k << 4);        // bytes: [b.0, a.k, b.2, b.3] of (a = word, b = 1.0f)
+                        const float gnx = __uint_as_float(__byte_perm(wnx, one, selb));
+                        const float gny = __uint_as_float(__byte_perm(wny, one, selb));
+                        const float gnz = __uint_as_float(__byte_perm(wnz, one, selb));
+                        const float gfx = __uint_as_float(__byte_perm(wfx, one, selb));
+                        const float gfy = __uint_as_float(__byte_perm(wfy, one, selb));
+                        const float gfz = __uint_as_float(__byte_perm(wfz, one, selb));
+                        float tn = fmaxf(fmaxf(fmaf(gnx, Bx, nAx), fmaf(gny, By, nAy)), fmaxf(fmaf(gnz, Bz, nAz), 0.0f));
+                        float tf = fminf(fminf(fmaf(gfx, Bx, fAx), fmaf(gfy, By, fAy)), fminf(fmaf(gfz, Bz, fAz), best.t));
+                        tf = tf * 1.00000047683715820312f;
+                        hit[k] = tn <= tf;
+                        key[k] = hit[k] ? ((__float_as_uint(tn) & ~3u) | (uint32_t)k) : 0xffffffffu;   // tn >= 0: bits order like ints
+                    }
+                    const uint32_t kmin = min(min(key[0], key[1]), min(key[2], key[3]));
+                    const bool any = kmin != 0xffffffffu;
+                    const int near = (int)(kmin & 3u);
+                    int nearc = cc[3];
+                    nearc = key[2] == kmin ? cc[2] : nearc; nearc = key[1] == kmin ? cc[1] : nearc; nearc = key[0] == kmin ? cc[0] : nearc;
+                    if (sp <= STACK_SMEM - 3) {                      // common case: predicated pushes, sentinel-terminated pop
+                        int t = sp;
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            if (hit[k] && key[k] > kmin) { st[t * WF_THREADS] = cc[k]; ++t; }   // every hit child but the nearest
+                        const int below = st[(t - 1) * WF_THREADS];
+                        sp = t - (any ? 0 : 1);
+                        cur = any ? nearc : below;
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            if (key[k] != 0xffffffffu && k != near) {
+                                if (sp < STACK_SMEM) st[sp * WF_THREADS] = cc[k]; else lstack[sp - STACK_SMEM] = cc[k];
+                                ++sp;
+                            }
+                        if (any) cur = nearc;
+                        else { --sp; cur = sp < STACK_SMEM ? st[sp * WF_THREADS] : lstack[sp - STACK_SMEM]; }
+                    }
+                    if (__popc(__activemask()) < thresh) break;
+                }
+                if (cur < 0 && cur != PRT_DONE) {
+                    if (COUNT) ++np;
+                    test_leaf(sc, (uint32_t)~cur, o, d, dn, rs, best);
+                    --sp; cur = sp < STACK_SMEM ? st[sp * WF_THREADS] : lstack[sp - STACK_SMEM];
+                }
+                if (cur == PRT_DONE) break;
+                if (__popc(__activemask()) < thresh) break;
             }
             if (cur == PRT_DONE) {
                 st_stream(&hits[idx], make_float4(best.t, __uint_as_float(best.code), best.u, best.v));
@@ -556,9 +692,11 @@ SceneView scene_view(const Ctx* c) {
     v.mats = (const MatRec*)c->mats.p; v.n_mats = c->n_mats;
     v.quad_mat = (const int*)c->quad_mat.p;
     v.nodes = (const BvhNode*)c->nodes.p; v.n_prims = c->n_prims;
+    v.wnodes = c->wide_built ? (const WideNode*)c->wnodes.p : nullptr;
     v.root_code = c->root_code;
     v.tri_tmin = 0.001f;                                  // kShapeRayTMin, shape.h:128
     v.sky_r = c->sky[0]; v.sky_g = c->sky[1]; v.sky_b = c->sky[2];
+    v.one_bits = 0x3f800000u;
     v.brute = 0;                                          // only wavefront_render's fused path turns it on
     return v;
 }
@@ -625,11 +763,13 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
     const uint32_t seed_lo = (uint32_t)seed, seed_hi = (uint32_t)(seed >> 32);
     const bool fused = c->fused < 0 ? (c->n_prims <= c->fused_max_prims) : (c->fused != 0);
     const bool timing = c->stage_timing != 0;
+    const bool wide = sc.wnodes != nullptr && c->n_prims > 1;          // staged extend walks the 4-wide quantised nodes
+    auto k_ext = wide ? (c->counters_on ? k_extend_wide<true> : k_extend_wide<false>)
+                      : (c->counters_on ? k_extend_pt<true> : k_extend_pt<false>);
     int grid_pt = grid_p;
     {   // persistent extend: exactly the CTAs that are resident at once
         int per_sm = 0;
-        cudaError_t e = c->counters_on ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_extend_pt<true>, WF_THREADS, 0)
-                                       : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_extend_pt<false>, WF_THREADS, 0);
+        cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ext, WF_THREADS, 0);
         if (e == cudaSuccess && per_sm > 0) grid_pt = c->num_sms * per_sm;
     }
 
@@ -696,8 +836,7 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
                     if (timing) spans.push_back({stamp(st), b == 0 ? 2 : 0});
                     if (c->persistent) {
                         uint32_t* work = qcount + (PRT_MAX_DEPTH + 2) + b;
-                        if (c->counters_on) k_extend_pt<true><<<grid_pt, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], hits, qcount, work, b, c->pt_refill, dstats);
-                        else k_extend_pt<false><<<grid_pt, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], hits, qcount, work, b, c->pt_refill, dstats);
+                        k_ext<<<grid_pt, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], hits, qcount, work, b, c->pt_refill, dstats);
                     } else if (c->counters_on) k_extend<true><<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], hits, qcount, b, dstats);
                     else k_extend<false><<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], hits, qcount, b, dstats);
                     if (timing) spans.push_back({stamp(st), 1});
@@ -766,7 +905,14 @@ int wavefront_trace_batch(Ctx* c, const prt_ray* rays, int n, prt_hit* out, int 
     const int G = (n + WF_THREADS - 1) / WF_THREADS;
     k_load_rays<<<G, WF_THREADS, 0, st>>>((const prt_ray*)d_rays.p, n, (float4*)c->q_o[0].p, (float4*)c->q_d[0].p, qcount);
     const int grid = std::min(G, c->num_sms * c->ctas_per_sm);
-    if (use_bvh && c->persistent) {
+    if (use_bvh == 2 && sc.wnodes != nullptr && c->n_prims > 1) {      // the 4-wide quantised nodes
+        uint32_t* work = qcount + (PRT_MAX_DEPTH + 2);
+        auto k = c->counters_on ? k_extend_wide<true> : k_extend_wide<false>;
+        int per_sm = 4;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, WF_THREADS, 0);
+        k<<<std::max(1, c->num_sms * std::max(1, per_sm)), WF_THREADS, 0, st>>>(sc, (const float4*)c->q_o[0].p, (const float4*)c->q_d[0].p,
+                                                                                (float4*)c->hits.p, qcount, work, 0, c->pt_refill, dstats);
+    } else if (use_bvh && c->persistent) {
         uint32_t* work = qcount + (PRT_MAX_DEPTH + 2);
         int per_sm = 4;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_extend_pt<false>, WF_THREADS, 0);

@@ -127,6 +127,41 @@ def test_closest_hit_vs_reference_vectors(ctx, gold, name):
     assert np.array_equal(ref_hits["front"][ok], got["front"][ok])
 
 
+@pytest.mark.parametrize("name", sorted(SCENES))
+def test_wide_nodes_equal_two_child_bvh(ctx, gold, name):
+    """The 4-wide quantised nodes (what the staged render path walks) return the same hit records, bit for bit,
+    as the two-child LBVH and as brute force, with fewer node visits; leaf tests may differ (other visit order)."""
+    sd = SCENES[name](gold)
+    ctx.set_option("bvh_wide", 1)                      # also for the small scenes that the auto policy leaves two-child
+    ctx.set_scene(sd); ctx.build_bvh()
+    ctx.set_option("bvh_wide", -1)
+    rays = util.fixed_ray_batch(sd, 65536, seed=11)
+    ctx.enable_counters(True)
+    two = ctx.trace_batch(rays, use_bvh=1); st2 = ctx.stats(); n2 = st2.nodes_visited
+    wide = ctx.trace_batch(rays, use_bvh=2); stw = ctx.stats(); nw = stw.nodes_visited
+    ctx.enable_counters(False)
+    for k in two.dtype.names:
+        assert np.array_equal(two[k], wide[k]), k
+    if sd.n_prims > 2:
+        assert 0 < nw < n2, (nw, n2)
+    if sd.n_prims <= 20000:
+        brute = ctx.trace_batch(rays, use_bvh=0)
+        assert np.array_equal(brute["prim_id"], wide["prim_id"]) and np.array_equal(brute["t"], wide["t"])
+
+
+def test_wide_nodes_off_renders_same_image(ctx, gold):
+    """bvh_wide=0 (two-child nodes only) and the default must give identical images and ray counts."""
+    sd = SCENES["dragon3"](gold); cam = S.Camera(pos=(0.0, 1.0, 5.0), front=S._normalize(S._v3(0, -1, -5)), width=96, height=64)
+    out = []
+    for widev in (1, 0):
+        ctx.set_option("bvh_wide", widev)
+        ctx.set_scene(sd); ctx.build_bvh(); ctx.set_camera(cam); ctx.clear_accum()
+        ctx.render(3, 8, seed=13)
+        out.append((ctx.read_accum(), list(ctx.stats().rays_per_bounce)))
+    ctx.set_option("bvh_wide", -1)
+    assert np.array_equal(out[0][0], out[1][0]) and out[0][1] == out[1][1]
+
+
 # ---------------------------------------------------------------- radiance
 @pytest.mark.parametrize("name,W,H,spp,depth", [("cornell", 128, 128, 8, 8), ("default", 96, 96, 4, 8),
                                                  ("random_balls_large", 96, 54, 4, 8), ("closed_cornell", 96, 96, 4, 8),

@@ -37,6 +37,7 @@ class Oracle:
         lib.po_num_prims.argtypes = [vp]
         lib.po_build_lbvh.argtypes = [vp]
         lib.po_get_lbvh.argtypes = [vp] * 7
+        lib.po_get_wide.argtypes = [vp, vp, vp]
         lib.po_trace_batch.argtypes = [vp, vp, i32, vp, i32, vp, i32]
         lib.po_camera_dirs.argtypes = [C.POINTER(CCamera), vp]
         lib.po_render.restype = u64
@@ -101,13 +102,21 @@ class OracleScene:
                              _ptr(d["node_parent"]), _ptr(d["node_bounds"]), _ptr(d["scene_bounds"]))
         return d
 
+    def get_wide(self):
+        """4-wide quantised nodes in the device layout: ((n-1, 16) uint32 words, (n-1,) valid = even depth)."""
+        self.build_lbvh()
+        ni = max(self.lib.po_num_prims(self.h) - 1, 0)
+        w, v = np.zeros((ni, 16), np.uint32), np.zeros(ni, np.uint8)
+        self.lib.po_get_wide(self.h, _ptr(w), _ptr(v))
+        return w, v.astype(bool)
+
     def trace_batch(self, rays, use_bvh=True, n_threads=8, counters=None):
         if use_bvh:
             self.build_lbvh()
         rays = np.ascontiguousarray(rays, ray_dt)
         out = np.zeros(len(rays), hit_dt)
         cnt = np.zeros(2, np.uint64)
-        self.lib.po_trace_batch(self.h, _ptr(rays), len(rays), _ptr(out), 1 if use_bvh else 0, _ptr(cnt), n_threads)
+        self.lib.po_trace_batch(self.h, _ptr(rays), len(rays), _ptr(out), int(use_bvh), _ptr(cnt), n_threads)
         if counters is not None:
             counters[:] = cnt
         return out

@@ -98,6 +98,9 @@ struct Scene {
     std::vector<uint32_t> morton, sorted_prim, sorted_key;
     std::vector<int> children, parent, leaf_parent;
     std::vector<V3> node_min, node_max;
+    struct WNode { float org[3], scale[3]; int code[4]; uint32_t qlo[3], qhi[3]; };   /* = device WideNode, 64 bytes of content */
+    std::vector<WNode> wide;            /* indexed like the internal nodes; only even-depth entries are meaningful */
+    std::vector<uint8_t> wide_valid;
     bool built = false;
     int n_prims() const { return (int)(spheres.size() + quads.size() + tris.size()); }
 };
@@ -371,6 +374,116 @@ Hit closest_bvh(const Scene& sc, V3 o, V3 d, uint64_t* n_nodes, uint64_t* n_test
     return h;
 }
 
+/* ---------------------------------------------------------------- 4-wide quantised nodes
+ * Restatement of k_emit_wide (parallelraytracing_b200/csrc/lbvh.cu): every internal node at even depth
+ * takes its children's children as 2..4 slots; child boxes are quantised to 8 bits on a per-node
+ * power-of-two grid, floor/ceil with a 2^-6-step margin. The reference has no counterpart (no BVH at all). */
+inline int dev_leaf_code(const Scene& sc, int pos) {
+    uint32_t q = sc.sorted_prim[pos], ns = (uint32_t)sc.spheres.size(), nq = (uint32_t)sc.quads.size();
+    uint32_t payload = q < ns ? q : q < ns + nq ? ((1u << 28) | (q - ns)) : ((2u << 28) | (uint32_t)pos);
+    return ~(int)payload;
+}
+inline float pow2_ceil_scale(float ext) {
+    float s = 8.673617379884035e-19f;                                   /* 2^-60 */
+    if (ext > 0.0f) { int e; frexpf(ext * (1.0f / 254.0f), &e); e = e < -60 ? -60 : e; s = ldexpf(1.0f, e); }
+    return s;
+}
+void build_wide(Scene& sc) {
+    int n = sc.n_prims(), ni = n > 1 ? n - 1 : 0;
+    sc.wide.assign(ni, Scene::WNode()); sc.wide_valid.assign(ni, 0);
+    for (int i = 0; i < ni; ++i) {
+        int depth = 0;
+        for (int p = sc.parent[i]; p >= 0; p = sc.parent[p]) ++depth;
+        if (depth & 1) continue;
+        V3 lo[4], hi[4]; int code[4]; int ns = 0;
+        for (int k = 0; k < 2; ++k) {
+            int ch = sc.children[2 * i + k];
+            if (ch < 0) { child_box(sc, ch, lo[ns], hi[ns]); code[ns++] = dev_leaf_code(sc, ~ch); }
+            else for (int g = 0; g < 2; ++g) {
+                int gc = sc.children[2 * ch + g];
+                child_box(sc, gc, lo[ns], hi[ns]); code[ns++] = gc < 0 ? dev_leaf_code(sc, ~gc) : gc;
+            }
+        }
+        Scene::WNode& w = sc.wide[i];
+        for (int k = 0; k < 3; ++k) {
+            float mn = comp(lo[0], k), mx = comp(hi[0], k);
+            for (int c = 1; c < ns; ++c) { mn = fminf(mn, comp(lo[c], k)); mx = fmaxf(mx, comp(hi[c], k)); }
+            float sc_k = pow2_ceil_scale(mx - mn);
+            uint32_t ql = 0, qh = 0;
+            for (int c = 0; c < 4; ++c) {
+                uint32_t a = 255u, b = 0u;
+                if (c < ns) {
+                    float fl = floorf((comp(lo[c], k) - mn) / sc_k - 0.015625f), fh = ceilf((comp(hi[c], k) - mn) / sc_k + 0.015625f);
+                    a = (uint32_t)fminf(fmaxf(fl, 0.0f), 255.0f); b = (uint32_t)fminf(fmaxf(fh, 0.0f), 255.0f);
+                }
+                ql |= a << (8 * c); qh |= b << (8 * c);
+            }
+            w.org[k] = mn; w.scale[k] = sc_k * 32768.0f; w.qlo[k] = ql; w.qhi[k] = qh;
+        }
+        for (int c = 0; c < 4; ++c) w.code[c] = c < ns ? code[c] : code[0];
+        sc.wide_valid[i] = 1;
+    }
+}
+
+inline float bits_f(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
+inline uint32_t f_bits(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
+
+/* Restatement of k_extend_wide's walk (wavefront.cu): same decode arithmetic (explicit fmaf, same order), nearest
+ * hit child next, the other hit children pushed in slot order; leaf codes are the device's. Counters comparable. */
+Hit closest_wide(const Scene& sc, V3 o, V3 d, uint64_t* n_nodes, uint64_t* n_tests) {
+    Hit h; hit_init(h);
+    int n = sc.n_prims();
+    if (n == 0) return h;
+    if (n == 1) return closest_bvh(sc, o, d, n_nodes, n_tests);
+    V3 inv = mk(safe_inv(d.x), safe_inv(d.y), safe_inv(d.z));
+    Shear rs = make_shear(d);
+    V3 dn = normalize(d);
+    const int ns = (int)sc.spheres.size();
+    std::vector<int> stack; stack.reserve(128);
+    const int DONE = (int)0x80000000;
+    int cur = 0;
+    const bool nx = inv.x < 0.0f, ny = inv.y < 0.0f, nz = inv.z < 0.0f;
+    const float e = 2.384185791015625e-07f;
+    for (;;) {
+        if (cur >= 0) {
+            if (n_nodes) ++*n_nodes;
+            const Scene::WNode& w = sc.wide[cur];
+            const float Bx = w.scale[0] * inv.x, By = w.scale[1] * inv.y, Bz = w.scale[2] * inv.z;
+            const float Ax = (w.org[0] - o.x) * inv.x, Ay = (w.org[1] - o.y) * inv.y, Az = (w.org[2] - o.z) * inv.z;
+            const float nAx = fmaf(-fabsf(Ax), e, Ax) - Bx, fAx = fmaf(fabsf(Ax), e, Ax) - Bx;
+            const float nAy = fmaf(-fabsf(Ay), e, Ay) - By, fAy = fmaf(fabsf(Ay), e, Ay) - By;
+            const float nAz = fmaf(-fabsf(Az), e, Az) - Bz, fAz = fmaf(fabsf(Az), e, Az) - Bz;
+            const uint32_t wnx = nx ? w.qhi[0] : w.qlo[0], wfx = nx ? w.qlo[0] : w.qhi[0];
+            const uint32_t wny = ny ? w.qhi[1] : w.qlo[1], wfy = ny ? w.qlo[1] : w.qhi[1];
+            const uint32_t wnz = nz ? w.qhi[2] : w.qlo[2], wfz = nz ? w.qlo[2] : w.qhi[2];
+            uint32_t key[4]; bool hit[4];
+            for (int k = 0; k < 4; ++k) {
+                auto g = [&](uint32_t word) { return bits_f(0x3f800000u | (((word >> (8 * k)) & 255u) << 8)); };
+                float tn = fmaxf(fmaxf(fmaf(g(wnx), Bx, nAx), fmaf(g(wny), By, nAy)), fmaxf(fmaf(g(wnz), Bz, nAz), 0.0f));
+                float tf = fminf(fminf(fmaf(g(wfx), Bx, fAx), fmaf(g(wfy), By, fAy)), fminf(fmaf(g(wfz), Bz, fAz), h.t));
+                tf = tf * 1.00000047683715820312f;
+                hit[k] = tn <= tf;
+                key[k] = hit[k] ? ((f_bits(tn) & ~3u) | (uint32_t)k) : 0xffffffffu;
+            }
+            uint32_t kmin = std::min(std::min(key[0], key[1]), std::min(key[2], key[3]));
+            if (kmin != 0xffffffffu) {
+                for (int k = 0; k < 4; ++k) if (hit[k] && key[k] > kmin) stack.push_back(w.code[k]);
+                cur = w.code[kmin & 3u];
+                continue;
+            }
+        } else {
+            if (n_tests) ++*n_tests;
+            uint32_t payload = (uint32_t)~cur, type = payload >> 28, idx = payload & 0x0fffffffu;
+            int q = type == 0 ? (int)idx : type == 1 ? ns + (int)idx : (int)sc.sorted_prim[idx];
+            test_prim(sc, q, o, d, dn, rs, h);
+        }
+        if (stack.empty()) break;
+        cur = stack.back(); stack.pop_back();
+        if (cur == DONE) break;
+    }
+    return h;
+}
+
 /* ---------------------------------------------------------------- surface + materials */
 struct Surface { V3 p, n; bool front; int mat; };
 
@@ -522,7 +635,21 @@ void* po_scene_create(const prt_sphere* spheres, int ns, const prt_quad* quads, 
 void po_scene_destroy(void* s) { delete (Scene*)s; }
 int po_num_prims(void* s) { return ((Scene*)s)->n_prims(); }
 
-void po_build_lbvh(void* s) { build_lbvh(*(Scene*)s); }
+void po_build_lbvh(void* s) { build_lbvh(*(Scene*)s); build_wide(*(Scene*)s); }
+
+/* 4-wide nodes in the device layout: 16 words per internal node {ox,oy,oz,sx, code[4], qlo[3], qhi[3], sy,sz}; valid[i] = even depth */
+void po_get_wide(void* s, uint32_t* words, uint8_t* valid) {
+    Scene& sc = *(Scene*)s;
+    for (size_t i = 0; i < sc.wide.size(); ++i) {
+        const Scene::WNode& w = sc.wide[i]; uint32_t* o = words + 16 * i;
+        if (valid) valid[i] = sc.wide_valid[i];
+        if (!words) continue;
+        o[0] = f_bits(w.org[0]); o[1] = f_bits(w.org[1]); o[2] = f_bits(w.org[2]); o[3] = f_bits(w.scale[0]);
+        for (int c = 0; c < 4; ++c) o[4 + c] = (uint32_t)w.code[c];
+        for (int k = 0; k < 3; ++k) { o[8 + k] = w.qlo[k]; o[11 + k] = w.qhi[k]; }
+        o[14] = f_bits(w.scale[1]); o[15] = f_bits(w.scale[2]);
+    }
+}
 
 /* same outputs as prt_debug_lbvh */
 void po_get_lbvh(void* s, uint32_t* morton, uint32_t* sorted_prim, int32_t* node_children, int32_t* node_parent,
@@ -543,7 +670,7 @@ void po_get_lbvh(void* s, uint32_t* morton, uint32_t* sorted_prim, int32_t* node
     }
 }
 
-/* closest hit for a ray batch. use_bvh: 0 brute force, 1 LBVH traversal. counters[0..1] += nodes, prim tests */
+/* closest hit for a ray batch. use_bvh: 0 brute force, 1 LBVH traversal, 2 the 4-wide quantised nodes. counters[0..1] += nodes, prim tests */
 void po_trace_batch(void* s, const prt_ray* rays, int n, prt_hit* out, int use_bvh, uint64_t* counters, int n_threads) {
     Scene& sc = *(Scene*)s;
     if (n_threads < 1) n_threads = 1;
@@ -551,7 +678,8 @@ void po_trace_batch(void* s, const prt_ray* rays, int n, prt_hit* out, int use_b
     auto work = [&](int tid) {
         for (int i = tid; i < n; i += n_threads) {
             V3 o = mk(rays[i].ox, rays[i].oy, rays[i].oz), d = mk(rays[i].dx, rays[i].dy, rays[i].dz);
-            Hit h = use_bvh ? closest_bvh(sc, o, d, &nn[tid], &np[tid]) : closest_brute(sc, o, d, &np[tid]);
+            Hit h = use_bvh == 2 ? closest_wide(sc, o, d, &nn[tid], &np[tid])
+                  : use_bvh ? closest_bvh(sc, o, d, &nn[tid], &np[tid]) : closest_brute(sc, o, d, &np[tid]);
             prt_hit r; memset(&r, 0, sizeof r);
             if (h.q < 0) { r.t = h.t; r.prim_id = -1; r.material = -1; }
             else {

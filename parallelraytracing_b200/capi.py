@@ -47,7 +47,7 @@ EXPORTS = [
     "prt_create", "prt_destroy", "prt_last_error", "prt_version", "prt_set_scene", "prt_build_bvh",
     "prt_set_camera", "prt_render", "prt_clear_accum", "prt_scale_accum", "prt_accum_device_ptr",
     "prt_set_accum_buffer", "prt_read_accum", "prt_accum_spp", "prt_set_accum_spp", "prt_resolve_display", "prt_trace_batch",
-    "prt_debug_lbvh", "prt_num_prims", "prt_enable_counters", "prt_get_stats", "prt_set_option",
+    "prt_debug_lbvh", "prt_debug_wide", "prt_num_prims", "prt_enable_counters", "prt_get_stats", "prt_set_option",
 ]
 
 _lib = None
@@ -86,6 +86,7 @@ def load_library():
     lib.prt_resolve_display.argtypes = [vp, f32, f32, vp]
     lib.prt_trace_batch.argtypes = [vp, vp, i32, vp, i32]
     lib.prt_debug_lbvh.argtypes = [vp, vp, vp, vp, vp, vp, vp]
+    lib.prt_debug_wide.argtypes = [vp, vp]
     lib.prt_num_prims.argtypes = [vp]
     lib.prt_enable_counters.argtypes = [vp, i32]
     lib.prt_get_stats.argtypes = [vp, C.POINTER(CStats)]
@@ -201,6 +202,12 @@ class Context:
                                             _ptr(d["node_parent"]), _ptr(d["node_bounds"]), _ptr(d["scene_bounds"])),
                     "prt_debug_lbvh")
         return d
+
+    def debug_wide(self):
+        """(n-1, 16) uint32: raw WideNode records; rows of odd-depth nodes are undefined."""
+        w = np.zeros((max(self.num_prims() - 1, 0), 16), np.uint32)
+        self._check(self.lib.prt_debug_wide(self.h, _ptr(w)), "prt_debug_wide")
+        return w
 
     def enable_counters(self, on=True):
         self._check(self.lib.prt_enable_counters(self.h, 1 if on else 0), "prt_enable_counters")

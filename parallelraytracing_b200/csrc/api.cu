@@ -323,6 +323,15 @@ int prt_debug_lbvh(prt_ctx* ctx, uint32_t* morton, uint32_t* sorted_prim, int32_
     return PRT_OK;
 }
 
+int prt_debug_wide(prt_ctx* ctx, uint32_t* words) {
+    if (!ctx || !words) return set_err(ctx ? &ctx->c : nullptr, PRT_ERR_INVALID, "prt_debug_wide: NULL argument");
+    Ctx* c = &ctx->c;
+    if (!c->bvh_built || !c->wide_built) return set_err(c, PRT_ERR_INVALID, "prt_debug_wide: wide nodes not built");
+    PRT_CUDA(c, cudaSetDevice(c->device));
+    PRT_CUDA(c, cudaMemcpy(words, c->wnodes.p, (size_t)(c->n_prims - 1) * sizeof(WideNode), cudaMemcpyDeviceToHost));
+    return PRT_OK;
+}
+
 int prt_enable_counters(prt_ctx* ctx, int on) {
     if (!ctx) return set_err(nullptr, PRT_ERR_INVALID, "prt_enable_counters: ctx is NULL");
     ctx->c.counters_on = on ? 1 : 0;

@@ -128,20 +128,31 @@ def test_closest_hit_vs_reference_vectors(ctx, gold, name):
 
 
 @pytest.mark.parametrize("name", sorted(SCENES))
-def test_wide_nodes_equal_two_child_bvh(ctx, gold, name):
+def test_wide_nodes_equal_two_child_bvh(ctx, oracle, gold, name):
     """The 4-wide quantised nodes (what the staged render path walks) return the same hit records, bit for bit,
     as the two-child LBVH and as brute force, with fewer node visits; leaf tests may differ (other visit order)."""
     sd = SCENES[name](gold)
     ctx.set_option("bvh_wide", 1)                      # also for the small scenes that the auto policy leaves two-child
     ctx.set_scene(sd); ctx.build_bvh()
     ctx.set_option("bvh_wide", -1)
-    rays = util.fixed_ray_batch(sd, 65536, seed=11)
+    rays = util.fixed_ray_batch(sd, 65536, seed=11, clamp_extent=60.0)
     ctx.enable_counters(True)
     two = ctx.trace_batch(rays, use_bvh=1); st2 = ctx.stats(); n2 = st2.nodes_visited
     wide = ctx.trace_batch(rays, use_bvh=2); stw = ctx.stats(); nw = stw.nodes_visited
     ctx.enable_counters(False)
     for k in two.dtype.names:
         assert np.array_equal(two[k], wide[k]), k
+    # the CPU restatement of the collapse + quantisation gives the same bytes, and its walk the same counters
+    if sd.n_prims > 1:
+        osc = oracle.scene(sd)
+        ow, valid = osc.get_wide()
+        gw = ctx.debug_wide()
+        assert valid[0] and 0.3 < valid.mean() < 0.8
+        assert np.array_equal(gw[valid], ow[valid]), "wide nodes: origin, scales, child codes, quantised boxes"
+        cnt = np.zeros(2, np.uint64)
+        owide = osc.trace_batch(rays, use_bvh=2, counters=cnt)
+        assert np.array_equal(owide, wide)
+        assert (stw.nodes_visited, stw.prims_tested) == (int(cnt[0]), int(cnt[1])), "wide traversal counters reproduce on the CPU"
     if sd.n_prims > 2:
         assert 0 < nw < n2, (nw, n2)
     if sd.n_prims <= 20000:

@@ -184,3 +184,36 @@ def test_rng_stream_is_what_reference_rand_sees(ref, oracle):
                               seed, pixel, sample, bounce)
     d = (n + ruv).astype(np.float32)
     assert ok and np.allclose(o, d / np.linalg.norm(d), atol=1e-6)
+
+
+@pytest.mark.parametrize("make", [lambda: S.closed_cornell(), lambda: S.make_scene(S.ScenePreset.RANDOM_BALLS_MEDIUM),
+                                  lambda: S.random_triangle_soup(3000)])
+def test_oracle_wide_nodes_walk_equals_two_child_and_brute(oracle, make):
+    """The CPU restatement of the 4-wide quantised nodes (collapse + 8-bit boxes, oracle/prt_oracle.cpp build_wide /
+    closest_wide) is conservative: same hit records as the two-child walk and as brute force, in fewer node visits;
+    every child box decodes to a superset of the true box."""
+    sd = make()
+    osc = oracle.scene(sd)
+    rays = util.fixed_ray_batch(sd, 20000, seed=5, clamp_extent=60.0)
+    c2, cw = np.zeros(2, np.uint64), np.zeros(2, np.uint64)
+    two = osc.trace_batch(rays, use_bvh=1, counters=c2)
+    wide = osc.trace_batch(rays, use_bvh=2, counters=cw)
+    brute = osc.trace_batch(rays, use_bvh=0)
+    assert np.array_equal(two, wide) and np.array_equal(brute, wide)
+    assert 0 < cw[0] < c2[0]
+    w, valid = osc.get_wide()
+    lb = osc.get_lbvh()
+    nb, ch = lb["node_bounds"], lb["node_children"]
+    for i in np.flatnonzero(valid)[:2000]:
+        org = w[i, 0:3].view(np.float32); step = np.array([w[i, 3], w[i, 14], w[i, 15]], np.uint32).view(np.float32) / 32768.0
+        boxes = []                                     # true child boxes in slot order
+        for side in range(2):
+            c = ch[i, side]
+            if c < 0:
+                boxes.append(nb[i, 6 * side:6 * side + 6])
+            else:
+                boxes += [nb[c, 0:6], nb[c, 6:12]]
+        for slot, b in enumerate(boxes):
+            qlo = np.array([(w[i, 8 + k] >> (8 * slot)) & 255 for k in range(3)], np.float64)
+            qhi = np.array([(w[i, 11 + k] >> (8 * slot)) & 255 for k in range(3)], np.float64)
+            assert np.all(org + qlo * step <= b[0:3]) and np.all(org + qhi * step >= b[3:6]), (i, slot)

@@ -330,7 +330,9 @@ def roofline_and_json(args, R):
         name = "k_primary + k_bounce (fused raygen/extend/shade/compaction)"
     else:
         queue_bytes = rays_step * (32 + 16) + rays_step * 64 + cont * 48 + paths_step * 16 + paths_step * 48
-        name = "k_extend_pt + k_shade (persistent LBVH traversal, shade/compaction)"
+        wide = sd.n_prims >= 4096 and not any(o.startswith("bvh_wide=0") for o in args.opt)
+        name = ("k_extend_wide + k_shade (persistent traversal of the 4-wide quantised nodes, shade/compaction)" if wide else
+                "k_extend_pt + k_shade (persistent LBVH traversal, shade/compaction)")
     alg_bytes = queue_bytes + rays_step * (b_shade + b_trav)
     # kernel time: summed per-launch CUDA-event spans; with two waves in flight (two streams) spans of different
     # waves overlap in time, so the sum is capped by the device time of the whole render

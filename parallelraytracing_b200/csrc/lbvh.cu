@@ -372,9 +372,8 @@ int lbvh_build(Ctx* c) {
     cudaStream_t st = c->stream;
     int rc;
     if ((rc = dev_reserve(c, c->scene_bounds, 6 * sizeof(int)))) return rc;
-    PRT_CUDA(c, cudaEventRecord(c->ev0, st));
-    k_init_bounds<<<1, 32, 0, st>>>((int*)c->scene_bounds.p);
     if (n == 0) {
+        k_init_bounds<<<1, 32, 0, st>>>((int*)c->scene_bounds.p);
         c->root_code = 0; c->bvh_built = true; c->build_ms = 0.f;
         PRT_CUDA(c, cudaStreamSynchronize(st));
         return PRT_OK;
@@ -391,6 +390,11 @@ int lbvh_build(Ctx* c) {
         return rc;
     const int nblocks = (n + RS_TILE - 1) / RS_TILE;
     if ((rc = dev_reserve(c, c->block_hist, ((size_t)nblocks * 256 + 256) * 4))) return rc;   // + 256 digit totals
+    const bool want_wide = n > 1 && (c->bvh_wide > 0 || (c->bvh_wide < 0 && n >= c->wide_min_prims));
+    if (want_wide && (rc = dev_reserve(c, c->wnodes, nn * sizeof(WideNode)))) return rc;
+    // every allocation is done: the timed region below is kernels only (cudaMalloc synchronises and is not build work)
+    PRT_CUDA(c, cudaEventRecord(c->ev0, st));
+    k_init_bounds<<<1, 32, 0, st>>>((int*)c->scene_bounds.p);
 
     const int T = 256, G = (n + T - 1) / T;
     k_prim_bounds<<<G, T, 0, st>>>((const SphereRec*)c->spheres.p, ns, (const QuadRec*)c->quads.p, nq,
@@ -422,8 +426,7 @@ int lbvh_build(Ctx* c) {
         k_refit<<<G, T, 0, st>>>(n, sprim, (const float4*)c->aabb_min.p, (const float4*)c->aabb_max.p,
                                  (const int*)c->children.p, parent, leaf_parent,
                                  (float4*)c->node_min.p, (float4*)c->node_max.p, (int*)c->flags.p, ns, nq, (BvhNode*)c->nodes.p);
-        if (c->bvh_wide > 0 || (c->bvh_wide < 0 && n >= c->wide_min_prims)) {
-            if ((rc = dev_reserve(c, c->wnodes, nn * sizeof(WideNode)))) return rc;
+        if (want_wide) {
             k_emit_wide<<<G, T, 0, st>>>(n - 1, parent, (const BvhNode*)c->nodes.p, (WideNode*)c->wnodes.p);
             c->wide_built = true;
         }

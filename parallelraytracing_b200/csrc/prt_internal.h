@@ -76,6 +76,7 @@ struct Ctx {
     int fused_max_prims = 64;                   // auto: fuse when traversal is a handful of nodes (shading dominates)
     int brute_max_prims = 8;                    // fused kernels: sphere/quad scenes this small skip the BVH (uniform loop over the list)
     int persistent = 1;                         // staged extend = persistent threads with per-lane dynamic fetch
+    int pt_refill_wide = 20;                    // same threshold for the 4-wide kernel (measured best 20: dragon960k, soup1m, soup10m)
     int pt_refill = 16;                         // refill the warp when fewer lanes than this are traversing
     int stage_timing = 1;                       // CUDA-event pairs around the hot kernels
     std::vector<cudaEvent_t> ev_pool;

@@ -836,7 +836,7 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
                     if (timing) spans.push_back({stamp(st), b == 0 ? 2 : 0});
                     if (c->persistent) {
                         uint32_t* work = qcount + (PRT_MAX_DEPTH + 2) + b;
-                        k_ext<<<grid_pt, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], hits, qcount, work, b, c->pt_refill, dstats);
+                        k_ext<<<grid_pt, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], hits, qcount, work, b, wide ? c->pt_refill_wide : c->pt_refill, dstats);
                     } else if (c->counters_on) k_extend<true><<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], hits, qcount, b, dstats);
                     else k_extend<false><<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], hits, qcount, b, dstats);
                     if (timing) spans.push_back({stamp(st), 1});
@@ -911,7 +911,7 @@ int wavefront_trace_batch(Ctx* c, const prt_ray* rays, int n, prt_hit* out, int 
         int per_sm = 4;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, WF_THREADS, 0);
         k<<<std::max(1, c->num_sms * std::max(1, per_sm)), WF_THREADS, 0, st>>>(sc, (const float4*)c->q_o[0].p, (const float4*)c->q_d[0].p,
-                                                                                (float4*)c->hits.p, qcount, work, 0, c->pt_refill, dstats);
+                                                                                (float4*)c->hits.p, qcount, work, 0, c->pt_refill_wide, dstats);
     } else if (use_bvh && c->persistent) {
         uint32_t* work = qcount + (PRT_MAX_DEPTH + 2);
         int per_sm = 4;

@@ -160,7 +160,7 @@ class CpuArm:
                                                                             self.w["depth"], self.cores)
 
 
-def run_reference_arm(args):
+def run_reference_arm(args, out_fd=1):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
@@ -183,7 +183,8 @@ def run_reference_arm(args):
            "spp_per_s_1080p": frac * args.steps / t_tot,
            "cpu_baseline": {"value": val, "unit": "Mrays/s", "cores": arm.cores, "kind": arm.kind, "sample": arm.describe(spp, rows)},
            "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(out))
+    sys.stdout.flush()
+    emit(json.dumps(out), out_fd)
     return 0
 
 
@@ -377,7 +378,16 @@ def roofline_and_json(args, R):
     return out
 
 
+def emit(line, fd):
+    os.write(fd, (line + "\n").encode())
+
+
 def main():
+    # stdout carries exactly ONE JSON line: anything libraries print there (e.g. "NCCL version ..." from rank 0)
+    # is sent to stderr by pointing fd 1 at fd 2 for the duration of the run
+    sys.stdout.flush()
+    out_fd = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -389,7 +399,7 @@ def main():
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
-        return run_reference_arm(args)
+        return run_reference_arm(args, out_fd)
     R = run_ours(args)
     if R["rank"] == 0:
         out = roofline_and_json(args, R)
@@ -401,7 +411,8 @@ def main():
                                    "sample": arm.describe(spp, rows), "seconds": dt}
         else:
             out["cpu_baseline"] = None
-        print(json.dumps(out))
+        sys.stdout.flush()
+        emit(json.dumps(out), out_fd)
     if R["world"] > 1:
         import torch.distributed as dist
         dist.barrier()

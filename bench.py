@@ -213,10 +213,21 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     sd, cam, w = make_workload(args.workload)
     W, H, spp, depth = w["W"], w["H"], w["spp"], w["depth"]
-    if w.get("strong"):                       # fixed total work: every rank takes an equal share of the samples
+    tiles = args.partition == "tiles"
+    if tiles and not w.get("strong"):
+        raise SystemExit("bench.py: --partition tiles needs a fixed-total-work workload (dragon960k_4k_*)")
+    if w.get("strong") and not tiles:         # fixed total work: every rank takes an equal share of the samples
         if spp % world:
             raise SystemExit("bench.py: %d spp does not split over %d ranks" % (spp, world))
         spp //= world
+    from parallelraytracing_b200.dist import pixel_range
+    pix_begin, pix_count = pixel_range(rank, world, W * H, W) if tiles else (0, W * H)
+
+    def render(seed):
+        if tiles:
+            ctx.render_region(spp, depth, seed=seed, sample_begin=0, pixel_begin=pix_begin, pixel_count=pix_count)
+        else:
+            ctx.render(spp, depth, seed=seed, sample_begin=rank * spp)
     ctx = Context(local)
     for kv in args.opt:
         k, v = kv.split("=")
@@ -233,7 +244,7 @@ def run_ours(args):
         """rank r renders samples [r*spp, (r+1)*spp) of step i's frame; sum-reduce to rank 0."""
         accum.zero_()
         ctx.clear_accum()
-        ctx.render(spp, depth, seed=1 + i, sample_begin=rank * spp)
+        render(1 + i)
         if world > 1:
             dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
 
@@ -260,7 +271,7 @@ def run_ours(args):
         accum.zero_()
         ctx.clear_accum()
         torch.cuda.synchronize()
-        ctx.render(spp, depth, seed=100 + i, sample_begin=rank * spp)     # synchronous, like ProgressiveRender
+        render(100 + i)                                                   # synchronous, like ProgressiveRender
         st = ctx.stats()
         rays += st.rays_total; launches += st.kernel_launches
         render_ms += st.render_ms; ext_ms += st.extend_ms; shd_ms += st.shade_ms; prim_ms += st.primary_ms
@@ -291,7 +302,10 @@ def run_ours(args):
         r.SetSeed(200 + i); r.SetNextSample(rank * spp)
         r.Init(film, sd, cam)                 # host scene -> H2D upload + GPU LBVH build + camera
         film.Clear()
-        r.ProgressiveRender()
+        if tiles:                             # this rank's band of rows, all samples
+            ctx.render_region(spp, depth, seed=200 + i, sample_begin=0, pixel_begin=pix_begin, pixel_count=pix_count)
+        else:
+            r.ProgressiveRender()
         img = film.ReadAccum()                # D2H of the float image
         e2e_rays += r.Stats().rays_total
     e2e_s = time.perf_counter() - t0
@@ -302,7 +316,7 @@ def run_ours(args):
         e2e_s, e2e_rays = float(tmax[0]), float(tsum[1])
     return dict(rank=rank, world=world, ctx=ctx, sd=sd, cam=cam, w=w, rays_all=rays_all, dev_ms_max=dev_ms_max,
                 launches_all=launches_all, ext_ms=ext_ms, shd_ms=shd_ms, prim_ms=prim_ms, render_ms=render_ms, red_ms=red_ms, rays=rays,
-                spp=spp, clk=clk, e2e_s=e2e_s, e2e_rays=e2e_rays, build_ms=build_ms, wall_ms=wall_ms, img_mean=float(img.mean()))
+                spp=spp, tiles=tiles, paths_step=pix_count * spp, clk=clk, e2e_s=e2e_s, e2e_rays=e2e_rays, build_ms=build_ms, wall_ms=wall_ms, img_mean=float(img.mean()))
 
 
 def roofline_and_json(args, R):
@@ -317,7 +331,7 @@ def roofline_and_json(args, R):
     n_node = st.nodes_visited / max(1, st.rays_total)
     n_leaf = st.prims_tested / max(1, st.rays_total)
     rays_step = R["rays"] / steps                      # this rank
-    paths_step = W * H * spp
+    paths_step = R["paths_step"]                       # this rank
     cont = rays_step - paths_step                      # segments that continued into another bounce
     fused = R["shd_ms"] == 0.0
     # ALGORITHMIC bytes: B_ray = B_queue + B_shade + 64*n_node + 48*n_leaf.
@@ -365,11 +379,11 @@ def roofline_and_json(args, R):
            "ms_per_step": R["dev_ms_max"] / steps, "higher_is_better": True, "scaling": "strong" if w.get("strong") else "weak",
            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
            "config": {"workload": args.workload, "scene": sd.name, "prims": sd.n_prims, "width": W, "height": H,
-                      "spp_per_step_per_gpu": spp, "depth": depth, "partition": "sample-range, NCCL sum-reduce to rank 0",
+                      "spp_per_step_per_gpu": spp, "depth": depth, "partition": ("bands of rows" if args.partition == "tiles" else "sample-range") + ", NCCL sum-reduce to rank 0",
                       "l2": "256 MiB L2 flush between timed steps; ray queues (GBs) also exceed the 126 MB L2",
                       "options": args.opt},
-           "spp_per_s_1080p": R["world"] * spp * steps / dev_s,
-           "mpaths_per_s": R["world"] * paths_step * steps / dev_s / 1e6,
+           "spp_per_s_1080p": (1 if R["tiles"] else R["world"]) * spp * steps / dev_s,
+           "mpaths_per_s": (1 if R["tiles"] else R["world"]) * W * H * spp * steps / dev_s / 1e6,
            "rays_per_path": rays_step / paths_step,
            "e2e": {"value": R["e2e_rays"] / R["e2e_s"] / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": scene_bytes(sd) + 64,
                    "d2h_bytes_per_step": W * H * 12, "what": "B200Renderer.Init(host scene)+ProgressiveRender+Film.ReadAccum per step, wall clock"},
@@ -395,6 +409,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--partition", default="samples", choices=["samples", "tiles"],
+                    help="multi-GPU split: sample ranges (default) or bands of rows (strong-scaling workloads only)")
     ap.add_argument("--opt", action="append", default=[], help="prt_set_option key=value (e.g. fused=0, wave_paths=8388608)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

@@ -169,6 +169,12 @@ int  prt_set_camera(prt_ctx* ctx, const prt_camera* cam);
  * (cpu/renderer.cpp:59-103 semantics) and ADDS them to the accumulation buffer.
  * Synchronous, like the reference (cudaDeviceSynchronize at renderer.cu:429). */
 int  prt_render(prt_ctx* ctx, int spp, int max_depth, uint64_t seed, int sample_begin);
+/* The same for the pixel range [pixel_begin, pixel_begin + pixel_count) only (row-major pixel index y*W+x; a band
+ * of rows is a contiguous range): the TILE partition of SURVEY 8e - each GPU renders all samples of its own pixels,
+ * pixels outside the range are left untouched, and the same sum-reduce assembles the frame. Identical per-pixel
+ * results to prt_render (the RNG is keyed by pixel and sample, not by launch geometry). Does not change the
+ * weight reported by prt_accum_spp unless the range is the whole frame. */
+int  prt_render_region(prt_ctx* ctx, int spp, int max_depth, uint64_t seed, int sample_begin, int pixel_begin, int pixel_count);
 
 /* Zero the accumulation buffer (Film::Clear, film.cu:25-35). */
 int  prt_clear_accum(prt_ctx* ctx);

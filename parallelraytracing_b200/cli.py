@@ -61,6 +61,8 @@ def main(argv=None):
     ap.add_argument("--gamma", type=float, default=2.2)
     ap.add_argument("--out", default=None, help="image file (.png or .ppm) written by rank 0")
     ap.add_argument("--raw", default=None, help="also save the float accumulation buffer (sum of samples) as .npy")
+    ap.add_argument("--partition", default="samples", choices=["samples", "tiles"],
+                    help="multi-GPU split of a frame: sample ranges, or bands of rows (SURVEY 8e)")
     ap.add_argument("--opt", action="append", default=[], help="prt_set_option key=value")
     args = ap.parse_args(argv)
 
@@ -92,7 +94,7 @@ def main(argv=None):
         from .dist import ShardedRenderer
         torch.cuda.set_device(local)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-        sharded = ShardedRenderer(r, film, torch.device("cuda", local))
+        sharded = ShardedRenderer(r, film, torch.device("cuda", local), partition=args.partition)
 
     render_ms, film_ms, rays = [], [], 0
     display = None

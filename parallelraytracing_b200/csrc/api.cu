@@ -244,7 +244,26 @@ int prt_render(prt_ctx* ctx, int spp, int max_depth, uint64_t seed, int sample_b
     if (spp == 0) return PRT_OK;
     PRT_CUDA(c, cudaSetDevice(c->device));
     if (max_depth == 0) { c->accum_spp += spp; return PRT_OK; }   // TraceRay(depth<=0) = 0, renderer.cpp:61
-    return wavefront_render(c, spp, max_depth, seed, sample_begin);
+    return wavefront_render(c, spp, max_depth, seed, sample_begin, 0, (int64_t)c->cam.width * c->cam.height);
+}
+
+int prt_render_region(prt_ctx* ctx, int spp, int max_depth, uint64_t seed, int sample_begin, int pixel_begin, int pixel_count) {
+    if (!ctx) return set_err(nullptr, PRT_ERR_INVALID, "prt_render_region: ctx is NULL");
+    Ctx* c = &ctx->c;
+    if (!c->scene_set || !c->bvh_built) return set_err(c, PRT_ERR_INVALID, "prt_render_region: scene/BVH not ready (prt_set_scene + prt_build_bvh)");
+    if (!c->cam_set) return set_err(c, PRT_ERR_INVALID, "prt_render_region: call prt_set_camera first");
+    const int64_t P = (int64_t)c->cam.width * c->cam.height;
+    if (spp < 0 || max_depth < 0 || max_depth > PRT_MAX_DEPTH || sample_begin < 0 || pixel_begin < 0 || pixel_count < 0 ||
+        (int64_t)pixel_begin + pixel_count > P)
+        return set_err(c, PRT_ERR_INVALID, "prt_render_region: bad spp / max_depth / sample_begin / pixel range");
+    if (spp == 0 || pixel_count == 0) return PRT_OK;
+    PRT_CUDA(c, cudaSetDevice(c->device));
+    const bool whole = pixel_begin == 0 && pixel_count == P;
+    if (max_depth == 0) { if (whole) c->accum_spp += spp; return PRT_OK; }
+    const int before = c->accum_spp;
+    int rc = wavefront_render(c, spp, max_depth, seed, sample_begin, pixel_begin, pixel_count);
+    if (!whole) c->accum_spp = before;
+    return rc;
 }
 
 int prt_clear_accum(prt_ctx* ctx) {

@@ -99,7 +99,7 @@ SceneView scene_view(const Ctx* c);
 // lbvh.cu
 int lbvh_build(Ctx* c);
 // wavefront.cu
-int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_begin);
+int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_begin, int64_t pixel_begin, int64_t pixel_count);
 int wavefront_trace_batch(Ctx* c, const prt_ray* rays, int n, prt_hit* out, int use_bvh);
 int film_resolve_display(Ctx* c, float exposure, float gamma, uint8_t* host_rgba);
 int film_scale_accum(Ctx* c, float s);

@@ -739,9 +739,8 @@ static int ensure_wave_buffers(Ctx* c, int64_t paths, bool second_set = false) {
     return PRT_OK;
 }
 
-int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_begin) {
-    const int W = c->cam.width, H = c->cam.height;
-    const int64_t P = (int64_t)W * H;
+int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_begin, int64_t pixel_begin, int64_t pixel_count) {
+    const int64_t P = pixel_count;                                   // pixels [pixel_begin, pixel_begin + P) of the frame
     int64_t cap = c->wave_paths_opt > 0 ? c->wave_paths_opt : (int64_t)64 << 20;   // 64 Mi paths: 8.6 GB of queues per set
     cap = std::min<int64_t>(cap, (int64_t)1 << 26);                  // slot must fit 27 bits
     // wave = pixel range [p0, p0+npix) x S samples
@@ -790,10 +789,10 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
     int64_t wave = 0;
     for (int s0 = 0; s0 < spp; s0 += S_wave) {
         const int S = std::min(S_wave, spp - s0);
-        for (int64_t p0 = 0; p0 < P; p0 += npix_wave, ++wave) {
+        for (int64_t p0 = pixel_begin; p0 < pixel_begin + P; p0 += npix_wave, ++wave) {
             const int set = (int)(wave % nsets);
             cudaStream_t st = sts[set];
-            const int npix = (int)std::min<int64_t>(npix_wave, P - p0);
+            const int npix = (int)std::min<int64_t>(npix_wave, pixel_begin + P - p0);
             const int n_paths = npix * S;
             const FastDiv div_npix = make_fastdiv((uint32_t)npix);
             paths += (uint64_t)n_paths;

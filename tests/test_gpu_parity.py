@@ -221,6 +221,25 @@ def test_sample_ranges_compose(ctx, gold):
     assert np.array_equal(a, c) and np.array_equal(a, d)
 
 
+def test_pixel_regions_compose(ctx, gold):
+    """TILE partition rule: rendering disjoint pixel ranges (bands of rows, ragged last range) leaves the
+    other pixels untouched and the union equals the whole-frame render bit for bit, fused and staged."""
+    for sd, cam in ((S.closed_cornell(), S.Camera(width=80, height=60)),
+                    (SCENES["dragon3"](gold), S.Camera(pos=(0.0, 1.0, 5.0), front=S._normalize(S._v3(0, -1, -5)), width=64, height=48))):
+        ctx.set_scene(sd); ctx.build_bvh(); ctx.set_camera(cam)
+        P = cam.width * cam.height
+        ctx.clear_accum(); ctx.render(3, 8, seed=9, sample_begin=2); whole = ctx.read_accum(); rays = ctx.stats().rays_total
+        ctx.clear_accum()
+        cuts, tot = [0, 17 * cam.width, 17 * cam.width + 5, 40 * cam.width, P], 0
+        for b, e in zip(cuts[:-1], cuts[1:]):
+            ctx.render_region(3, 8, seed=9, sample_begin=2, pixel_begin=b, pixel_count=e - b); tot += ctx.stats().rays_total
+            part = ctx.read_accum().reshape(P, 3)
+            assert not part[e:].any(), "pixels after the rendered ranges stay zero"
+        assert np.array_equal(ctx.read_accum(), whole) and tot == rays and ctx.accum_spp() == 0
+    with pytest.raises(PrtError):
+        ctx.render_region(1, 8, pixel_begin=P - 1, pixel_count=2)
+
+
 def test_staged_pipeline_equals_fused(ctx, gold):
     """fused=0 runs raygen / extend / shade as separate kernels with a hit queue; fused=1 (default)
     removes the stage boundaries. Same device functions, same order: identical bits and ray counts."""

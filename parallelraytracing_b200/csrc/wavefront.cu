@@ -461,9 +461,13 @@ __device__ __forceinline__ void sq_put(float* __restrict__ q, int e, V3 o, V3 d,
 }
 
 // Shade queue entries [first, first+n) (n <= 32), one per lane, and push the continuing paths. Whole warp calls.
+// A continuing path as it leaves shading; with DEFER the caller pushes it (block-wide, push_block) instead of the warp.
+struct ShadeOut { bool cont; V3 np, ndir, beta; uint32_t sb, key; };
+
+template <bool DEFER = false>
 __device__ __forceinline__ void sq_shade(const SceneView& sc, const float* __restrict__ q, int first, int n, uint32_t lane,
                                          int bounce, int max_depth, float4* __restrict__ contrib, uint32_t* __restrict__ next_count,
-                                         float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb) {
+                                         float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb, ShadeOut* out = nullptr) {
     bool cont = false;
     V3 beta = mk(0, 0, 0), np = beta, ndir = beta;
     uint32_t key = 0, sb = 0;
@@ -478,15 +482,41 @@ __device__ __forceinline__ void sq_shade(const SceneView& sc, const float* __res
                              q[13 * SQ_CAP + e], q[14 * SQ_CAP + e], beta, np, ndir, L);
         if (!cont) st_stream(&contrib[sb >> 5], make_float4(L.x, L.y, L.z, 0.f));
     }
-    push_compacted(cont, lane, next_count, no, nd, nb, np, ndir, beta, sb + 1u, key);
+    if (DEFER) { out->cont = cont; out->np = np; out->ndir = ndir; out->beta = beta; out->sb = sb + 1u; out->key = key; }
+    else push_compacted(cont, lane, next_count, no, nd, nb, np, ndir, beta, sb + 1u, key);
+}
+
+// Block-wide compaction: ONE atomic on the queue counter per block and round instead of one per warp. All 256 threads
+// call it the same number of times. (ncu on the staged k_shade: 57 % of the stall samples sat on the per-warp
+// atomicAdd - ~0.6 M same-address atomics per launch at ~2 ns each were the kernel's whole duration.)
+__device__ __forceinline__ void push_block(const ShadeOut& o, uint32_t lane, uint32_t* __restrict__ next_count,
+                                           float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb) {
+    __shared__ uint32_t wcnt[WF_WARPS];
+    __shared__ uint32_t block_base;
+    const uint32_t warp = threadIdx.x >> 5;
+    const uint32_t mask = __ballot_sync(0xffffffffu, o.cont);
+    if (lane == 0) wcnt[warp] = (uint32_t)__popc(mask);
+    __syncthreads();
+    uint32_t pre = 0, tot = 0;
+#pragma unroll
+    for (uint32_t k = 0; k < (uint32_t)WF_WARPS; ++k) { const uint32_t v = wcnt[k]; pre += k < warp ? v : 0u; tot += v; }
+    if (threadIdx.x == 0 && tot) block_base = atomicAdd(next_count, tot);
+    __syncthreads();
+    if (o.cont) {
+        const uint32_t j = block_base + pre + (uint32_t)__popc(mask & ((1u << lane) - 1u));
+        st_stream(&no[j], make_float4(o.np.x, o.np.y, o.np.z, __uint_as_float(o.sb)));
+        st_stream(&nd[j], make_float4(o.ndir.x, o.ndir.y, o.ndir.z, __uint_as_float(o.key)));
+        st_stream(&nb[j], make_float4(o.beta.x, o.beta.y, o.beta.z, 0.f));
+    }
 }
 
 // One batch of <= 32 segments whose closest hit is known: misses end here, hits go through the queue.
 // `live` = this lane holds a segment. Returns the new queue length. Whole warp calls.
+template <bool DEFER = false>
 __device__ __forceinline__ int sq_batch(const SceneView& sc, float* __restrict__ q, int qn, uint32_t lane, bool live,
                                         V3 o, V3 d, V3 beta, uint32_t key, uint32_t slot_bounce, float t, uint32_t code, float u, float v,
                                         int bounce, int max_depth, float4* __restrict__ contrib, uint32_t* __restrict__ next_count,
-                                        float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb) {
+                                        float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb, ShadeOut* out = nullptr) {
     const bool hit = live && code != PRT_NO_HIT;
     if (live && !hit) {                                                 // cpu/renderer.cpp:99
         V3 L = beta * mk(sc.sky_r, sc.sky_g, sc.sky_b);
@@ -498,7 +528,7 @@ __device__ __forceinline__ int sq_batch(const SceneView& sc, float* __restrict__
     __syncwarp();
     if (qn >= 32) {
         qn -= 32;
-        sq_shade(sc, q, qn, 32, lane, bounce, max_depth, contrib, next_count, no, nd, nb);
+        sq_shade<DEFER>(sc, q, qn, 32, lane, bounce, max_depth, contrib, next_count, no, nd, nb, out);
         __syncwarp();
     }
     return qn;
@@ -515,15 +545,20 @@ k_shade(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ 
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t stride = gridDim.x * WF_THREADS;
     int qn = 0;
-    for (uint32_t base = blockIdx.x * WF_THREADS + (threadIdx.x & ~31u); base < count; base += stride) {
-        uint32_t i = base + lane;
+    ShadeOut out;
+    for (uint32_t cbase = blockIdx.x * WF_THREADS; cbase < count; cbase += stride) {      // block-uniform trip count
+        const uint32_t i = cbase + threadIdx.x;
         float4 o4 = make_float4(0, 0, 0, 0), d4 = o4, b4 = o4, h = o4;
         const bool live = i < count;
         if (live) { o4 = ld_stream(&qo[i]); d4 = ld_stream(&qd[i]); b4 = ld_stream(&qb[i]); h = ld_stream(&hits[i]); }
-        qn = sq_batch(sc, q, qn, lane, live, xyz(o4), xyz(d4), xyz(b4), __float_as_uint(d4.w), __float_as_uint(o4.w),
-                      h.x, __float_as_uint(h.y), h.z, h.w, bounce, max_depth, contrib, &qcount[bounce + 1], no, nd, nb);
+        out.cont = false;
+        qn = sq_batch<true>(sc, q, qn, lane, live, xyz(o4), xyz(d4), xyz(b4), __float_as_uint(d4.w), __float_as_uint(o4.w),
+                            h.x, __float_as_uint(h.y), h.z, h.w, bounce, max_depth, contrib, &qcount[bounce + 1], no, nd, nb, &out);
+        push_block(out, lane, &qcount[bounce + 1], no, nd, nb);
     }
-    if (qn > 0) sq_shade(sc, q, 0, qn, lane, bounce, max_depth, contrib, &qcount[bounce + 1], no, nd, nb);
+    out.cont = false;
+    if (qn > 0) sq_shade<true>(sc, q, 0, qn, lane, bounce, max_depth, contrib, &qcount[bounce + 1], no, nd, nb, &out);
+    push_block(out, lane, &qcount[bounce + 1], no, nd, nb);
 }
 
 // ------------------------------------------------------------------ fused stages

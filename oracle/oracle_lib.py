@@ -38,6 +38,7 @@ class Oracle:
         lib.po_build_lbvh.argtypes = [vp]
         lib.po_get_lbvh.argtypes = [vp] * 7
         lib.po_get_wide.argtypes = [vp, vp, vp]
+        lib.po_set_estimator.argtypes = [vp, i32, C.c_float]
         lib.po_trace_batch.argtypes = [vp, vp, i32, vp, i32, vp, i32]
         lib.po_camera_dirs.argtypes = [C.POINTER(CCamera), vp]
         lib.po_render.restype = u64
@@ -101,6 +102,10 @@ class OracleScene:
         self.lib.po_get_lbvh(self.h, _ptr(d["morton"]), _ptr(d["sorted_prim"]), _ptr(d["node_children"]),
                              _ptr(d["node_parent"]), _ptr(d["node_bounds"]), _ptr(d["scene_bounds"]))
         return d
+
+    def set_estimator(self, rr_start=-1, clamp=0.0):
+        """Estimator options of the device path (default off): Russian roulette from bounce rr_start, radiance clamp."""
+        self.lib.po_set_estimator(self.h, int(rr_start), float(clamp))
 
     def get_wide(self):
         """4-wide quantised nodes in the device layout: ((n-1, 16) uint32 words, (n-1,) valid = even depth)."""

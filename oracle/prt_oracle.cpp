@@ -102,6 +102,7 @@ struct Scene {
     std::vector<WNode> wide;            /* indexed like the internal nodes; only even-depth entries are meaningful */
     std::vector<uint8_t> wide_valid;
     bool built = false;
+    int rr_start = -1; float clamp = INFINITY;      /* estimator options of the device path (default off), po_set_estimator */
     int n_prims() const { return (int)(spheres.size() + quads.size() + tris.size()); }
 };
 
@@ -590,17 +591,24 @@ V3 camera_dir(const Cam& c, float px, float py) {
 /* CPURenderer::TraceRay (cpu/renderer.cpp:59-103), iterative: at most max_depth closest-hit queries */
 V3 trace_path(const Scene& sc, V3 o, V3 d, uint32_t key, int max_depth, bool use_bvh, uint64_t* rays) {
     V3 beta = mk(1.f, 1.f, 1.f), L = mk(0.f, 0.f, 0.f);
+    auto clampL = [&](V3 v) { return sc.clamp < INFINITY ? mk(fminf(v.x, sc.clamp), fminf(v.y, sc.clamp), fminf(v.z, sc.clamp)) : v; };
     for (int bounce = 0; bounce < max_depth; ++bounce) {
         ++*rays;
         Hit h = use_bvh ? closest_bvh(sc, o, d, nullptr, nullptr) : closest_brute(sc, o, d, nullptr);
-        if (h.q < 0) { L = add(L, mulv(beta, mk(sc.sky[0], sc.sky[1], sc.sky[2]))); break; }   /* renderer.cpp:99 */
+        if (h.q < 0) { L = add(L, clampL(mulv(beta, mk(sc.sky[0], sc.sky[1], sc.sky[2])))); break; }   /* renderer.cpp:99 */
         Surface s = make_surface(sc, o, d, h);
         Rng rng = rng_for_bounce(key, (uint32_t)bounce);
         V3 atten, nd, emit;
         bool ok = scatter(sc, s.mat, d, s, rng, atten, nd, emit);
-        L = add(L, mulv(beta, emit));                                                          /* renderer.cpp:74 */
+        L = add(L, clampL(mulv(beta, emit)));                                                   /* renderer.cpp:74 */
         if (!ok) break;
         beta = mulv(beta, atten);                                                               /* renderer.cpp:93 */
+        /* options of the device path, off by default (the reference has neither): Russian roulette */
+        if (sc.rr_start >= 0 && bounce >= sc.rr_start && bounce + 1 < max_depth) {
+            const float p = fmaxf(fminf(fmaxf(fmaxf(beta.x, beta.y), beta.z), 1.0f), 0.05f);
+            if (rng_uniform(rng) > p) break;
+            beta = mk(beta.x / p, beta.y / p, beta.z / p);
+        }
         o = s.p; d = nd;
     }
     return L;
@@ -633,6 +641,7 @@ void* po_scene_create(const prt_sphere* spheres, int ns, const prt_quad* quads, 
     return sc;
 }
 void po_scene_destroy(void* s) { delete (Scene*)s; }
+void po_set_estimator(void* s, int rr_start, float clamp) { Scene& sc = *(Scene*)s; sc.rr_start = rr_start; sc.clamp = clamp > 0.f ? clamp : INFINITY; }
 int po_num_prims(void* s) { return ((Scene*)s)->n_prims(); }
 
 void po_build_lbvh(void* s) { build_lbvh(*(Scene*)s); build_wide(*(Scene*)s); }

@@ -404,6 +404,8 @@ int prt_set_option(prt_ctx* ctx, const char* key, int64_t value) {
     else if (!strcmp(key, "persistent")) c->persistent = value ? 1 : 0;
     else if (!strcmp(key, "pt_refill")) { if (value < 0 || value > 32) return set_err(c, PRT_ERR_INVALID, "pt_refill out of range"); c->pt_refill = (int)value; }
     else if (!strcmp(key, "pt_refill_wide")) { if (value < 0 || value > 32) return set_err(c, PRT_ERR_INVALID, "pt_refill_wide out of range"); c->pt_refill_wide = (int)value; }
+    else if (!strcmp(key, "rr_start")) c->rr_start = value < 0 ? -1 : (int)value;                 // -1 = off (reference estimator)
+    else if (!strcmp(key, "firefly_clamp_milli")) c->firefly_clamp = value <= 0 ? 0.f : (float)value * 1e-3f;   // 0 = off
     else if (!strcmp(key, "stage_timing")) c->stage_timing = value ? 1 : 0;
     else return set_err(c, PRT_ERR_INVALID, std::string("unknown option: ") + key);
     return PRT_OK;

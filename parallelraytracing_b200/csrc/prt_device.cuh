@@ -142,6 +142,8 @@ struct SceneView {
     int              root_code; // root: 0 if n_prims>1, leaf code (negative-as-~) if n_prims==1
     float            tri_tmin;
     float sky_r, sky_g, sky_b;
+    int              rr_start; // estimator option, default off (-1): Russian roulette from this bounce on
+    float            clamp;    // estimator option, default off (+inf): per-path radiance clamp ("firefly clamp")
     uint32_t         one_bits; // 0x3f800000, read from the constant bank so that PRMT keeps its selector as the immediate
     int              brute;    // tiny sphere/quad scene: test every primitive in list order, no BVH (see traverse())
 };

@@ -78,6 +78,8 @@ struct Ctx {
     int persistent = 1;                         // staged extend = persistent threads with per-lane dynamic fetch
     int pt_refill_wide = 20;                    // same threshold for the 4-wide kernel (measured best 20: dragon960k, soup1m, soup10m)
     int pt_refill = 16;                         // refill the warp when fewer lanes than this are traversing
+    int rr_start = -1;                          // estimator options, both OFF by default so that parity with the
+    float firefly_clamp = 0.f;                  // reference's estimator stays checkable: Russian roulette / radiance clamp
     int stage_timing = 1;                       // CUDA-event pairs around the hot kernels
     std::vector<cudaEvent_t> ev_pool;
     prt_stats stats{};

@@ -14,6 +14,7 @@
 // accumulated image is deterministic (no float atomics).
 #include "prt_internal.h"
 #include <algorithm>
+#include <cmath>
 
 namespace prt {
 
@@ -402,10 +403,16 @@ k_extend_brute(SceneView sc, const uint32_t* __restrict__ sorted_prim, const flo
 // ------------------------------------------------------------------ shade / scatter + compaction
 // One path segment after its closest hit is known: L = beta*Le (or beta*sky on a miss), then
 // scatter. Returns true when the path continues with (np, ndir, beta*atten).
+// Firefly clamp (OFF by default = +inf): a path contributes once, when it ends; that contribution is clamped per channel.
+__device__ __forceinline__ V3 clamp_radiance(const SceneView& sc, V3 L) {
+    if (!(sc.clamp < __int_as_float(0x7f800000))) return L;             // off: bit-identical to the reference estimator
+    return mk(fminf(L.x, sc.clamp), fminf(L.y, sc.clamp), fminf(L.z, sc.clamp));
+}
+
 __device__ __forceinline__ bool shade_segment(const SceneView& sc, V3 o, V3 d, uint32_t key, int bounce, int max_depth,
                                               float t, uint32_t code, float hu, float hv, V3& beta, V3& np, V3& ndir, V3& L) {
     if (code == PRT_NO_HIT) {
-        L = beta * mk(sc.sky_r, sc.sky_g, sc.sky_b);                    // cpu/renderer.cpp:99
+        L = clamp_radiance(sc, beta * mk(sc.sky_r, sc.sky_g, sc.sky_b));   // cpu/renderer.cpp:99
         return false;
     }
     Surface s = make_surface(sc, o, d, t, code, hu, hv);
@@ -415,8 +422,19 @@ __device__ __forceinline__ bool shade_segment(const SceneView& sc, V3 o, V3 d, u
     Rng rng = rng_for_bounce(key, (uint32_t)bounce);
     V3 atten, emit;
     bool sc_ok = scatter(m, d, s, rng, atten, ndir, emit);
-    L = beta * emit;                                                    // L += emitted (renderer.cpp:74)
-    if (sc_ok && bounce + 1 < max_depth) { beta = beta * atten; np = s.p; return true; }
+    L = clamp_radiance(sc, beta * emit);                                // L += emitted (renderer.cpp:74)
+    if (sc_ok && bounce + 1 < max_depth) {
+        beta = beta * atten;
+        // Russian roulette (OFF by default: the reference has none, wavefront.md:98-104 lists it as wanted): survive with
+        // p = clamp(max(beta), 0.05, 1), the uniform is the next draw of this bounce's stream, survivors are re-weighted
+        if (sc.rr_start >= 0 && bounce >= sc.rr_start) {
+            const float p = fmaxf(fminf(fmaxf(fmaxf(beta.x, beta.y), beta.z), 1.0f), 0.05f);
+            if (rng_uniform(rng) > p) return false;
+            beta = mk(beta.x / p, beta.y / p, beta.z / p);
+        }
+        np = s.p;
+        return true;
+    }
     return false;
 }
 
@@ -519,7 +537,7 @@ __device__ __forceinline__ int sq_batch(const SceneView& sc, float* __restrict__
                                         float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb, ShadeOut* out = nullptr) {
     const bool hit = live && code != PRT_NO_HIT;
     if (live && !hit) {                                                 // cpu/renderer.cpp:99
-        V3 L = beta * mk(sc.sky_r, sc.sky_g, sc.sky_b);
+        V3 L = clamp_radiance(sc, beta * mk(sc.sky_r, sc.sky_g, sc.sky_b));
         st_stream(&contrib[slot_bounce >> 5], make_float4(L.x, L.y, L.z, 0.f));
     }
     const uint32_t mask = __ballot_sync(0xffffffffu, hit);
@@ -732,6 +750,7 @@ SceneView scene_view(const Ctx* c) {
     v.tri_tmin = 0.001f;                                  // kShapeRayTMin, shape.h:128
     v.sky_r = c->sky[0]; v.sky_g = c->sky[1]; v.sky_b = c->sky[2];
     v.one_bits = 0x3f800000u;
+    v.rr_start = c->rr_start; v.clamp = c->firefly_clamp > 0.f ? c->firefly_clamp : INFINITY;
     v.brute = 0;                                          // only wavefront_render's fused path turns it on
     return v;
 }

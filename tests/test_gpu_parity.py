@@ -221,6 +221,30 @@ def test_sample_ranges_compose(ctx, gold):
     assert np.array_equal(a, c) and np.array_equal(a, d)
 
 
+def test_estimator_options_match_oracle_and_are_off_by_default(ctx, oracle, gold):
+    """Russian roulette and the firefly clamp exist only behind options, default OFF. With them on, the
+    image still equals the oracle's (same rule, same RNG draw) bit for bit, fewer rays are traced, and the estimate
+    stays unbiased (roulette) / bounded (clamp)."""
+    sd = S.closed_cornell(); cam = S.Camera(width=96, height=64)           # enclosed: paths run to the depth limit
+    osc = oracle.scene(sd)
+    ctx.set_scene(sd); ctx.build_bvh(); ctx.set_camera(cam)
+    ctx.clear_accum(); ctx.render(64, 12, seed=4); base = ctx.read_accum(); rays0 = ctx.stats().rays_total
+    ctx.set_option("rr_start", 1)
+    ctx.clear_accum(); ctx.render(64, 12, seed=4); rr = ctx.read_accum(); rays1 = ctx.stats().rays_total
+    osc.set_estimator(rr_start=1)
+    want, orays = osc.render(cam, 64, 12, seed=4)
+    assert np.array_equal(rr, want) and rays1 == orays and rays1 < rays0
+    assert abs(rr.mean() - base.mean()) <= 0.03 * base.mean()               # unbiased: same mean within MC noise
+    ctx.set_option("firefly_clamp_milli", 2500)
+    ctx.clear_accum(); ctx.render(8, 12, seed=4); cl = ctx.read_accum()
+    osc.set_estimator(rr_start=1, clamp=2.5)
+    want, _ = osc.render(cam, 8, 12, seed=4)
+    assert np.array_equal(cl, want) and cl.max() <= 8 * 2.5 + 1e-3 and base.max() > 64 * 2.5
+    ctx.set_option("rr_start", -1); ctx.set_option("firefly_clamp_milli", 0)
+    ctx.clear_accum(); ctx.render(64, 12, seed=4)
+    assert np.array_equal(ctx.read_accum(), base)
+
+
 def test_pixel_regions_compose(ctx, gold):
     """TILE partition rule: rendering disjoint pixel ranges (bands of rows, ragged last range) leaves the
     other pixels untouched and the union equals the whole-frame render bit for bit, fused and staged."""

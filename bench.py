@@ -387,7 +387,8 @@ def roofline_and_json(args, R):
            "rays_per_path": rays_step / paths_step,
            "e2e": {"value": R["e2e_rays"] / R["e2e_s"] / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": scene_bytes(sd) + 64,
                    "d2h_bytes_per_step": W * H * 12, "what": "B200Renderer.Init(host scene)+ProgressiveRender+Film.ReadAccum per step, wall clock"},
-           "gpu_launches": R["launches_all"], "bvh_build_ms": R["build_ms"], "reduce_ms_per_step": R["red_ms"] / steps,
+           "gpu_launches": R["launches_all"], "bvh_build_ms": R["build_ms"],
+           "bvh_build_mprims_per_s": (sd.n_prims / (R["build_ms"] * 1e-3) / 1e6) if R["build_ms"] > 0 else None, "reduce_ms_per_step": R["red_ms"] / steps,
            "wall_ms_per_step": R["wall_ms"] / steps, "clocks": R["clk"], "roofline": roof}
     return out
 
@@ -404,7 +405,7 @@ def main():
     os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))

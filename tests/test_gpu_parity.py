@@ -371,3 +371,48 @@ def test_cpp_shim_dropin(ctx, tmp_path):
         assert np.array_equal(accum, ctx.read_accum())
         mine = ctx.resolve_display(1.0, 2.2)
         assert np.abs(mine.astype(int) - disp.astype(int)).max() <= 1     # reference GPU tonemap (film.cu:101-121)
+
+
+# ---------------------------------------------------------------- BASELINE.json's full sizes, by size-independent properties
+def test_full_size_1080p_properties(ctx):
+    """configs[1] geometry (reference Cornell, 1920x1080, depth 8) at a few spp: determinism, sample ranges and pixel
+    regions compose, two-stream waves equal one stream - on 2 M pixels instead of the small parity frames."""
+    sd = S.cornell(); cam = S.Camera(width=1920, height=1080)
+    ctx.set_scene(sd); ctx.build_bvh(); ctx.set_camera(cam)
+    P = 1920 * 1080
+    ctx.clear_accum(); ctx.render(6, 8, seed=77); a = ctx.read_accum(); rays = ctx.stats().rays_total
+    ctx.clear_accum(); ctx.render(6, 8, seed=77); assert np.array_equal(ctx.read_accum(), a)          # deterministic
+    ctx.clear_accum(); ctx.render(2, 8, seed=77); ctx.render(4, 8, seed=77, sample_begin=2)
+    assert np.array_equal(ctx.read_accum(), a)
+    ctx.set_option("wave_paths", 3_000_000); ctx.set_option("overlap", 0)                            # 4+ waves, one stream
+    ctx.clear_accum(); ctx.render(6, 8, seed=77); b = ctx.read_accum()
+    ctx.set_option("overlap", 1)
+    ctx.clear_accum(); ctx.render(6, 8, seed=77); c2 = ctx.read_accum()
+    ctx.set_option("wave_paths", 0)
+    assert np.array_equal(a, b) and np.array_equal(a, c2)
+    ctx.clear_accum()
+    for b0, n in ((0, P // 3), (P // 3, P // 3 + 11), (2 * (P // 3) + 11, P - 2 * (P // 3) - 11)):
+        ctx.render_region(6, 8, seed=77, pixel_begin=b0, pixel_count=n)
+    assert np.array_equal(ctx.read_accum(), a)
+    assert P * 6 < rays <= P * 6 * 8 and np.isfinite(a).all() and a.min() >= 0.0
+    assert a.max() <= 6 * 15.0 + 1e-3                                                                  # no pixel brighter than the light
+
+
+def test_full_size_10m_triangles_wide_equals_two_child():
+    """configs[4] geometry (10 M random triangles, depth 16): brute force is out of reach, so the two traversal
+    structures check each other - the image through the 4-wide quantised nodes equals the image through the two-child
+    LBVH bit for bit, with about half the node visits."""
+    sd = S.random_triangle_soup(10_000_000)
+    cam = S.Camera(pos=(0.0, 0.0, 150.0), front=(0.0, 0.0, -1.0), width=640, height=360)
+    out = []
+    with Context(0) as c:
+        c.enable_counters(True)
+        for wide in (1, 0):
+            c.set_option("bvh_wide", wide)
+            c.set_scene(sd); c.build_bvh(); c.set_camera(cam); c.clear_accum()
+            c.render(1, 16, seed=5)
+            st = c.stats()
+            out.append((c.read_accum(), st.rays_total, st.nodes_visited))
+    assert np.array_equal(out[0][0], out[1][0]) and out[0][1] == out[1][1]
+    assert out[0][2] < 0.7 * out[1][2]
+    assert out[0][0].max() > 0

@@ -152,6 +152,19 @@ class CpuArm:
             return max(1, int(target_s / full_spp)), None
         return 1, max(8, min(H, int(target_s / per_row_spp)))
 
+    def as_shipped(self):
+        """SURVEY 8d (1): the reference CPURenderer EXACTLY as shipped (depth literal 20, std::rand behind its global lock,
+        one std::async task per 16x16 tile), one ProgressiveRender() = 1 spp of the whole frame, wall clock. Preset scenes
+        with oracle/_ref only. It counts no rays, so the figure is spp/s."""
+        import oracle_lib
+        ref = oracle_lib.load_ref()
+        if ref is None or self.w["scene"] not in PRESET_OF:
+            return None
+        sec, _ = ref.render_shipped(PRESET_OF[self.w["scene"]], self.cam, 1, want_accum=False)
+        return {"spp_per_s": 1.0 / sec, "seconds_per_ProgressiveRender": sec, "depth": 20,
+                "what": "CPURenderer::ProgressiveRender unmodified (oracle/_ref), %dx%d, %d host threads available" %
+                        (self.cam.width, self.cam.height, self.cores)}
+
     def describe(self, spp, rows):
         H, W = self.cam.height, self.cam.width
         what = ("reference Intersect/Scatter/GetCameraRay (oracle/_ref) + TraceRay recursion, deterministic rand()"
@@ -426,6 +439,9 @@ def main():
             dt, rays = arm.run(spp, rows)
             out["cpu_baseline"] = {"value": rays / dt / 1e6, "unit": "Mrays/s", "cores": arm.cores, "kind": arm.kind,
                                    "sample": arm.describe(spp, rows), "seconds": dt}
+            shipped = arm.as_shipped()
+            if shipped:
+                out["cpu_baseline"]["as_shipped"] = shipped
         else:
             out["cpu_baseline"] = None
         sys.stdout.flush()

@@ -121,6 +121,7 @@ void prt_destroy(prt_ctx* ctx) {
                       &c->q2_o[0], &c->q2_o[1], &c->q2_d[0], &c->q2_d[1], &c->q2_b[0], &c->q2_b[1], &c->hits2, &c->contrib2,
                       &c->qcount2, &c->qcount, &c->stats_dev};
     for (DevBuf* b : bufs) dev_free(*b);
+    if (c->stats_host) cudaFreeHost(c->stats_host);
     for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
     for (cudaEvent_t e : {c->ev_res[0], c->ev_res[1], c->ev_join}) if (e) cudaEventDestroy(e);
     if (c->stream2) { cudaStreamSynchronize(c->stream2); cudaStreamDestroy(c->stream2); }
@@ -142,7 +143,7 @@ int prt_set_scene(prt_ctx* ctx, const prt_sphere* spheres, int n_spheres, const 
     if ((int64_t)n_spheres + n_quads + n_tris >= ((int64_t)1 << 28))
         return set_err(c, PRT_ERR_UNSUPPORTED, "prt_set_scene: more than 2^28 primitives");
     PRT_CUDA(c, cudaSetDevice(c->device));
-    c->scene_set = false; c->bvh_built = false;
+    c->scene_set = false; c->bvh_built = false; c->hint_rays[0] = 0;
     int rc;
     // spheres
     std::vector<SphereRec> hs((size_t)n_spheres);
@@ -395,6 +396,10 @@ int prt_set_option(prt_ctx* ctx, const char* key, int64_t value) {
     if (!strcmp(key, "wave_paths")) { if (value < 0) return set_err(c, PRT_ERR_INVALID, "wave_paths < 0"); c->wave_paths_opt = value; }
     else if (!strcmp(key, "ctas_per_sm")) { if (value < 1 || value > 32) return set_err(c, PRT_ERR_INVALID, "ctas_per_sm out of range"); c->ctas_per_sm = (int)value; }
     else if (!strcmp(key, "use_graph")) c->use_graph = value ? 1 : 0;
+    else if (!strcmp(key, "tail_bounce")) c->tail_bounce = value < 0 ? 0 : value;
+    else if (!strcmp(key, "tail_max_paths")) c->tail_max_paths = value < 0 ? 0 : value;
+    else if (!strcmp(key, "tail_adaptive")) c->tail_adaptive = value ? 1 : 0;
+    else if (!strcmp(key, "tail_rays")) c->tail_rays = value < 0 ? 0 : value;
     else if (!strcmp(key, "fused")) c->fused = value < 0 ? -1 : (value ? 1 : 0);
     else if (!strcmp(key, "fused_max_prims")) c->fused_max_prims = (int)value;
     else if (!strcmp(key, "brute_max_prims")) c->brute_max_prims = (int)value;

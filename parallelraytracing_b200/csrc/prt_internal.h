@@ -72,6 +72,12 @@ struct Ctx {
     int ctas_per_sm = 8;
     int counters_on = 0;
     int use_graph = 1;
+    unsigned long long* stats_host = nullptr;   // pinned copy of stats_dev
+    int tail_bounce = 2;               // fused path: bounces >= this run in ONE in-thread kernel, k_tail (0 = never); with
+    int tail_adaptive = 1;             //   tail_adaptive the start is the first bounce whose queue is expected to hold <= tail_rays
+    int tail_rays = 512 << 10;         //   rays (survival per bounce taken from the previous call on this scene; none yet: 1.0)
+    int tail_max_paths = 1 << 26;      // waves with more paths never use the tail
+    unsigned long long hint_rays[PRT_MAX_DEPTH] = {0};   // rays per bounce of the last fused render of this scene; [0] = 0: none yet
     int fused = -1;                             // 1: k_primary/k_bounce, 0: raygen/extend/shade as separate stages, -1: by scene size
     int fused_max_prims = 64;                   // auto: fuse when traversal is a handful of nodes (shading dominates)
     int brute_max_prims = 8;                    // fused kernels: sphere/quad scenes this small skip the BVH (uniform loop over the list)

@@ -663,6 +663,57 @@ k_bounce(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&stats[bounce], (unsigned long long)count);
 }
 
+// Tail of a SMALL wave. With few rays left, one launch per bounce costs more than the bounce: at 1080p, 1 spp (the
+// reference's ProgressiveRender granularity) a k_bounce launch takes ~9 us for < 100 K rays and 3.7 us on an empty
+// queue, times 17 bounces at depth 20. k_tail takes the queue of bounce `bounce0` and follows every ray in it to the
+// end of its path inside the thread: no queue, no compaction, one launch. Same device functions, same RNG keys, one
+// contribution per path => the image and the per-bounce ray counts are bit-identical to the launch-per-bounce form.
+template <bool COUNT, bool BRUTE>
+__global__ void __launch_bounds__(WF_THREADS)
+k_tail(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ qd, const float4* __restrict__ qb,
+       float4* __restrict__ contrib, const uint32_t* __restrict__ qcount, int bounce0, int max_depth,
+       unsigned long long* __restrict__ stats) {
+    __shared__ int sstack[BRUTE ? 1 : FUSED_STACK * WF_THREADS];
+    __shared__ uint32_t rays_at[PRT_MAX_DEPTH];                        // this block's rays per bounce
+    for (int k = threadIdx.x; k < PRT_MAX_DEPTH; k += WF_THREADS) rays_at[k] = 0u;
+    __syncthreads();
+    const uint32_t count = qcount[bounce0];
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t stride = gridDim.x * WF_THREADS;
+    uint32_t nn = 0, npr = 0;
+    for (uint32_t base = blockIdx.x * WF_THREADS + (threadIdx.x & ~31u); base < count; base += stride) {
+        const uint32_t i = base + lane;
+        bool alive = i < count;
+        V3 o = mk(0, 0, 0), d = o, beta = o;
+        uint32_t key = 0, slot = 0;
+        if (alive) {
+            const float4 o4 = ld_stream(&qo[i]), d4 = ld_stream(&qd[i]), b4 = ld_stream(&qb[i]);
+            o = xyz(o4); d = xyz(d4); beta = xyz(b4); key = __float_as_uint(d4.w); slot = __float_as_uint(o4.w) >> 5;
+        }
+        for (int bounce = bounce0; bounce < max_depth; ++bounce) {
+            const uint32_t act = __ballot_sync(0xffffffffu, alive);
+            if (!act) break;
+            if (lane == 0) atomicAdd(&rays_at[bounce], (uint32_t)__popc(act));
+            if (alive) {
+                const Best b = traverse<COUNT, BRUTE, FUSED_STACK>(sc, o, d, BRUTE ? sstack : sstack + threadIdx.x, nn, npr);
+                V3 np, ndir, L;
+                if (shade_segment(sc, o, d, key, bounce, max_depth, b.t, b.code, b.u, b.v, beta, np, ndir, L)) { o = np; d = ndir; }
+                else { st_stream(&contrib[slot], make_float4(L.x, L.y, L.z, 0.f)); alive = false; }
+            }
+        }
+    }
+    if (COUNT) {
+        for (int o = 16; o > 0; o >>= 1) { nn += __shfl_xor_sync(0xffffffffu, nn, o); npr += __shfl_xor_sync(0xffffffffu, npr, o); }
+        if (lane == 0 && (nn | npr)) {
+            atomicAdd(&stats[PRT_MAX_DEPTH + 0], (unsigned long long)nn);
+            atomicAdd(&stats[PRT_MAX_DEPTH + 1], (unsigned long long)npr);
+        }
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < PRT_MAX_DEPTH; k += WF_THREADS)
+        if (rays_at[k]) atomicAdd(&stats[k], (unsigned long long)rays_at[k]);
+}
+
 // ------------------------------------------------------------------ resolve (accumulate)
 // accum[3p+c] += sum over the wave's samples, in sample order (Film::AddSample, film.cu:37-55)
 __global__ void __launch_bounds__(WF_THREADS)
@@ -869,7 +920,17 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
                 if (timing) stamp(st);
                 ++launches;
                 cur = 1;
-                for (int b = 1; b < max_depth; ++b) {
+                // small waves: launch-per-bounce up to tail_bounce, then ONE kernel finishes the paths in-thread
+                int tail_b = (c->tail_bounce > 0 && n_paths <= c->tail_max_paths) ? c->tail_bounce : max_depth;
+                if (tail_b < max_depth && c->tail_adaptive) {
+                    const unsigned long long p0 = c->hint_rays[0];
+                    tail_b = max_depth;
+                    for (int b = 1; b < max_depth; ++b) {          // expected queue length at bounce b
+                        const double expect = p0 ? (double)n_paths * (double)c->hint_rays[b] / (double)p0 : (double)n_paths;
+                        if (expect <= (double)c->tail_rays) { tail_b = b; break; }
+                    }
+                }
+                for (int b = 1; b < std::min(max_depth, tail_b); ++b) {
                     if (timing) spans.push_back({stamp(st), 0});
                     {
                         auto kb = c->counters_on ? (brute ? k_bounce<true, true> : k_bounce<true, false>)
@@ -880,6 +941,14 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
                     if (timing) stamp(st);
                     ++launches;
                     cur ^= 1;
+                }
+                if (tail_b < max_depth) {
+                    if (timing) spans.push_back({stamp(st), 0});
+                    auto kt = c->counters_on ? (brute ? k_tail<true, true> : k_tail<true, false>)
+                                             : (brute ? k_tail<false, true> : k_tail<false, false>);
+                    kt<<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], qb[cur], contrib, qcount, tail_b, max_depth, dstats);
+                    if (timing) stamp(st);
+                    ++launches;
                 }
             } else {
                 k_raygen<<<(n_paths + WF_THREADS - 1) / WF_THREADS, WF_THREADS, 0, st>>>(
@@ -913,18 +982,21 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
     }
     cudaStream_t st = c->stream;
     PRT_CUDA(c, cudaEventRecord(c->ev1, st));
+    // counters come back through pinned memory behind the last kernel: one host wake-up per call, not two
+    if (!c->stats_host) PRT_CUDA(c, cudaHostAlloc((void**)&c->stats_host, (PRT_MAX_DEPTH + 4) * 8, cudaHostAllocDefault));
+    PRT_CUDA(c, cudaMemcpyAsync(c->stats_host, dstats, (PRT_MAX_DEPTH + 4) * 8, cudaMemcpyDeviceToHost, st));
     PRT_CUDA(c, cudaStreamSynchronize(st));
     PRT_CUDA(c, cudaGetLastError());
     c->accum_spp += spp;
 
-    unsigned long long h[PRT_MAX_DEPTH + 4];
-    PRT_CUDA(c, cudaMemcpy(h, dstats, sizeof(h), cudaMemcpyDeviceToHost));
+    const unsigned long long* h = c->stats_host;
     prt_stats& s = c->stats;
     s.rays_total = 0;
     for (int b = 0; b < PRT_MAX_DEPTH; ++b) { s.rays_per_bounce[b] = h[b]; s.rays_total += h[b]; }
     s.nodes_visited = h[PRT_MAX_DEPTH]; s.prims_tested = h[PRT_MAX_DEPTH + 1];
     s.paths = paths;
     s.kernel_launches = launches;
+    if (fused) for (int b = 0; b < PRT_MAX_DEPTH; ++b) c->hint_rays[b] = h[b];
     cudaEventElapsedTime(&s.render_ms, c->ev0, c->ev1);
     float ms[3] = {0.f, 0.f, 0.f};
     int n_primary = 0;

@@ -4,6 +4,7 @@
 #include "b200_renderer.h"
 #include "flatten.h"
 #include <cstdio>
+#include <cuda_runtime_api.h>
 
 B200Renderer::~B200Renderer() { prt_destroy(m_Ctx); }
 
@@ -42,6 +43,9 @@ void B200Renderer::ProgressiveRender()
     if (!m_Ctx || !m_Ok || !m_Film || !m_Camera) return;
     if (m_Film->GetWidth() != (uint32_t)m_Camera->GetWidth() || m_Film->GetHeight() != (uint32_t)m_Camera->GetHeight()) return;
     const int k = m_SamplesPerCall;
+    // Film::AddSampleBufferGPU of the previous frame ran on the legacy default stream and returned without waiting
+    // (film.cu:90-99); the context's streams are non-blocking, so the sample buffer must not be rewritten before it is read
+    cudaStreamSynchronize(cudaStreamLegacy);
     if (prt_clear_accum(m_Ctx) != PRT_OK || prt_render(m_Ctx, k, m_Depth, m_Seed, m_NextSample) != PRT_OK) {
         std::fprintf(stderr, "[B200Renderer] %s\n", prt_last_error(m_Ctx));
         return;

@@ -296,6 +296,41 @@ def test_tiny_scene_list_loop_equals_bvh(ctx):
         assert np.array_equal(out[0][0], out[1][0]) and out[0][1] == out[1][1], sd.name
 
 
+def test_small_wave_tail_kernel_is_invisible(ctx):
+    """Small waves finish bounces >= tail_bounce inside ONE kernel (k_tail, in-thread loop) instead of one launch per
+    bounce. Same device functions and RNG keys: image, per-bounce ray counts and traversal counters must not change,
+    wherever the tail starts, at the reference's depth literal 20 (cpu/renderer.h:34)."""
+    ctx.enable_counters(True)
+    for sd in (S.cornell(), S.closed_cornell(), S.make_scene(S.ScenePreset.MATERIAL_TEST), S.make_scene(S.ScenePreset.DEFAULT)):
+        cam = S.Camera(width=96, height=72)
+        ctx.set_scene(sd); ctx.build_bvh(); ctx.set_camera(cam)
+        out = []
+        for tail in (0, 1, 2, 3, 7, 19, 25):
+            ctx.set_option("fused", 1); ctx.set_option("tail_bounce", tail); ctx.set_option("tail_adaptive", 0)
+            ctx.clear_accum(); ctx.render(2, 20, seed=5)
+            st = ctx.stats()
+            out.append((ctx.read_accum(), list(st.rays_per_bounce), st.nodes_visited, st.prims_tested, st.kernel_launches))
+        ctx.set_option("tail_bounce", 2); ctx.set_option("fused", -1)
+        assert out[0][4] == 21 and out[3][4] == 5 and out[1][4] == 3        # 1 + 19 + resolve / primary, b1, b2, tail, resolve
+        for o in out[1:]:
+            assert np.array_equal(o[0], out[0][0]) and o[1:4] == out[0][1:4], sd.name
+        ctx.set_option("tail_max_paths", 100)                                # wave larger than the limit: no tail
+        ctx.set_option("fused", 1); ctx.clear_accum(); ctx.render(2, 20, seed=5)
+        assert ctx.stats().kernel_launches == 21
+        ctx.set_option("tail_max_paths", 1 << 26); ctx.set_option("tail_adaptive", 1)
+        ctx.clear_accum(); ctx.render(2, 20, seed=5)                         # 13 824 paths <= tail_rays: tail right after the primary
+        st = ctx.stats()
+        assert st.kernel_launches == 3 and np.array_equal(ctx.read_accum(), out[0][0]) and list(st.rays_per_bounce) == out[0][1]
+        ctx.set_option("tail_rays", 1000)                                    # adaptive: starts where the last call's queue fell to 1000
+        ctx.clear_accum(); ctx.render(2, 20, seed=5)
+        st = ctx.stats()
+        first = next((b for b in range(1, 20) if out[0][1][b] <= 1000), 20)
+        assert np.array_equal(ctx.read_accum(), out[0][0]) and list(st.rays_per_bounce) == out[0][1]
+        assert st.kernel_launches == (first + 2 if first < 20 else 21)      # primary + (first-1) bounces + tail + resolve
+        ctx.set_option("tail_rays", 512 << 10); ctx.set_option("fused", -1)
+    ctx.enable_counters(False)
+
+
 def test_display_resolve_exact(ctx, oracle):
     sd = S.cornell(); cam = S.Camera(width=64, height=64)
     ctx.set_scene(sd); ctx.build_bvh(); ctx.set_camera(cam); ctx.clear_accum(); ctx.render(4, 8, seed=1)

@@ -301,7 +301,7 @@ class RefScene:
 def build_ref():
     """Build oracle/_ref/libprt_ref.so from the sources under /root/reference (only where they exist)."""
     if os.path.isdir("/root/reference/src"):
-        subprocess.run(["make", "-C", ORACLE_DIR, "ref", "shim"], check=True, capture_output=True)
+        subprocess.run(["make", "-C", ORACLE_DIR, "ref", "shim", "refgpu"], check=True, capture_output=True)
     return REF_SO if os.path.exists(REF_SO) else None
 
 

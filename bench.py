@@ -165,6 +165,27 @@ class CpuArm:
                 "what": "CPURenderer::ProgressiveRender unmodified (oracle/_ref), %dx%d, %d host threads available" %
                         (self.cam.width, self.cam.height, self.cores)}
 
+    def reference_gpu(self):
+        """the reference's own CUDA backends (compiled unmodified for sm_100 into oracle/_ref by `make -C oracle
+        refgpu`) and B200Renderer behind the same C++ Renderer interface, on THIS GPU, the viewer's call pattern: one
+        ProgressiveRender = 1 spp at the reference's depth literal 20, wall clock per call. Preset scenes only."""
+        import subprocess
+        exe = os.path.join(ROOT, "oracle", "_ref", "ref_gpu_driver")
+        if not os.path.exists(exe) or self.w["scene"] not in PRESET_OF:
+            return None
+        res = {"depth": 20, "spp_per_call": 1, "what": "ms per Renderer::ProgressiveRender(), %dx%d, 30 calls after 3" %
+               (self.cam.width, self.cam.height)}
+        for backend in ("wavefront", "megakernel", "b200"):
+            try:
+                r = subprocess.run([exe, backend, str(int(PRESET_OF[self.w["scene"]])), str(self.cam.width), str(self.cam.height),
+                                    "3", "30", "1", "0"], capture_output=True, text=True, timeout=300)
+                j = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
+                res["ref_" + backend if backend != "b200" else "B200Renderer"] = {
+                    "ms_per_call": j["ms_per_call"], "spp_per_s": j["spp_per_s"], "mean_radiance": j["mean_radiance"]}
+            except Exception as e:  # noqa: BLE001
+                res[backend] = {"error": str(e)[:200]}
+        return res
+
     def describe(self, spp, rows):
         H, W = self.cam.height, self.cam.width
         what = ("reference Intersect/Scatter/GetCameraRay (oracle/_ref) + TraceRay recursion, deterministic rand()"
@@ -442,6 +463,9 @@ def main():
             shipped = arm.as_shipped()
             if shipped:
                 out["cpu_baseline"]["as_shipped"] = shipped
+            refgpu = arm.reference_gpu()
+            if refgpu:
+                out["reference_cuda_backends"] = refgpu
         else:
             out["cpu_baseline"] = None
         sys.stdout.flush()

@@ -400,6 +400,7 @@ int prt_set_option(prt_ctx* ctx, const char* key, int64_t value) {
     else if (!strcmp(key, "tail_max_paths")) c->tail_max_paths = value < 0 ? 0 : value;
     else if (!strcmp(key, "tail_adaptive")) c->tail_adaptive = value ? 1 : 0;
     else if (!strcmp(key, "tail_rays")) c->tail_rays = value < 0 ? 0 : value;
+    else if (!strcmp(key, "tail_rays_staged")) c->tail_rays_staged = value < 0 ? 0 : value;
     else if (!strcmp(key, "fused")) c->fused = value < 0 ? -1 : (value ? 1 : 0);
     else if (!strcmp(key, "fused_max_prims")) c->fused_max_prims = (int)value;
     else if (!strcmp(key, "brute_max_prims")) c->brute_max_prims = (int)value;

@@ -909,6 +909,17 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
                    *qb[2] = {(float4*)bb[0].p, (float4*)bb[1].p};
             float4 *hits = (float4*)(set ? c->hits2.p : c->hits.p), *contrib = (float4*)(set ? c->contrib2.p : c->contrib.p);
             int cur = 0;
+            // small waves: launch-per-bounce up to tail_bounce, then ONE kernel finishes the paths in-thread
+            int tail_b = (c->tail_bounce > 0 && n_paths <= c->tail_max_paths) ? c->tail_bounce : max_depth;
+            if (c->counters_on && wide && !fused) tail_b = max_depth;   // counters then mean WIDE nodes: keep one kind of walk
+            if (tail_b < max_depth && c->tail_adaptive) {
+                const unsigned long long p0 = c->hint_rays[0];
+                tail_b = max_depth;
+                for (int b = 1; b < max_depth; ++b) {          // expected queue length at bounce b
+                    const double expect = p0 ? (double)n_paths * (double)c->hint_rays[b] / (double)p0 : (double)n_paths;
+                    if (expect <= (double)(fused ? c->tail_rays : c->tail_rays_staged)) { tail_b = b; break; }
+                }
+            }
             if (fused) {
                 if (timing) spans.push_back({stamp(st), 2});
                 {
@@ -920,16 +931,6 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
                 if (timing) stamp(st);
                 ++launches;
                 cur = 1;
-                // small waves: launch-per-bounce up to tail_bounce, then ONE kernel finishes the paths in-thread
-                int tail_b = (c->tail_bounce > 0 && n_paths <= c->tail_max_paths) ? c->tail_bounce : max_depth;
-                if (tail_b < max_depth && c->tail_adaptive) {
-                    const unsigned long long p0 = c->hint_rays[0];
-                    tail_b = max_depth;
-                    for (int b = 1; b < max_depth; ++b) {          // expected queue length at bounce b
-                        const double expect = p0 ? (double)n_paths * (double)c->hint_rays[b] / (double)p0 : (double)n_paths;
-                        if (expect <= (double)c->tail_rays) { tail_b = b; break; }
-                    }
-                }
                 for (int b = 1; b < std::min(max_depth, tail_b); ++b) {
                     if (timing) spans.push_back({stamp(st), 0});
                     {
@@ -942,19 +943,11 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
                     ++launches;
                     cur ^= 1;
                 }
-                if (tail_b < max_depth) {
-                    if (timing) spans.push_back({stamp(st), 0});
-                    auto kt = c->counters_on ? (brute ? k_tail<true, true> : k_tail<true, false>)
-                                             : (brute ? k_tail<false, true> : k_tail<false, false>);
-                    kt<<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], qb[cur], contrib, qcount, tail_b, max_depth, dstats);
-                    if (timing) stamp(st);
-                    ++launches;
-                }
             } else {
                 k_raygen<<<(n_paths + WF_THREADS - 1) / WF_THREADS, WF_THREADS, 0, st>>>(
                     cam, (int)p0, npix, div_npix, n_paths, (uint32_t)(sample_begin + s0), seed_lo, seed_hi, qo[0], qd[0], qb[0], qcount);
                 ++launches;
-                for (int b = 0; b < max_depth; ++b) {
+                for (int b = 0; b < std::min(max_depth, tail_b); ++b) {
                     if (timing) spans.push_back({stamp(st), b == 0 ? 2 : 0});
                     if (c->persistent) {
                         uint32_t* work = qcount + (PRT_MAX_DEPTH + 2) + b;
@@ -968,6 +961,14 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
                     launches += 2;
                     cur ^= 1;
                 }
+            }
+            if (tail_b < max_depth) {                                  // staged scenes walk the two-child tree here
+                if (timing) spans.push_back({stamp(st), 0});
+                auto kt = c->counters_on ? (brute && fused ? k_tail<true, true> : k_tail<true, false>)
+                                         : (brute && fused ? k_tail<false, true> : k_tail<false, false>);
+                kt<<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], qb[cur], contrib, qcount, tail_b, max_depth, dstats);
+                if (timing) stamp(st);
+                ++launches;
             }
             // resolves read-modify-write the same accumulation pixels: keep them in wave order across the two streams
             if (nsets > 1 && wave > 0) PRT_CUDA(c, cudaStreamWaitEvent(st, c->ev_res[(wave - 1) & 1], 0));
@@ -996,7 +997,7 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
     s.nodes_visited = h[PRT_MAX_DEPTH]; s.prims_tested = h[PRT_MAX_DEPTH + 1];
     s.paths = paths;
     s.kernel_launches = launches;
-    if (fused) for (int b = 0; b < PRT_MAX_DEPTH; ++b) c->hint_rays[b] = h[b];
+    for (int b = 0; b < PRT_MAX_DEPTH; ++b) c->hint_rays[b] = h[b];
     cudaEventElapsedTime(&s.render_ms, c->ev0, c->ev1);
     float ms[3] = {0.f, 0.f, 0.f};
     int n_primary = 0;

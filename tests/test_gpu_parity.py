@@ -331,6 +331,24 @@ def test_small_wave_tail_kernel_is_invisible(ctx):
     ctx.enable_counters(False)
 
 
+def test_small_wave_tail_kernel_staged_scenes(ctx, gold):
+    """The same tail on the staged pipeline (scenes above fused_max_prims): k_tail walks the two-child tree in-thread, also where
+    the extend kernels use the 4-wide nodes - the closest-hit rule is order-free, so image and ray counts must not move."""
+    for sd, launches0 in ((S.make_scene(S.ScenePreset.RANDOM_BALLS_SMALL), None), (SCENES["dragon3"](gold), None)):
+        cam = S.Camera(width=96, height=72)
+        ctx.set_scene(sd); ctx.build_bvh(); ctx.set_camera(cam)
+        out = []
+        for tail in (0, 1, 3, 11):
+            ctx.set_option("tail_bounce", tail); ctx.set_option("tail_adaptive", 0)
+            ctx.clear_accum(); ctx.render(2, 12, seed=9)
+            st = ctx.stats()
+            out.append((ctx.read_accum(), list(st.rays_per_bounce), st.kernel_launches))
+        ctx.set_option("tail_bounce", 2); ctx.set_option("tail_adaptive", 1)
+        assert [o[2] for o in out] == [26, 5, 9, 25]          # raygen + 2/bounce + resolve; raygen + 2*tail + k_tail + resolve
+        for o in out[1:]:
+            assert np.array_equal(o[0], out[0][0]) and o[1] == out[0][1], sd.name
+
+
 def test_display_resolve_exact(ctx, oracle):
     sd = S.cornell(); cam = S.Camera(width=64, height=64)
     ctx.set_scene(sd); ctx.build_bvh(); ctx.set_camera(cam); ctx.clear_accum(); ctx.render(4, 8, seed=1)

@@ -236,7 +236,8 @@ int  prt_get_stats(prt_ctx* ctx, prt_stats* out);
  * "brute_max_prims", "persistent", "pt_refill", "pt_refill_wide", "bvh_wide", "wide_min_prims", "overlap",
  * "stage_timing", "rr_start", "firefly_clamp_milli", and for small waves (one sample per call, the reference's
  * ProgressiveRender granularity) "tail_bounce" (0 = one launch per bounce always), "tail_adaptive", "tail_rays", "tail_rays_staged",
- * "tail_max_paths": bounces from the tail start on run inside one kernel. None of them changes the image except
+ * "tail_max_paths": bounces from the tail start on run inside one kernel; "sort_rays", "sort_key_bits",
+ * "sort_min_rays": re-sort the ray queue of every bounce by origin cell and direction octant (staged pipeline, off). None of them changes the image except
  * rr_start / firefly_clamp_milli (estimator options, default off). Unknown keys -> PRT_ERR_INVALID. */
 int  prt_set_option(prt_ctx* ctx, const char* key, int64_t value);
 

@@ -119,7 +119,9 @@ void prt_destroy(prt_ctx* ctx) {
                       &c->flags, &c->nodes, &c->wnodes, &c->tri_v, &c->tri_n, &c->morton, &c->accum_own, &c->display,
                       &c->q_o[0], &c->q_o[1], &c->q_d[0], &c->q_d[1], &c->q_b[0], &c->q_b[1], &c->hits, &c->contrib,
                       &c->q2_o[0], &c->q2_o[1], &c->q2_d[0], &c->q2_d[1], &c->q2_b[0], &c->q2_b[1], &c->hits2, &c->contrib2,
-                      &c->qcount2, &c->qcount, &c->stats_dev};
+                      &c->qcount2, &c->qcount, &c->stats_dev, &c->ray_keys[0][0], &c->ray_keys[0][1], &c->ray_keys[1][0],
+                      &c->ray_keys[1][1], &c->ray_vals[0][0], &c->ray_vals[0][1], &c->ray_vals[1][0], &c->ray_vals[1][1],
+                      &c->ray_hist[0], &c->ray_hist[1]};
     for (DevBuf* b : bufs) dev_free(*b);
     if (c->stats_host) cudaFreeHost(c->stats_host);
     for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
@@ -400,6 +402,9 @@ int prt_set_option(prt_ctx* ctx, const char* key, int64_t value) {
     else if (!strcmp(key, "tail_max_paths")) c->tail_max_paths = value < 0 ? 0 : value;
     else if (!strcmp(key, "tail_adaptive")) c->tail_adaptive = value ? 1 : 0;
     else if (!strcmp(key, "tail_rays")) c->tail_rays = value < 0 ? 0 : value;
+    else if (!strcmp(key, "sort_rays")) c->sort_rays = value ? 1 : 0;
+    else if (!strcmp(key, "sort_key_bits")) c->sort_key_bits = (int)value;
+    else if (!strcmp(key, "sort_min_rays")) c->sort_min_rays = value < 0 ? 0 : (int)value;
     else if (!strcmp(key, "tail_rays_staged")) c->tail_rays_staged = value < 0 ? 0 : value;
     else if (!strcmp(key, "fused")) c->fused = value < 0 ? -1 : (value ? 1 : 0);
     else if (!strcmp(key, "fused_max_prims")) c->fused_max_prims = (int)value;

@@ -115,8 +115,13 @@ constexpr int RS_TILE = RS_THREADS * RS_ITEMS;   // 4096 keys per block
 constexpr int RS_WARPS = RS_THREADS / 32;
 
 __global__ void __launch_bounds__(RS_THREADS)
-k_rs_hist(const uint32_t* __restrict__ keys, int n, int shift, uint32_t* __restrict__ block_hist, int nblocks) {
+k_rs_hist(const uint32_t* __restrict__ keys, int n, int shift, uint32_t* __restrict__ block_hist, int nblocks,
+          const uint32_t* __restrict__ n_dev = nullptr) {
     __shared__ uint32_t h[256];
+    if (n_dev) {                       // ray queues: the length lives on the device, the grid is sized for the capacity
+        n = (int)*n_dev; nblocks = (n + RS_TILE - 1) / RS_TILE;
+        if ((int)blockIdx.x >= nblocks) return;
+    }
     h[threadIdx.x] = 0;
     __syncthreads();
     int base = blockIdx.x * RS_TILE;
@@ -133,8 +138,10 @@ k_rs_hist(const uint32_t* __restrict__ keys, int n, int shift, uint32_t* __restr
 // the blocks (in place) and writes the row total to digit_total[d]; the 256 digit bases are then a
 // 256-element scan that every scatter CTA redoes in shared memory. (A single-CTA scan of all
 // 256*nblocks counters took 574 us per pass at 10 M keys: 40 % of the whole build.)
-__global__ void __launch_bounds__(256) k_rs_scan_rows(uint32_t* __restrict__ hist, int nblocks, uint32_t* __restrict__ digit_total) {
+__global__ void __launch_bounds__(256) k_rs_scan_rows(uint32_t* __restrict__ hist, int nblocks, uint32_t* __restrict__ digit_total,
+                                                      const uint32_t* __restrict__ n_dev = nullptr) {
     __shared__ uint32_t warp_sum[8];
+    if (n_dev) nblocks = ((int)*n_dev + RS_TILE - 1) / RS_TILE;
     uint32_t* row = hist + (size_t)blockIdx.x * nblocks;
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const int per = (nblocks + 255) / 256;
@@ -157,8 +164,13 @@ __global__ void __launch_bounds__(256) k_rs_scan_rows(uint32_t* __restrict__ his
 __global__ void __launch_bounds__(RS_THREADS)
 k_rs_scatter(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
              uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int n, int shift,
-             const uint32_t* __restrict__ block_off, int nblocks, const uint32_t* __restrict__ digit_total) {
+             const uint32_t* __restrict__ block_off, int nblocks, const uint32_t* __restrict__ digit_total,
+             const uint32_t* __restrict__ n_dev = nullptr) {
     __shared__ uint32_t cnt[RS_WARPS][256];
+    if (n_dev) {
+        n = (int)*n_dev; nblocks = (n + RS_TILE - 1) / RS_TILE;
+        if ((int)blockIdx.x >= nblocks) return;
+    }
     __shared__ uint32_t dbase[256];
     __shared__ uint32_t dwarp[8];
     int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
@@ -208,6 +220,64 @@ k_rs_scatter(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ 
             keys_out[pos] = key[r]; vals_out[pos] = val[r];
         }
     }
+}
+
+// ------------------------------------------------------------------ ray re-sorting (the reference lists it as wanted, wavefront.md:86-96)
+// After a diffuse bounce the queue order is the order in which paths happened to finish shading: neighbouring lanes start
+// anywhere in the scene. Sorting the queue by the Morton code of the ORIGIN cell (then the direction octant) puts rays
+// that start in the same place and head the same way into the same warp. The order of a queue has no influence on any
+// path (RNG is keyed by pixel/sample/bounce, contributions are slot-indexed): the image is bit-identical with and without.
+__global__ void k_ray_keys(const float4* __restrict__ qo, const float4* __restrict__ qd, const uint32_t* __restrict__ n_dev,
+                           const int* __restrict__ bounds, int key_bits, uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+    const uint32_t n = *n_dev;
+    const float lx = ord2f(bounds[0]), ly = ord2f(bounds[1]), lz = ord2f(bounds[2]);
+    const float hx = ord2f(bounds[3]), hy = ord2f(bounds[4]), hz = ord2f(bounds[5]);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float4 o = __ldcs(&qo[i]), d = __ldcs(&qd[i]);
+        const uint32_t m = (expand10(quant10(o.x, lx, hx)) << 2) | (expand10(quant10(o.y, ly, hy)) << 1) | expand10(quant10(o.z, lz, hz));
+        const uint32_t oct = (d.x < 0.f ? 4u : 0u) | (d.y < 0.f ? 2u : 0u) | (d.z < 0.f ? 1u : 0u);
+        keys[i] = ((m >> (33 - key_bits)) << 3) | oct;         // key_bits - 3 Morton bits above the octant
+        vals[i] = i;
+    }
+}
+
+__global__ void k_ray_gather(const uint32_t* __restrict__ order, const uint32_t* __restrict__ n_dev,
+                             const float4* __restrict__ so, const float4* __restrict__ sd, const float4* __restrict__ sb,
+                             float4* __restrict__ to, float4* __restrict__ td, float4* __restrict__ tb) {
+    const uint32_t n = *n_dev;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t j = order[i];
+        const float4 o = __ldcs(&so[j]), d = __ldcs(&sd[j]), b = __ldcs(&sb[j]);
+        __stcs(&to[i], o); __stcs(&td[i], d); __stcs(&tb[i], b);
+    }
+}
+
+// Sort the ray queue (so, sd, sb)[0 .. *n_dev) into (to, td, tb). `capacity` sizes the grids; nothing returns to the host.
+int sort_ray_queue(Ctx* c, cudaStream_t st, int set, int64_t capacity, const uint32_t* n_dev, const float4* so, const float4* sd,
+                   const float4* sb, float4* to, float4* td, float4* tb) {
+    int rc;
+    const size_t cap = (size_t)capacity;
+    DevBuf* rk = c->ray_keys[set]; DevBuf* rv = c->ray_vals[set];
+    const int nblocks = (int)((cap + RS_TILE - 1) / RS_TILE);
+    for (int k = 0; k < 2; ++k)
+        if ((rc = dev_reserve(c, rk[k], cap * 4)) || (rc = dev_reserve(c, rv[k], cap * 4))) return rc;
+    if ((rc = dev_reserve(c, c->ray_hist[set], ((size_t)nblocks * 256 + 256) * 4))) return rc;
+    const int key_bits = std::min(24, std::max(8, c->sort_key_bits));
+    const int passes = (key_bits + 7) / 8;
+    const int G = (int)std::min<size_t>((cap + 255) / 256, (size_t)c->num_sms * 16);
+    k_ray_keys<<<G, 256, 0, st>>>(so, sd, n_dev, (const int*)c->scene_bounds.p, key_bits, (uint32_t*)rk[0].p, (uint32_t*)rv[0].p);
+    uint32_t* hist = (uint32_t*)c->ray_hist[set].p;
+    int cur = 0;
+    for (int pass = 0; pass < passes; ++pass) {
+        const int shift = pass * 8;
+        k_rs_hist<<<nblocks, RS_THREADS, 0, st>>>((const uint32_t*)rk[cur].p, 0, shift, hist, nblocks, n_dev);
+        k_rs_scan_rows<<<256, 256, 0, st>>>(hist, nblocks, hist + (size_t)nblocks * 256, n_dev);
+        k_rs_scatter<<<nblocks, RS_THREADS, 0, st>>>((const uint32_t*)rk[cur].p, (const uint32_t*)rv[cur].p, (uint32_t*)rk[cur ^ 1].p,
+                                                     (uint32_t*)rv[cur ^ 1].p, 0, shift, hist, nblocks, hist + (size_t)nblocks * 256, n_dev);
+        cur ^= 1;
+    }
+    k_ray_gather<<<G, 256, 0, st>>>((const uint32_t*)rv[cur].p, n_dev, so, sd, sb, to, td, tb);
+    return PRT_OK;
 }
 
 // ------------------------------------------------------------------ Karras hierarchy

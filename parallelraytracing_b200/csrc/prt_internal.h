@@ -33,6 +33,10 @@ struct Ctx {
     DevBuf scene_bounds;                        // 6 ordered-int floats
     DevBuf keys[2], vals[2];                    // radix sort ping-pong
     DevBuf block_hist;                          // digit-major per-block histograms
+    DevBuf ray_keys[2][2], ray_vals[2][2], ray_hist[2];   // ray re-sorting, per buffer set: key/index ping-pong + histograms
+    int sort_rays = 0;                          // staged pipeline: sort the queue of every bounce >= 1 (0 off, 1 on)
+    int sort_key_bits = 24;                     // origin-cell Morton bits + 3 octant bits (8..24 => 1..3 radix passes)
+    int sort_min_rays = 1 << 20;                // ... only while the queue is expected to hold at least this many rays
     DevBuf children, parent, node_min, node_max, flags;
     DevBuf nodes;                               // BvhNode per internal node
     DevBuf wnodes;                              // WideNode at the index of every even-depth internal node
@@ -107,6 +111,8 @@ SceneView scene_view(const Ctx* c);
 
 // lbvh.cu
 int lbvh_build(Ctx* c);
+int sort_ray_queue(Ctx* c, cudaStream_t st, int set, int64_t capacity, const uint32_t* n_dev, const float4* so, const float4* sd,
+                   const float4* sb, float4* to, float4* td, float4* tb);
 // wavefront.cu
 int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_begin, int64_t pixel_begin, int64_t pixel_count);
 int wavefront_trace_batch(Ctx* c, const prt_ray* rays, int n, prt_hit* out, int use_bvh);

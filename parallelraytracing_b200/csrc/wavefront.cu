@@ -960,6 +960,17 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
                     if (timing) stamp(st);
                     launches += 2;
                     cur ^= 1;
+                    // ray re-sorting (option): the queue this bounce produced, by origin cell and octant
+                    if (c->sort_rays && b + 1 < std::min(max_depth, tail_b)) {
+                        const unsigned long long h0 = c->hint_rays[0];
+                        const double expect = h0 ? (double)n_paths * (double)c->hint_rays[b + 1] / (double)h0 : (double)n_paths;
+                        if (expect >= (double)c->sort_min_rays) {
+                            if ((rc = sort_ray_queue(c, st, set, n_paths, &qcount[b + 1], qo[cur], qd[cur], qb[cur],
+                                                     qo[cur ^ 1], qd[cur ^ 1], qb[cur ^ 1]))) return rc;
+                            launches += 2 + 3 * ((std::min(24, std::max(8, c->sort_key_bits)) + 7) / 8);
+                            cur ^= 1;
+                        }
+                    }
                 }
             }
             if (tail_b < max_depth) {                                  // staged scenes walk the two-child tree here

@@ -349,6 +349,29 @@ def test_small_wave_tail_kernel_staged_scenes(ctx, gold):
             assert np.array_equal(o[0], out[0][0]) and o[1] == out[0][1], sd.name
 
 
+def test_ray_resorting_is_invisible(ctx, gold):
+    """Option sort_rays (default off): the staged pipeline sorts the queue of every bounce >= 1 by the Morton code
+    of the ray origin's cell and the direction octant (device-side length, radix sort shared with the LBVH build). Queue
+    order has no influence on any path: image, per-bounce ray counts and traversal counters must be bit-identical."""
+    ctx.enable_counters(True)
+    for sd in (S.make_scene(S.ScenePreset.RANDOM_BALLS_SMALL), SCENES["dragon3"](gold), S.random_triangle_soup(20000)):
+        cam = S.Camera(width=128, height=96)
+        ctx.set_scene(sd); ctx.build_bvh(); ctx.set_camera(cam)
+        out = []
+        for sort, bits in ((0, 24), (1, 24), (1, 16), (1, 8)):
+            ctx.set_option("sort_rays", sort); ctx.set_option("sort_key_bits", bits); ctx.set_option("sort_min_rays", 0)
+            ctx.set_option("tail_bounce", 0)
+            ctx.clear_accum(); ctx.render(3, 10, seed=13)
+            st = ctx.stats()
+            out.append((ctx.read_accum(), list(st.rays_per_bounce), st.nodes_visited, st.prims_tested, st.kernel_launches))
+        ctx.set_option("sort_rays", 0); ctx.set_option("sort_key_bits", 24); ctx.set_option("sort_min_rays", 1 << 20)
+        ctx.set_option("tail_bounce", 2)
+        assert out[1][4] == out[0][4] + 9 * 11 and out[3][4] == out[0][4] + 9 * 5     # 9 sorted queues: keys + 3 per pass + gather
+        for o in out[1:]:
+            assert np.array_equal(o[0], out[0][0]) and o[1:4] == out[0][1:4], sd.name
+    ctx.enable_counters(False)
+
+
 def test_display_resolve_exact(ctx, oracle):
     sd = S.cornell(); cam = S.Camera(width=64, height=64)
     ctx.set_scene(sd); ctx.build_bvh(); ctx.set_camera(cam); ctx.clear_accum(); ctx.render(4, 8, seed=1)

@@ -377,6 +377,71 @@ k_extend_wide(SceneView sc, const float4* __restrict__ qo, const float4* __restr
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&stats[bounce], (unsigned long long)count);
 }
 
+// The same walk over the 4-wide quantised nodes for ONE ray held by ONE thread (no queue, no refill): k_tail's traversal on
+// scenes that have wide nodes. The node step is the one of k_extend_wide above (same decode, same conservative slack,
+// nearest hit child first); SS stack entries per thread in shared memory, the rest in local memory.
+template <bool COUNT, int SS>
+__device__ __forceinline__ Best traverse_wide(const SceneView& sc, V3 o, V3 d, int* __restrict__ st, uint32_t& nn, uint32_t& np) {
+    Best best; best_init(best);
+    const V3 inv = mk(safe_inv(d.x), safe_inv(d.y), safe_inv(d.z));
+    RayShear rs; rs.kx = 0; rs.ky = 1; rs.kz = 2; rs.sx = rs.sy = rs.sz = 0.f;
+    if (sc.n_tris > 0) rs = make_shear(d);
+    const V3 dn = sc.n_spheres > 0 ? normalize(d) : d;
+    const bool nx = inv.x < 0.0f, ny = inv.y < 0.0f, nz = inv.z < 0.0f;
+    int lstack[STACK_LOCAL + STACK_SMEM - SS];
+    int cur = sc.root_code, sp = 1;
+    st[0] = PRT_DONE;
+    while (cur != PRT_DONE) {
+        if (cur >= 0) {
+            const WideNode* nd = sc.wnodes + cur;
+            float4 a0, a1, b0, b1;
+            ldg8(nd, a0, a1); ldg8(reinterpret_cast<const char*>(nd) + 32, b0, b1);
+            if (COUNT) ++nn;
+            const float Bx = a0.w * inv.x, By = b1.z * inv.y, Bz = b1.w * inv.z;
+            const float Ax = (a0.x - o.x) * inv.x, Ay = (a0.y - o.y) * inv.y, Az = (a0.z - o.z) * inv.z;
+            const float e = 2.384185791015625e-07f;                                        // 2^-22
+            const float nAx = fmaf(-fabsf(Ax), e, Ax) - Bx, fAx = fmaf(fabsf(Ax), e, Ax) - Bx;
+            const float nAy = fmaf(-fabsf(Ay), e, Ay) - By, fAy = fmaf(fabsf(Ay), e, Ay) - By;
+            const float nAz = fmaf(-fabsf(Az), e, Az) - Bz, fAz = fmaf(fabsf(Az), e, Az) - Bz;
+            const uint32_t lx = __float_as_uint(b0.x), ly = __float_as_uint(b0.y), lz = __float_as_uint(b0.z);
+            const uint32_t hx = __float_as_uint(b0.w), hy = __float_as_uint(b1.x), hz = __float_as_uint(b1.y);
+            const uint32_t wnx = nx ? hx : lx, wfx = nx ? lx : hx;
+            const uint32_t wny = ny ? hy : ly, wfy = ny ? ly : hy;
+            const uint32_t wnz = nz ? hz : lz, wfz = nz ? lz : hz;
+            const int cc[4] = {__float_as_int(a1.x), __float_as_int(a1.y), __float_as_int(a1.z), __float_as_int(a1.w)};
+            uint32_t key[4];
+            const uint32_t one = sc.one_bits;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const uint32_t selb = 0x7604u | ((uint32_t)k << 4);
+                const float gnx = __uint_as_float(__byte_perm(wnx, one, selb)), gny = __uint_as_float(__byte_perm(wny, one, selb));
+                const float gnz = __uint_as_float(__byte_perm(wnz, one, selb)), gfx = __uint_as_float(__byte_perm(wfx, one, selb));
+                const float gfy = __uint_as_float(__byte_perm(wfy, one, selb)), gfz = __uint_as_float(__byte_perm(wfz, one, selb));
+                const float tn = fmaxf(fmaxf(fmaf(gnx, Bx, nAx), fmaf(gny, By, nAy)), fmaxf(fmaf(gnz, Bz, nAz), 0.0f));
+                float tf = fminf(fminf(fmaf(gfx, Bx, fAx), fmaf(gfy, By, fAy)), fminf(fmaf(gfz, Bz, fAz), best.t));
+                tf = tf * 1.00000047683715820312f;
+                key[k] = tn <= tf ? ((__float_as_uint(tn) & ~3u) | (uint32_t)k) : 0xffffffffu;
+            }
+            const uint32_t kmin = min(min(key[0], key[1]), min(key[2], key[3]));
+            int nearc = cc[3];
+            nearc = key[2] == kmin ? cc[2] : nearc; nearc = key[1] == kmin ? cc[1] : nearc; nearc = key[0] == kmin ? cc[0] : nearc;
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (key[k] != 0xffffffffu && key[k] > kmin) {                         // every hit child but the nearest
+                    if (sp < SS) st[sp * WF_THREADS] = cc[k]; else lstack[sp - SS] = cc[k];
+                    ++sp;
+                }
+            if (kmin != 0xffffffffu) { cur = nearc; continue; }
+        } else {
+            if (COUNT) ++np;
+            test_leaf(sc, (uint32_t)~cur, o, d, dn, rs, best);
+        }
+        --sp;
+        cur = sp < SS ? st[sp * WF_THREADS] : lstack[sp - SS];
+    }
+    return best;
+}
+
 // Brute force over every primitive = the reference's own algorithm (primitive.cpp:21-59);
 // used for parity (`prt_trace_batch(use_bvh=0)`), never on the render path.
 __global__ void __launch_bounds__(WF_THREADS)
@@ -668,7 +733,7 @@ k_bounce(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__
 // queue, times 17 bounces at depth 20. k_tail takes the queue of bounce `bounce0` and follows every ray in it to the
 // end of its path inside the thread: no queue, no compaction, one launch. Same device functions, same RNG keys, one
 // contribution per path => the image and the per-bounce ray counts are bit-identical to the launch-per-bounce form.
-template <bool COUNT, bool BRUTE>
+template <bool COUNT, bool BRUTE, bool WIDE = false>
 __global__ void __launch_bounds__(WF_THREADS)
 k_tail(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ qd, const float4* __restrict__ qb,
        float4* __restrict__ contrib, const uint32_t* __restrict__ qcount, int bounce0, int max_depth,
@@ -695,7 +760,8 @@ k_tail(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ q
             if (!act) break;
             if (lane == 0) atomicAdd(&rays_at[bounce], (uint32_t)__popc(act));
             if (alive) {
-                const Best b = traverse<COUNT, BRUTE, FUSED_STACK>(sc, o, d, BRUTE ? sstack : sstack + threadIdx.x, nn, npr);
+                const Best b = WIDE ? traverse_wide<COUNT, FUSED_STACK>(sc, o, d, sstack + threadIdx.x, nn, npr)
+                                    : traverse<COUNT, BRUTE, FUSED_STACK>(sc, o, d, BRUTE ? sstack : sstack + threadIdx.x, nn, npr);
                 V3 np, ndir, L;
                 if (shade_segment(sc, o, d, key, bounce, max_depth, b.t, b.code, b.u, b.v, beta, np, ndir, L)) { o = np; d = ndir; }
                 else { st_stream(&contrib[slot], make_float4(L.x, L.y, L.z, 0.f)); alive = false; }
@@ -911,7 +977,6 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
             int cur = 0;
             // small waves: launch-per-bounce up to tail_bounce, then ONE kernel finishes the paths in-thread
             int tail_b = (c->tail_bounce > 0 && n_paths <= c->tail_max_paths) ? c->tail_bounce : max_depth;
-            if (c->counters_on && wide && !fused) tail_b = max_depth;   // counters then mean WIDE nodes: keep one kind of walk
             if (tail_b < max_depth && c->tail_adaptive) {
                 const unsigned long long p0 = c->hint_rays[0];
                 tail_b = max_depth;
@@ -973,10 +1038,11 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
                     }
                 }
             }
-            if (tail_b < max_depth) {                                  // staged scenes walk the two-child tree here
+            if (tail_b < max_depth) {
                 if (timing) spans.push_back({stamp(st), 0});
-                auto kt = c->counters_on ? (brute && fused ? k_tail<true, true> : k_tail<true, false>)
-                                         : (brute && fused ? k_tail<false, true> : k_tail<false, false>);
+                const bool tw = wide && !fused;                        // staged scenes with wide nodes: same walk as their extend kernel
+                auto kt = c->counters_on ? (brute && fused ? k_tail<true, true> : tw ? k_tail<true, false, true> : k_tail<true, false>)
+                                         : (brute && fused ? k_tail<false, true> : tw ? k_tail<false, false, true> : k_tail<false, false>);
                 kt<<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], qb[cur], contrib, qcount, tail_b, max_depth, dstats);
                 if (timing) stamp(st);
                 ++launches;

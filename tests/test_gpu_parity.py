@@ -332,8 +332,9 @@ def test_small_wave_tail_kernel_is_invisible(ctx):
 
 
 def test_small_wave_tail_kernel_staged_scenes(ctx, gold):
-    """The same tail on the staged pipeline (scenes above fused_max_prims): k_tail walks the two-child tree in-thread, also where
-    the extend kernels use the 4-wide nodes - the closest-hit rule is order-free, so image and ray counts must not move."""
+    """The same tail on the staged pipeline (scenes above fused_max_prims): k_tail walks in-thread the kind of node the extend kernel uses
+    (two-child below 4096 primitives, 4-wide above): image, ray counts and traversal counters must not move."""
+    ctx.enable_counters(True)
     for sd, launches0 in ((S.make_scene(S.ScenePreset.RANDOM_BALLS_SMALL), None), (SCENES["dragon3"](gold), None)):
         cam = S.Camera(width=96, height=72)
         ctx.set_scene(sd); ctx.build_bvh(); ctx.set_camera(cam)
@@ -342,11 +343,12 @@ def test_small_wave_tail_kernel_staged_scenes(ctx, gold):
             ctx.set_option("tail_bounce", tail); ctx.set_option("tail_adaptive", 0)
             ctx.clear_accum(); ctx.render(2, 12, seed=9)
             st = ctx.stats()
-            out.append((ctx.read_accum(), list(st.rays_per_bounce), st.kernel_launches))
+            out.append((ctx.read_accum(), list(st.rays_per_bounce), st.kernel_launches, st.nodes_visited, st.prims_tested))
         ctx.set_option("tail_bounce", 2); ctx.set_option("tail_adaptive", 1)
         assert [o[2] for o in out] == [26, 5, 9, 25]          # raygen + 2/bounce + resolve; raygen + 2*tail + k_tail + resolve
-        for o in out[1:]:
-            assert np.array_equal(o[0], out[0][0]) and o[1] == out[0][1], sd.name
+        for o in out[1:]:      # the tail walks the same kind of node as the extend kernel (two-child / 4-wide): counters equal too
+            assert np.array_equal(o[0], out[0][0]) and o[1] == out[0][1] and o[3:] == out[0][3:], sd.name
+    ctx.enable_counters(False)
 
 
 def test_ray_resorting_is_invisible(ctx, gold):

@@ -5,7 +5,9 @@
  * (parallelraytracing_b200/host/b200_renderer.{h,cpp}) through the reference's unmodified
  * Renderer / Film / Scene / Camera classes. Linked with the reference objects built by oracle/Makefile
  * and with libprt_b200.so. Dumps Film's device accumulators so tests can compare them with the C-ABI path.
- *   shim_driver <preset> <W> <H> <calls> <spp_per_call> <depth> <seed> <out.bin>
+ *   shim_driver <preset> <W> <H> <calls> <spp_per_call> <depth> <seed> <out.bin> [<mesh.ply> <mat_type> <r> <g> <b> <param> <tx> <ty> <tz>]...
+ * Every trailing 9-tuple loads a PLY with the reference's own Mesh class (mesh.cpp:23-184) and registers it with
+ * B200Renderer::AddMesh (the reference Scene cannot hold meshes).
  */
 #define private public          /* Film::d_Accum / d_Weights have no getter (film.h:50-55) */
 #include <core/film.h>
@@ -13,6 +15,7 @@
 #include <core/scene.h>
 #include <core/camera.h>
 #include <core/renderer.h>
+#include <core/mesh.h>
 #include <cstdio>
 #include <cstdlib>
 #include <memory>
@@ -33,6 +36,14 @@ int main(int argc, char** argv)
 
     auto backend = std::make_shared<B200Renderer>();
     backend->SetMaxDepth(depth); backend->SetSamplesPerCall(spp); backend->SetSeed(seed);
+    std::vector<std::unique_ptr<Mesh>> meshes;
+    for (int a = 9; a + 8 < argc; a += 9) {
+        meshes.emplace_back(new Mesh(argv[a]));
+        prt_material m{};
+        m.type = std::atoi(argv[a + 1]); m.r = (float)std::atof(argv[a + 2]); m.g = (float)std::atof(argv[a + 3]);
+        m.b = (float)std::atof(argv[a + 4]); m.param = (float)std::atof(argv[a + 5]);
+        backend->AddMesh(*meshes.back(), m, (float)std::atof(argv[a + 6]), (float)std::atof(argv[a + 7]), (float)std::atof(argv[a + 8]));
+    }
     std::shared_ptr<Renderer> renderer = backend;                          // held as the abstract type, main.cpp:152-163
     renderer->Init(film, scene, camera);                                   // main.cpp:165-166
     film.Clear();                                                          // main.cpp:168

@@ -17,6 +17,14 @@ void B200Renderer::Init(Film& film, const Scene& scene, const Camera& camera)
     }
     prt_host::FlatScene fs = prt_host::FlattenScene(scene);
     if (!fs.ok) { std::fprintf(stderr, "[B200Renderer] %s\n", fs.error.c_str()); return; }
+    if (!m_Meshes.empty()) {
+        if (fs.tri_material.empty()) fs.tri_prim_base = (int)scene.GetPrimitives().size();
+        else if (fs.tri_prim_base + (int)fs.tri_material.size() != (int)scene.GetPrimitives().size()) {
+            std::fprintf(stderr, "[B200Renderer] AddMesh: the scene's own triangles must end its primitive list\n"); return;
+        }
+        for (const MeshRef& m : m_Meshes)
+            prt_host::AppendMesh(fs, *m.mesh, m.material, glm::vec3(m.offset[0], m.offset[1], m.offset[2]));
+    }
     const float sky[3] = {0.4f, 0.3f, 0.6f};              // m_SkyLight, cpu/renderer.h:31
     int nt = (int)fs.tri_material.size();
     if (prt_set_scene(m_Ctx, fs.spheres.data(), (int)fs.spheres.size(), fs.quads.data(), (int)fs.quads.size(),

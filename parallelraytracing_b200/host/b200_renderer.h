@@ -5,6 +5,8 @@
 // runs film.UpdateDisplayGPU()). Compiled against the unmodified reference headers.
 #pragma once
 #include <core/renderer.h>
+#include <core/mesh.h>
+#include <vector>
 #include "prt.h"
 
 class B200Renderer : public Renderer
@@ -22,6 +24,10 @@ public:
     void SetSamplesPerCall(int spp) { m_SamplesPerCall = spp < 1 ? 1 : spp; }
     void SetSeed(uint64_t seed) { m_Seed = seed; }
     void SetDevice(int device) { m_Device = device; }
+    // Mesh -> scene glue: the reference Scene cannot hold a Mesh; meshes registered here BEFORE Init are appended
+    // to the flattened scene as world-space triangles (after the Scene's own primitives). The Mesh must outlive Init.
+    void AddMesh(const Mesh& mesh, const prt_material& material, float tx = 0.f, float ty = 0.f, float tz = 0.f)
+    { m_Meshes.push_back({&mesh, material, {tx, ty, tz}}); }
     prt_ctx* Context() const { return m_Ctx; }
     bool Ok() const { return m_Ok; }
 
@@ -36,4 +42,6 @@ private:
     int m_SamplesPerCall = 1;
     int m_NextSample = 0;
     uint64_t m_Seed = 1;
+    struct MeshRef { const Mesh* mesh; prt_material material; float offset[3]; };
+    std::vector<MeshRef> m_Meshes;
 };

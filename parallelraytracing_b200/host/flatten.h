@@ -55,6 +55,28 @@ inline int FlattenMaterial(const MaterialHandle& h, std::map<const void*, int>& 
     return idx;
 }
 
+// Mesh -> scene glue: the reference's Scene has no triangle pool (shape.h:107-126, scene.h:41) although its
+// Mesh loader exists (mesh.h:8-21). Appends every face of `mesh`, translated by `offset`, as world-space triangles with
+// material `mat` AFTER the primitives already flattened (so prim_id order = scene primitives, then meshes in AddMesh order).
+// Vertex normals as the Mesh holds them (mesh.h:13); a mesh without normals gets flat face normals.
+inline void AppendMesh(FlatScene& fs, const Mesh& mesh, const prt_material& mat, const glm::vec3& offset) {
+    const auto& V = mesh.GetVertices(); const auto& N = mesh.GetNormals(); const auto& I = mesh.GetIndices();
+    const int mi = (int)fs.materials.size();
+    fs.materials.push_back(mat);
+    const bool has_n = N.size() == V.size() && !N.empty();
+    for (size_t f = 0; f + 2 < I.size(); f += 3) {
+        glm::vec3 p[3], n[3];
+        for (int k = 0; k < 3; ++k) p[k] = V[I[f + k]] + offset;
+        if (has_n) for (int k = 0; k < 3; ++k) n[k] = N[I[f + k]];
+        else { const glm::vec3 fn = glm::normalize(glm::cross(p[1] - p[0], p[2] - p[0])); n[0] = n[1] = n[2] = fn; }
+        for (int k = 0; k < 3; ++k) {
+            fs.tri_verts.push_back(p[k].x); fs.tri_verts.push_back(p[k].y); fs.tri_verts.push_back(p[k].z);
+            fs.tri_normals.push_back(n[k].x); fs.tri_normals.push_back(n[k].y); fs.tri_normals.push_back(n[k].z);
+        }
+        fs.tri_material.push_back(mi);
+    }
+}
+
 inline FlatScene FlattenPrimitives(const std::vector<Primitive>& prims) {
     FlatScene fs;
     std::map<const void*, int> seen;

@@ -428,6 +428,34 @@ def mesh_scene(mesh, subdiv=0, instances=((-1.5, 0, 0), (0, 0, 0), (1.5, 0, 0)),
     return b.build()
 
 
+def add_meshes(sd, meshes):
+    """Mesh -> scene glue (SURVEY 8f-2), the host mirror of `B200Renderer::AddMesh` / `prt_host::AppendMesh`
+    (host/flatten.h): every (mesh, material, offset) is appended to a triangle-free scene as world-space triangles after
+    its own primitives; material = (type, (r, g, b), param) gets the next index in the table. mesh = PLY path or
+    (verts, normals, faces)."""
+    if sd.n_tris:
+        raise ValueError("add_meshes: the scene already has triangles")
+    out = SceneData(spheres=sd.spheres, quads=sd.quads, materials=sd.materials, sky=sd.sky, name=sd.name + "+mesh")
+    mats, tv, tn, tm = [tuple(m) for m in sd.materials.tolist()], [], [], []
+    for mesh, (mtype, rgb, param), off in meshes:
+        verts, normals, faces = load_ply(mesh) if isinstance(mesh, (str, os.PathLike)) else mesh
+        v, n = _face_arrays(np.asarray(verts, f32), None if normals is None else np.asarray(normals, f32),
+                            np.asarray(faces).reshape(-1, 3))
+        v = (v + _v3(*off)).astype(f32)
+        if n is None:
+            fn = np.cross(v[:, 1] - v[:, 0], v[:, 2] - v[:, 0]).astype(f32)
+            fn = (fn / np.sqrt((fn * fn).sum(-1, keepdims=True), dtype=f32)).astype(f32)
+            n = np.repeat(fn[:, None, :], 3, axis=1)
+        rec = np.zeros(1, material_dt)
+        rec["type"] = mtype; rec["r"], rec["g"], rec["b"] = rgb; rec["param"] = param
+        mats.append(tuple(rec.tolist()[0]))
+        tv.append(v.reshape(-1, 9)); tn.append(n.reshape(-1, 9)); tm.append(np.full(len(v), len(mats) - 1, np.int32))
+    out.materials = np.array(mats, dtype=material_dt)
+    out.tri_verts, out.tri_normals, out.tri_material = np.concatenate(tv), np.concatenate(tn), np.concatenate(tm)
+    out.tri_prim_base = len(sd.spheres) + len(sd.quads)
+    return out
+
+
 def random_triangle_soup(n_tris, seed=0xB200, extent=50.0, edge=0.25, albedo=0.7):
     """n random triangles, centre ~U([-extent,extent]^3), edges ~U([-edge,edge]^3),
     flat normals, all Lambertian(albedo). Counter-based integer generator -> identical bits anywhere."""

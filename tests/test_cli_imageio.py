@@ -63,3 +63,22 @@ def test_cli_end_to_end(tmp_path):
     assert np.array_equal(np.load(raw), film.ReadAccum())
     assert np.array_equal(imageio.read_png_rgb8(out), film.UpdateDisplay()[:, :, :3])
     rr.close()
+
+
+def test_add_meshes_host_mirror():
+    """scene.add_meshes = the host mirror of B200Renderer::AddMesh (SURVEY 8f-2): triangles after the scene's own
+    primitives, one new material per mesh, flat unit normals when the mesh has none, offsets applied in fp32."""
+    from parallelraytracing_b200 import scene as S
+    v = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [0, 0, 1]], np.float32)
+    f = np.array([[0, 1, 2], [0, 1, 3], [0, 2, 3], [1, 2, 3]], np.uint32)
+    base = S.make_scene(S.ScenePreset.MATERIAL_TEST)
+    sd = S.add_meshes(base, [((v, None, f), (S.MAT_LAMBERTIAN, (0.8, 0.3, 0.3), 0.0), (0, 1, 2)),
+                             ((v, None, f), (S.MAT_METAL, (0.9, 0.9, 0.9), 0.05), (1.5, 1, 2))])
+    assert sd.n_prims == base.n_prims + 8 and sd.tri_prim_base == base.n_prims and sd.n_tris == 8
+    assert len(sd.materials) == len(base.materials) + 2 and list(sd.tri_material) == [4] * 4 + [5] * 4
+    assert np.array_equal(sd.tri_verts[0].reshape(3, 3), v[f[0]] + np.array([0, 1, 2], np.float32))
+    nrm = sd.tri_normals.reshape(-1, 3, 3)
+    assert np.allclose(np.linalg.norm(nrm, axis=-1), 1.0, atol=1e-6) and np.allclose(nrm[0], [[0, 0, 1]] * 3)
+    assert float(sd.materials[5]["param"]) == float(np.float32(0.05)) and int(sd.materials[5]["type"]) == S.MAT_METAL
+    with pytest.raises(ValueError):
+        S.add_meshes(sd, [((v, None, f), (S.MAT_LAMBERTIAN, (1, 1, 1), 0.0), (0, 0, 0))])

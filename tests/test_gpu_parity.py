@@ -451,6 +451,46 @@ def test_cpp_shim_dropin(ctx, tmp_path):
         assert np.abs(mine.astype(int) - disp.astype(int)).max() <= 1     # reference GPU tonemap (film.cu:101-121)
 
 
+def test_cpp_shim_add_mesh(ctx, gold, tmp_path):
+    """Mesh -> scene glue on the C++ side (SURVEY 8f-2): the reference's own `Mesh` class loads a PLY, `B200Renderer::AddMesh`
+    appends it to the flattened `Scene(preset)`; the reference Film's accumulator must equal, bit for bit, the C-ABI
+    render of the host mirror `scene.add_meshes` (binary PLY written from the golden dragon arrays: exact floats)."""
+    import os
+    import subprocess
+    exe = os.path.join(util.ROOT, "oracle", "_ref", "shim_driver")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/shim_driver not built (needs /root/reference at build time)")
+    v = np.ascontiguousarray(gold["mesh_dragon_v"], np.float32); n = np.ascontiguousarray(gold["mesh_dragon_n"], np.float32)
+    f = np.ascontiguousarray(gold["mesh_dragon_f"], np.uint32).reshape(-1, 3)
+    ply = str(tmp_path / "dragon_bin.ply")
+    with open(ply, "wb") as fh:
+        fh.write(("ply\nformat binary_little_endian 1.0\nelement vertex %d\nproperty float x\nproperty float y\nproperty float z\n"
+                  "property float nx\nproperty float ny\nproperty float nz\nelement face %d\n"
+                  "property list uchar uint vertex_indices\nend_header\n" % (len(v), len(f))).encode())
+        fh.write(np.concatenate([v, n], axis=1).astype("<f4").tobytes())
+        rec = np.zeros(len(f), dtype=[("k", "u1"), ("i", "<u4", (3,))]); rec["k"] = 3; rec["i"] = f
+        fh.write(rec.tobytes())
+    got = S.load_ply(ply)                                        # the host loader reads the same file back exactly
+    assert np.array_equal(got[0], v) and np.array_equal(got[1], n) and np.array_equal(np.asarray(got[2]).reshape(-1, 3), f)
+    W, H, calls, depth, seed = 160, 90, 3, 12, 5
+    preset = int(S.ScenePreset.MATERIAL_TEST)
+    out = str(tmp_path / "shim_mesh.bin")
+    r = subprocess.run([exe, str(preset), str(W), str(H), str(calls), "1", str(depth), str(seed), out,
+                        ply, "1", "0.8", "0.3", "0.3", "0", "0", "1", "2", ply, "2", "0.9", "0.9", "0.9", "0.05", "1.5", "1", "2"],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    accum = np.fromfile(out, np.uint8)[:W * H * 12].view(np.float32).reshape(H, W, 3)
+    sd = S.add_meshes(S.make_scene(preset), [((v, n, f), (1, (0.8, 0.3, 0.3), 0.0), (0, 1, 2)),
+                                             ((v, n, f), (2, (0.9, 0.9, 0.9), 0.05), (1.5, 1, 2))])
+    assert sd.n_prims == 4 + 2 * len(f) and sd.tri_prim_base == 4
+    ctx.set_scene(sd); ctx.build_bvh(); ctx.set_camera(S.Camera(width=W, height=H)); ctx.clear_accum()
+    for i in range(calls):
+        ctx.render(1, depth, seed=seed, sample_begin=i)
+    mine = ctx.read_accum()
+    assert np.array_equal(accum, mine)
+    assert (mine.reshape(-1, 3) != mine.reshape(-1, 3)[0]).any()
+
+
 def test_reference_cuda_backends_agree(tmp_path):
     """The reference's OWN CUDA backends (cuda_wavefront, cuda_megakernel: compiled unmodified for sm_100 into oracle/_ref by
     `make -C oracle refgpu`) and B200Renderer, behind the same Renderer interface on this GPU. They use cuRAND, so parity

@@ -388,14 +388,15 @@ def roofline_and_json(args, R):
     ker_ms = min(R["ext_ms"] + R["shd_ms"], R["render_ms"]) / steps
     peak, peak_src = peaks()
     ach = alg_bytes / (ker_ms * 1e-3) / 1e9
-    traffic = None
+    traffic = l2_traffic = None
     try:
         tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
         traffic = tj.get(args.workload, {}).get("dram_bytes_per_step")
+        l2_traffic = tj.get(args.workload, {}).get("l2_bytes_per_step")      # lts__t_sectors.sum x 32 B, same ncu capture
     except Exception:
         pass
     roof = {"bound": "hbm", "kernel": name, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-            "traffic": traffic, "peak_source": peak_src, "kernel_ms_per_step": ker_ms,
+            "traffic": traffic, "l2_traffic": l2_traffic, "peak_source": peak_src, "kernel_ms_per_step": ker_ms,
             "extend_ms_per_step": R["ext_ms"] / steps, "shade_ms_per_step": R["shd_ms"] / steps,
             "primary_ms_per_step": R["prim_ms"] / steps, "render_ms_per_step": R["render_ms"] / steps,
             "nodes_per_ray": n_node, "leaf_tests_per_ray": n_leaf,

@@ -24,8 +24,10 @@ def main(path, extra):
     H, U = rows[0], rows[1]
     ix = {h: i for i, h in enumerate(H)}
     print("%-22s" % "kernel" + "".join("%11s" % c[1] for c in COLS))
-    tot_ns, tot_b = 0.0, 0.0
+    tot_ns, tot_b, tot_l2 = 0.0, 0.0, 0.0
     for r in rows[2:]:
+        if "lts__t_sectors.sum" in ix:                                   # L2-level traffic: every sector the L2 served, 32 B each
+            tot_l2 += float(r[ix["lts__t_sectors.sum"]].replace(",", "")) * 32.0
         line = "%-22s" % r[ix["Kernel Name"]].split("(")[0].replace("void ", "").replace("prt::", "")[:22]
         for name, label, scale in COLS:
             if name not in ix:
@@ -39,12 +41,13 @@ def main(path, extra):
                 v *= scale
             line += "%11.1f" % v
         print(line)
-    print("total: %.3f ms (ncu: cold cache, serialised launches), %.1f MB DRAM traffic" % (tot_ns * 1e-6, tot_b * 1e-6))
+    print("total: %.3f ms (ncu: cold cache, serialised launches), %.1f MB DRAM traffic, %.1f MB L2-level traffic (lts__t_sectors.sum x 32 B)"
+          % (tot_ns * 1e-6, tot_b * 1e-6, tot_l2 * 1e-6))
     if extra[:1] == ["--traffic-json"]:
         wl, waves = extra[1], int(extra[2])
         p = os.path.join(os.path.dirname(os.path.abspath(__file__)), "traffic.json")
         j = json.load(open(p)) if os.path.exists(p) else {}
-        j[wl] = {"dram_bytes_per_step": tot_b * waves, "dram_bytes_per_wave": tot_b,
+        j[wl] = {"dram_bytes_per_step": tot_b * waves, "dram_bytes_per_wave": tot_b, "l2_bytes_per_step": tot_l2 * waves,
                  "source": "profiles/wave_table.py %s: dram__bytes_read.sum+dram__bytes_write.sum over the captured launches of one wave x %d waves per step"
                            % (os.path.basename(path), waves)}
         json.dump(j, open(p, "w"), indent=1)

@@ -275,6 +275,14 @@ void build_lbvh(Scene& sc) {
         hi[0] = fmaxf(hi[0], sc.amax[q].x); hi[1] = fmaxf(hi[1], sc.amax[q].y); hi[2] = fmaxf(hi[2], sc.amax[q].z);
     }
     for (int k = 0; k < 3; ++k) { sc.bounds[k] = lo[k]; sc.bounds[3 + k] = hi[k]; }
+    /* The Morton grid spans the bounds of the box CENTRES, not the scene bounds: one large primitive (a ground quad) no
+     * longer spends the 10 bits per axis on empty space (lbvh.cu:k_prim_bounds / k_morton, option morton_centroid = 1). */
+    for (int k = 0; k < 3; ++k) { lo[k] = INFINITY; hi[k] = -INFINITY; }
+    for (int q = 0; q < n; ++q) {
+        float cx = (sc.amin[q].x + sc.amax[q].x) * 0.5f, cy = (sc.amin[q].y + sc.amax[q].y) * 0.5f, cz = (sc.amin[q].z + sc.amax[q].z) * 0.5f;
+        lo[0] = fminf(lo[0], cx); lo[1] = fminf(lo[1], cy); lo[2] = fminf(lo[2], cz);
+        hi[0] = fmaxf(hi[0], cx); hi[1] = fmaxf(hi[1], cy); hi[2] = fmaxf(hi[2], cz);
+    }
     std::vector<std::pair<uint32_t, uint32_t>> kv(n);
     for (int q = 0; q < n; ++q) {
         float cx = (sc.amin[q].x + sc.amax[q].x) * 0.5f, cy = (sc.amin[q].y + sc.amax[q].y) * 0.5f, cz = (sc.amin[q].z + sc.amax[q].z) * 0.5f;

@@ -14,9 +14,9 @@ namespace prt {
 __device__ __forceinline__ int f2ord(float f) { int i = __float_as_int(f); return i >= 0 ? i : i ^ 0x7fffffff; }
 __device__ __forceinline__ float ord2f(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
 
+// b[0..5] = bounds of the primitives' boxes (scene bounds), b[6..11] = bounds of the box CENTRES (Morton quantisation grid)
 __global__ void k_init_bounds(int* b) {
-    if (threadIdx.x < 3) b[threadIdx.x] = 0x7fffffff;           // min = +max ordered
-    else if (threadIdx.x < 6) b[threadIdx.x] = (int)0x80000000; // max = lowest ordered
+    if (threadIdx.x < 12) b[threadIdx.x] = (threadIdx.x % 6) < 3 ? 0x7fffffff : (int)0x80000000;   // min = +max ordered, max = lowest
 }
 
 // AABB of primitive q (input order: spheres, quads, triangles). The exact expression
@@ -57,12 +57,13 @@ __global__ void k_prim_bounds(const SphereRec* __restrict__ spheres, int ns,
         amin[q] = make_float4(lo[0], lo[1], lo[2], 0.f);
         amax[q] = make_float4(hi[0], hi[1], hi[2], 0.f);
     }
-    // block reduction of the scene bounds (min/max are exact, so order does not matter)
-    __shared__ float s_lo[3][8], s_hi[3][8];
+    // block reduction of the scene bounds and of the bounds of the box centres (min/max are exact, so order does not matter)
+    __shared__ float s_lo[6][8], s_hi[6][8];
     int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
 #pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        float a = lo[k], b = hi[k];
+    for (int k = 0; k < 6; ++k) {
+        float a = lo[k % 3], b = hi[k % 3];
+        if (k >= 3) { a = q < n ? (lo[k - 3] + hi[k - 3]) * 0.5f : a; b = q < n ? a : b; }      // centre, as k_morton computes it
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             a = fminf(a, __shfl_xor_sync(0xffffffffu, a, o));
@@ -71,11 +72,12 @@ __global__ void k_prim_bounds(const SphereRec* __restrict__ spheres, int ns,
         if (lane == 0) { s_lo[k][w] = a; s_hi[k][w] = b; }
     }
     __syncthreads();
-    if (threadIdx.x < 3) {
+    if (threadIdx.x < 6) {
         int k = threadIdx.x;
         float a = s_lo[k][0], b = s_hi[k][0];
         for (int i = 1; i < (int)(blockDim.x >> 5); ++i) { a = fminf(a, s_lo[k][i]); b = fmaxf(b, s_hi[k][i]); }
-        if (a <= b) { atomicMin(&bounds[k], f2ord(a)); atomicMax(&bounds[3 + k], f2ord(b)); }
+        const int at = k < 3 ? k : 6 + (k - 3);
+        if (a <= b) { atomicMin(&bounds[at], f2ord(a)); atomicMax(&bounds[at + 3], f2ord(b)); }
     }
 }
 
@@ -441,7 +443,7 @@ int lbvh_build(Ctx* c) {
     c->bvh_built = false; c->wide_built = false;
     cudaStream_t st = c->stream;
     int rc;
-    if ((rc = dev_reserve(c, c->scene_bounds, 6 * sizeof(int)))) return rc;
+    if ((rc = dev_reserve(c, c->scene_bounds, 12 * sizeof(int)))) return rc;
     if (n == 0) {
         k_init_bounds<<<1, 32, 0, st>>>((int*)c->scene_bounds.p);
         c->root_code = 0; c->bvh_built = true; c->build_ms = 0.f;
@@ -471,7 +473,7 @@ int lbvh_build(Ctx* c) {
                                    (const float4*)c->tri_in_v.p, nt, (float4*)c->aabb_min.p,
                                    (float4*)c->aabb_max.p, (int*)c->scene_bounds.p);
     k_morton<<<G, T, 0, st>>>((const float4*)c->aabb_min.p, (const float4*)c->aabb_max.p, n,
-                              (const int*)c->scene_bounds.p, (uint32_t*)c->keys[0].p,
+                              (const int*)c->scene_bounds.p + (c->morton_centroid ? 6 : 0), (uint32_t*)c->keys[0].p,
                               (uint32_t*)c->vals[0].p, (uint32_t*)c->morton.p);
     int cur = 0;
     for (int pass = 0; pass < 4; ++pass) {

@@ -34,6 +34,7 @@ struct Ctx {
     DevBuf keys[2], vals[2];                    // radix sort ping-pong
     DevBuf block_hist;                          // digit-major per-block histograms
     DevBuf ray_keys[2][2], ray_vals[2][2], ray_hist[2];   // ray re-sorting, per buffer set: key/index ping-pong + histograms
+    int morton_centroid = 1;                    // Morton grid over the bounds of the box centres (1) or the scene bounds (0)
     int sort_rays = 0;                          // staged pipeline: sort the queue of every bounce >= 1 (0 off, 1 on)
     int sort_key_bits = 24;                     // origin-cell Morton bits + 3 octant bits (8..24 => 1..3 radix passes)
     int sort_min_rays = 1 << 20;                // ... only while the queue is expected to hold at least this many rays

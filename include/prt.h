@@ -169,6 +169,13 @@ int  prt_set_camera(prt_ctx* ctx, const prt_camera* cam);
  * (cpu/renderer.cpp:59-103 semantics) and ADDS them to the accumulation buffer.
  * Synchronous, like the reference (cudaDeviceSynchronize at renderer.cu:429). */
 int  prt_render(prt_ctx* ctx, int spp, int max_depth, uint64_t seed, int sample_begin);
+/* "Clear, then render" in one call: afterwards the sample buffer holds exactly the sum of these `spp` samples and
+ * prt_accum_spp() == spp. This is what one Renderer::ProgressiveRender() needs before it hands the buffer to
+ * Film::AddSampleBufferGPU (cuda_wavefront/renderer.cu:372-433 refills its own m_DeviceFilmBuffer every frame the same
+ * way). With spp = 1 and a frame that fits one wave the paths write their contribution straight into the buffer: no
+ * memset, no contribution plane, no resolve pass. Same image, bit for bit, as prt_clear_accum + prt_render. */
+int  prt_render_fresh(prt_ctx* ctx, int spp, int max_depth, uint64_t seed, int sample_begin);
+
 /* The same for the pixel range [pixel_begin, pixel_begin + pixel_count) only (row-major pixel index y*W+x; a band
  * of rows is a contiguous range): the TILE partition of SURVEY 8e - each GPU renders all samples of its own pixels,
  * pixels outside the range are left untouched, and the same sum-reduce assembles the frame. Identical per-pixel

@@ -45,7 +45,7 @@ class PrtError(RuntimeError):
 
 EXPORTS = [
     "prt_create", "prt_destroy", "prt_last_error", "prt_version", "prt_set_scene", "prt_build_bvh",
-    "prt_set_camera", "prt_render", "prt_render_region", "prt_clear_accum", "prt_scale_accum", "prt_accum_device_ptr",
+    "prt_set_camera", "prt_render", "prt_render_fresh", "prt_render_region", "prt_clear_accum", "prt_scale_accum", "prt_accum_device_ptr",
     "prt_set_accum_buffer", "prt_read_accum", "prt_accum_spp", "prt_set_accum_spp", "prt_resolve_display", "prt_trace_batch",
     "prt_debug_lbvh", "prt_debug_wide", "prt_num_prims", "prt_enable_counters", "prt_get_stats", "prt_set_option",
 ]
@@ -76,6 +76,7 @@ def load_library():
     lib.prt_build_bvh.argtypes = [vp]
     lib.prt_set_camera.argtypes = [vp, C.POINTER(CCamera)]
     lib.prt_render.argtypes = [vp, i32, i32, u64, i32]
+    lib.prt_render_fresh.argtypes = [vp, i32, i32, u64, i32]
     lib.prt_render_region.argtypes = [vp, i32, i32, u64, i32, i32, i32]
     lib.prt_clear_accum.argtypes = [vp]
     lib.prt_scale_accum.argtypes = [vp, f32]
@@ -154,6 +155,10 @@ class Context:
 
     def render(self, spp, max_depth, seed=1, sample_begin=0):
         self._check(self.lib.prt_render(self.h, spp, max_depth, seed, sample_begin), "prt_render")
+
+    def render_fresh(self, spp, max_depth, seed=1, sample_begin=0):
+        """clear + render in one call (prt_render_fresh); 1 spp in one wave goes straight into the sample buffer."""
+        self._check(self.lib.prt_render_fresh(self.h, spp, max_depth, seed, sample_begin), "prt_render_fresh")
 
     def render_region(self, spp, max_depth, seed=1, sample_begin=0, pixel_begin=0, pixel_count=0):
         self._check(self.lib.prt_render_region(self.h, spp, max_depth, seed, sample_begin, pixel_begin, pixel_count), "prt_render_region")

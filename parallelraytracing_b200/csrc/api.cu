@@ -250,6 +250,23 @@ int prt_render(prt_ctx* ctx, int spp, int max_depth, uint64_t seed, int sample_b
     return wavefront_render(c, spp, max_depth, seed, sample_begin, 0, (int64_t)c->cam.width * c->cam.height);
 }
 
+int prt_render_fresh(prt_ctx* ctx, int spp, int max_depth, uint64_t seed, int sample_begin) {
+    if (!ctx) return set_err(nullptr, PRT_ERR_INVALID, "prt_render_fresh: ctx is NULL");
+    Ctx* c = &ctx->c;
+    if (!c->scene_set || !c->bvh_built) return set_err(c, PRT_ERR_INVALID, "prt_render_fresh: scene/BVH not ready (prt_set_scene + prt_build_bvh)");
+    if (!c->cam_set) return set_err(c, PRT_ERR_INVALID, "prt_render_fresh: call prt_set_camera first");
+    if (spp < 1 || max_depth < 0 || max_depth > PRT_MAX_DEPTH || sample_begin < 0)
+        return set_err(c, PRT_ERR_INVALID, "prt_render_fresh: bad spp / max_depth / sample_begin");
+    PRT_CUDA(c, cudaSetDevice(c->device));
+    if (max_depth == 0) {                                          // TraceRay(depth<=0) = 0, renderer.cpp:61
+        PRT_CUDA(c, cudaMemsetAsync(c->accum, 0, (size_t)c->cam.width * c->cam.height * 12, c->stream));
+        PRT_CUDA(c, cudaStreamSynchronize(c->stream));
+        c->accum_spp = spp;
+        return PRT_OK;
+    }
+    return wavefront_render(c, spp, max_depth, seed, sample_begin, 0, (int64_t)c->cam.width * c->cam.height, true);
+}
+
 int prt_render_region(prt_ctx* ctx, int spp, int max_depth, uint64_t seed, int sample_begin, int pixel_begin, int pixel_count) {
     if (!ctx) return set_err(nullptr, PRT_ERR_INVALID, "prt_render_region: ctx is NULL");
     Ctx* c = &ctx->c;

@@ -145,6 +145,7 @@ struct SceneView {
     int              rr_start; // estimator option, default off (-1): Russian roulette from this bounce on
     float            clamp;    // estimator option, default off (+inf): per-path radiance clamp ("firefly clamp")
     uint32_t         one_bits; // 0x3f800000, read from the constant bank so that PRMT keeps its selector as the immediate
+    float*           direct;   // != nullptr: a 1-spp single-wave "fresh" render writes each path's contribution straight to accum[3*slot..] (no contribution plane, no resolve)
     int              brute;    // tiny sphere/quad scene: test every primitive in list order, no BVH (see traverse())
 };
 

@@ -115,7 +115,7 @@ int lbvh_build(Ctx* c);
 int sort_ray_queue(Ctx* c, cudaStream_t st, int set, int64_t capacity, const uint32_t* n_dev, const float4* so, const float4* sd,
                    const float4* sb, float4* to, float4* td, float4* tb);
 // wavefront.cu
-int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_begin, int64_t pixel_begin, int64_t pixel_count);
+int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_begin, int64_t pixel_begin, int64_t pixel_count, bool fresh = false);
 int wavefront_trace_batch(Ctx* c, const prt_ray* rays, int n, prt_hit* out, int use_bvh);
 int film_resolve_display(Ctx* c, float exposure, float gamma, uint8_t* host_rgba);
 int film_scale_accum(Ctx* c, float s);

@@ -474,6 +474,13 @@ __device__ __forceinline__ V3 clamp_radiance(const SceneView& sc, V3 L) {
     return mk(fminf(L.x, sc.clamp), fminf(L.y, sc.clamp), fminf(L.z, sc.clamp));
 }
 
+// A path's contribution, written once when the path ends: into the wave's contribution plane (k_resolve sums it into the
+// accumulator in sample order), or - prt_render_fresh with one sample and one wave - straight into the accumulator.
+__device__ __forceinline__ void put_contrib(const SceneView& sc, float4* __restrict__ contrib, uint32_t slot, V3 L) {
+    if (sc.direct) { float* a = sc.direct + 3 * (size_t)slot; a[0] = L.x; a[1] = L.y; a[2] = L.z; }
+    else st_stream(&contrib[slot], make_float4(L.x, L.y, L.z, 0.f));
+}
+
 __device__ __forceinline__ bool shade_segment(const SceneView& sc, V3 o, V3 d, uint32_t key, int bounce, int max_depth,
                                               float t, uint32_t code, float hu, float hv, V3& beta, V3& np, V3& ndir, V3& L) {
     if (code == PRT_NO_HIT) {
@@ -563,7 +570,7 @@ __device__ __forceinline__ void sq_shade(const SceneView& sc, const float* __res
         V3 L;
         cont = shade_segment(sc, o, d, key, bounce, max_depth, q[11 * SQ_CAP + e], __float_as_uint(q[12 * SQ_CAP + e]),
                              q[13 * SQ_CAP + e], q[14 * SQ_CAP + e], beta, np, ndir, L);
-        if (!cont) st_stream(&contrib[sb >> 5], make_float4(L.x, L.y, L.z, 0.f));
+        if (!cont) put_contrib(sc, contrib, sb >> 5, L);
     }
     if (DEFER) { out->cont = cont; out->np = np; out->ndir = ndir; out->beta = beta; out->sb = sb + 1u; out->key = key; }
     else push_compacted(cont, lane, next_count, no, nd, nb, np, ndir, beta, sb + 1u, key);
@@ -603,7 +610,7 @@ __device__ __forceinline__ int sq_batch(const SceneView& sc, float* __restrict__
     const bool hit = live && code != PRT_NO_HIT;
     if (live && !hit) {                                                 // cpu/renderer.cpp:99
         V3 L = clamp_radiance(sc, beta * mk(sc.sky_r, sc.sky_g, sc.sky_b));
-        st_stream(&contrib[slot_bounce >> 5], make_float4(L.x, L.y, L.z, 0.f));
+        put_contrib(sc, contrib, slot_bounce >> 5, L);
     }
     const uint32_t mask = __ballot_sync(0xffffffffu, hit);
     if (hit) sq_put(q, qn + __popc(mask & ((1u << lane) - 1u)), o, d, beta, key, slot_bounce, t, code, u, v);
@@ -764,7 +771,7 @@ k_tail(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ q
                                     : traverse<COUNT, BRUTE, FUSED_STACK>(sc, o, d, BRUTE ? sstack : sstack + threadIdx.x, nn, npr);
                 V3 np, ndir, L;
                 if (shade_segment(sc, o, d, key, bounce, max_depth, b.t, b.code, b.u, b.v, beta, np, ndir, L)) { o = np; d = ndir; }
-                else { st_stream(&contrib[slot], make_float4(L.x, L.y, L.z, 0.f)); alive = false; }
+                else { put_contrib(sc, contrib, slot, L); alive = false; }
             }
         }
     }
@@ -869,6 +876,7 @@ SceneView scene_view(const Ctx* c) {
     v.one_bits = 0x3f800000u;
     v.rr_start = c->rr_start; v.clamp = c->firefly_clamp > 0.f ? c->firefly_clamp : INFINITY;
     v.brute = 0;                                          // only wavefront_render's fused path turns it on
+    v.direct = nullptr;
     return v;
 }
 
@@ -910,7 +918,7 @@ static int ensure_wave_buffers(Ctx* c, int64_t paths, bool second_set = false) {
     return PRT_OK;
 }
 
-int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_begin, int64_t pixel_begin, int64_t pixel_count) {
+int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_begin, int64_t pixel_begin, int64_t pixel_count, bool fresh) {
     const int64_t P = pixel_count;                                   // pixels [pixel_begin, pixel_begin + P) of the frame
     int64_t cap = c->wave_paths_opt > 0 ? c->wave_paths_opt : (int64_t)64 << 20;   // 64 Mi paths: 8.6 GB of queues per set
     cap = std::min<int64_t>(cap, (int64_t)1 << 26);                  // slot must fit 27 bits
@@ -926,6 +934,11 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
 
     SceneView sc = scene_view(c);
     CamView cam = cam_view(c->cam);
+    // fresh = "clear, then render": with ONE sample in ONE wave every pixel of the range gets exactly one contribution, so the
+    // paths write it straight into the accumulator (no memset, no contribution plane, no resolve); otherwise clear first
+    const bool direct = fresh && n_waves == 1 && spp == 1;
+    if (fresh && !direct) PRT_CUDA(c, cudaMemsetAsync(c->accum + 3 * pixel_begin, 0, (size_t)P * 12, c->stream));
+    if (direct) sc.direct = c->accum + 3 * pixel_begin;
     unsigned long long* dstats = (unsigned long long*)c->stats_dev.p;
     const bool brute = c->n_tris == 0 && c->n_prims <= c->brute_max_prims;   // fused kernels only
     sc.brute = brute ? 1 : 0;
@@ -1048,10 +1061,12 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
                 ++launches;
             }
             // resolves read-modify-write the same accumulation pixels: keep them in wave order across the two streams
-            if (nsets > 1 && wave > 0) PRT_CUDA(c, cudaStreamWaitEvent(st, c->ev_res[(wave - 1) & 1], 0));
-            k_resolve<<<(npix + WF_THREADS - 1) / WF_THREADS, WF_THREADS, 0, st>>>(contrib, (int)p0, npix, S, c->accum);
-            if (nsets > 1) PRT_CUDA(c, cudaEventRecord(c->ev_res[wave & 1], st));
-            ++launches;
+            if (!direct) {
+                if (nsets > 1 && wave > 0) PRT_CUDA(c, cudaStreamWaitEvent(st, c->ev_res[(wave - 1) & 1], 0));
+                k_resolve<<<(npix + WF_THREADS - 1) / WF_THREADS, WF_THREADS, 0, st>>>(contrib, (int)p0, npix, S, c->accum);
+                if (nsets > 1) PRT_CUDA(c, cudaEventRecord(c->ev_res[wave & 1], st));
+                ++launches;
+            }
         }
     }
     if (nsets > 1) {
@@ -1065,7 +1080,7 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
     PRT_CUDA(c, cudaMemcpyAsync(c->stats_host, dstats, (PRT_MAX_DEPTH + 4) * 8, cudaMemcpyDeviceToHost, st));
     PRT_CUDA(c, cudaStreamSynchronize(st));
     PRT_CUDA(c, cudaGetLastError());
-    c->accum_spp += spp;
+    c->accum_spp = (fresh ? 0 : c->accum_spp) + spp;
 
     const unsigned long long* h = c->stats_host;
     prt_stats& s = c->stats;

@@ -54,7 +54,7 @@ void B200Renderer::ProgressiveRender()
     // Film::AddSampleBufferGPU of the previous frame ran on the legacy default stream and returned without waiting
     // (film.cu:90-99); the context's streams are non-blocking, so the sample buffer must not be rewritten before it is read
     cudaStreamSynchronize(cudaStreamLegacy);
-    if (prt_clear_accum(m_Ctx) != PRT_OK || prt_render(m_Ctx, k, m_Depth, m_Seed, m_NextSample) != PRT_OK) {
+    if (prt_render_fresh(m_Ctx, k, m_Depth, m_Seed, m_NextSample) != PRT_OK) {          // clear + render; 1 spp writes the buffer directly
         std::fprintf(stderr, "[B200Renderer] %s\n", prt_last_error(m_Ctx));
         return;
     }

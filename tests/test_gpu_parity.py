@@ -374,6 +374,31 @@ def test_ray_resorting_is_invisible(ctx, gold):
     ctx.enable_counters(False)
 
 
+def test_render_fresh_equals_clear_plus_render(ctx, gold):
+    """prt_render_fresh = clear + render in one call (what one ProgressiveRender needs). With 1 spp in one wave the paths
+    write straight into the sample buffer (no memset, no contribution plane, no resolve launch): same bits."""
+    for sd in (S.cornell(), S.make_scene(S.ScenePreset.DEFAULT), S.make_scene(S.ScenePreset.RANDOM_BALLS_SMALL), SCENES["dragon3"](gold)):
+        cam = S.Camera(width=160, height=90)
+        ctx.set_scene(sd); ctx.build_bvh(); ctx.set_camera(cam)
+        for spp in (1, 3):
+            ctx.clear_accum(); ctx.render(5, 6, seed=2)                      # stale content that fresh must replace
+            ctx.clear_accum(); ctx.render(spp, 20, seed=7, sample_begin=4)
+            want, l0 = ctx.read_accum(), ctx.stats().kernel_launches
+            ctx.render(2, 6, seed=3)                                         # dirty again
+            ctx.render_fresh(spp, 20, seed=7, sample_begin=4)
+            assert np.array_equal(ctx.read_accum(), want), (sd.name, spp)
+            assert ctx.accum_spp() == spp
+            assert ctx.stats().kernel_launches == l0 - (1 if spp == 1 else 0)    # 1 spp: no resolve pass
+    ctx.set_option("wave_paths", 4000)                                       # 1 spp but several waves: clear + resolve path
+    ctx.set_scene(S.cornell()); ctx.build_bvh(); ctx.set_camera(S.Camera(width=160, height=90))
+    ctx.clear_accum(); ctx.render(1, 8, seed=7); want = ctx.read_accum()
+    ctx.render(3, 8, seed=1); ctx.render_fresh(1, 8, seed=7)
+    ctx.set_option("wave_paths", 0)
+    assert np.array_equal(ctx.read_accum(), want) and ctx.accum_spp() == 1
+    ctx.render_fresh(2, 0, seed=1)                                           # depth 0: TraceRay returns 0
+    assert not ctx.read_accum().any() and ctx.accum_spp() == 2
+
+
 def test_display_resolve_exact(ctx, oracle):
     sd = S.cornell(); cam = S.Camera(width=64, height=64)
     ctx.set_scene(sd); ctx.build_bvh(); ctx.set_camera(cam); ctx.clear_accum(); ctx.render(4, 8, seed=1)

@@ -76,7 +76,6 @@ struct Ctx {
     DevBuf stats_dev;                           // uint64 [PRT_MAX_DEPTH + 4]
     int ctas_per_sm = 8;
     int counters_on = 0;
-    int use_graph = 1;
     unsigned long long* stats_host = nullptr;   // pinned copy of stats_dev
     int tail_bounce = 2;               // fused path: bounces >= this run in ONE in-thread kernel, k_tail (0 = never); with
     int tail_adaptive = 1;             //   tail_adaptive the start is the first bounce whose queue is expected to hold <= tail_rays

@@ -231,7 +231,8 @@ int  prt_debug_lbvh(prt_ctx* ctx, uint32_t* morton, uint32_t* sorted_prim,
                     float* node_bounds, float* scene_bounds);
 /* The 4-wide quantised nodes (only when built: option bvh_wide, or automatically for large scenes), raw device
  * layout: 16 words per internal node {ox, oy, oz, scale_x, code[4], qlo[3], qhi[3], scale_y, scale_z}, indexed like
- * the two-child nodes. Only entries of EVEN-depth nodes are defined. Returns PRT_ERR_INVALID if not built. */
+ * the two-child nodes; every internal node has a record (greedy collapse by surface area, 2..4 slots). Returns
+ * PRT_ERR_INVALID if not built. */
 int  prt_debug_wide(prt_ctx* ctx, uint32_t* words);
 int  prt_num_prims(const prt_ctx* ctx);
 

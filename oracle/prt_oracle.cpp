@@ -401,18 +401,29 @@ void build_wide(Scene& sc) {
     int n = sc.n_prims(), ni = n > 1 ? n - 1 : 0;
     sc.wide.assign(ni, Scene::WNode()); sc.wide_valid.assign(ni, 0);
     for (int i = 0; i < ni; ++i) {
-        int depth = 0;
-        for (int p = sc.parent[i]; p >= 0; p = sc.parent[p]) ++depth;
-        if (depth & 1) continue;
-        V3 lo[4], hi[4]; int code[4]; int ns = 0;
+        /* greedy collapse by surface area, lbvh.cu:k_emit_wide: start from the two children, twice open the internal slot
+         * with the largest box (ties: lowest slot), its two children take its place */
+        V3 lo[4], hi[4]; int code[4]; int raw[4]; int ns = 2;
         for (int k = 0; k < 2; ++k) {
-            int ch = sc.children[2 * i + k];
-            if (ch < 0) { child_box(sc, ch, lo[ns], hi[ns]); code[ns++] = dev_leaf_code(sc, ~ch); }
-            else for (int g = 0; g < 2; ++g) {
-                int gc = sc.children[2 * ch + g];
-                child_box(sc, gc, lo[ns], hi[ns]); code[ns++] = gc < 0 ? dev_leaf_code(sc, ~gc) : gc;
-            }
+            raw[k] = sc.children[2 * i + k];
+            child_box(sc, raw[k], lo[k], hi[k]);
         }
+        for (int round = 0; round < 2; ++round) {
+            int s = -1; float best = -1.0f;
+            for (int c = 0; c < ns; ++c)
+                if (raw[c] >= 0) {
+                    const float dx = hi[c].x - lo[c].x, dy = hi[c].y - lo[c].y, dz = hi[c].z - lo[c].z;
+                    const float ar = (dx * dy + dy * dz) + dz * dx;
+                    if (ar > best) { best = ar; s = c; }
+                }
+            if (s < 0) break;
+            for (int c = ns; c > s + 1; --c) { raw[c] = raw[c - 1]; lo[c] = lo[c - 1]; hi[c] = hi[c - 1]; }
+            const int node = raw[s];
+            raw[s] = sc.children[2 * node]; raw[s + 1] = sc.children[2 * node + 1];
+            child_box(sc, raw[s], lo[s], hi[s]); child_box(sc, raw[s + 1], lo[s + 1], hi[s + 1]);
+            ++ns;
+        }
+        for (int c = 0; c < ns; ++c) code[c] = raw[c] < 0 ? dev_leaf_code(sc, ~raw[c]) : raw[c];
         Scene::WNode& w = sc.wide[i];
         for (int k = 0; k < 3; ++k) {
             float mn = comp(lo[0], k), mx = comp(hi[0], k);

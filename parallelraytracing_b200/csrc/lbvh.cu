@@ -373,10 +373,11 @@ __global__ void k_gather_tris(int n, int ns, int nq, int tri_prim_base, const ui
 }
 
 // ------------------------------------------------------------------ 4-wide quantised nodes
-// Collapse the two-child tree by grandchildren: every internal node at EVEN depth becomes a wide node whose
-// slots are its children's children (a leaf child keeps its own slot), 2..4 slots. Wide nodes live at the
-// index of the binary node they replace (odd-depth entries stay unused), so child codes need no remapping
-// and the root is still node 0. Depth comes from walking the parent chain (<= tree height steps).
+// Collapse the two-child tree greedily by SURFACE AREA: a wide node starts with its two children and, twice, replaces the
+// internal slot with the largest box by that slot's two children (the new pair takes the slot's place, order kept), so the
+// 2..4 slots may sit one to three levels below. Unbalanced LBVH subtrees (a big primitive next to small ones) get their
+// big side opened instead of a fixed two levels. EVERY internal node gets a record, at its own index - which ones a ray
+// ever visits follows from the child codes, the root is still node 0, child codes need no remapping.
 __device__ __forceinline__ float pow2_ceil_scale(float ext) {
     // smallest power of two s with ext / s <= 254 (room for the 2^-6 margin and the ceil); >= 2^-60
     float s = 8.673617379884035e-19f;                                  // 2^-60
@@ -388,29 +389,38 @@ __device__ __forceinline__ float pow2_ceil_scale(float ext) {
     return s;
 }
 
+__device__ __forceinline__ float box_area(const float* lo, const float* hi) {
+    const float dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
+    return (dx * dy + dy * dz) + dz * dx;
+}
+
 __global__ void k_emit_wide(int n_internal, const int* __restrict__ parent, const BvhNode* __restrict__ nodes,
                             WideNode* __restrict__ wide) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_internal) return;
-    int depth = 0;
-    for (int p = parent[i]; p >= 0; p = parent[p]) ++depth;
-    if (depth & 1) return;
-    float lo[4][3], hi[4][3]; int code[4]; int ns = 0;
-    BvhNode nd = nodes[i];
-    const int cc[2] = {__float_as_int(nd.lmin.w), __float_as_int(nd.lmax.w)};
-    const float4 bmin[2] = {nd.lmin, nd.rmin}, bmax[2] = {nd.lmax, nd.rmax};
-#pragma unroll
-    for (int k = 0; k < 2; ++k) {
-        if (cc[k] < 0) {
-            lo[ns][0] = bmin[k].x; lo[ns][1] = bmin[k].y; lo[ns][2] = bmin[k].z;
-            hi[ns][0] = bmax[k].x; hi[ns][1] = bmax[k].y; hi[ns][2] = bmax[k].z; code[ns++] = cc[k];
-        } else {
-            BvhNode ch = nodes[cc[k]];
-            lo[ns][0] = ch.lmin.x; lo[ns][1] = ch.lmin.y; lo[ns][2] = ch.lmin.z;
-            hi[ns][0] = ch.lmax.x; hi[ns][1] = ch.lmax.y; hi[ns][2] = ch.lmax.z; code[ns++] = __float_as_int(ch.lmin.w);
-            lo[ns][0] = ch.rmin.x; lo[ns][1] = ch.rmin.y; lo[ns][2] = ch.rmin.z;
-            hi[ns][0] = ch.rmax.x; hi[ns][1] = ch.rmax.y; hi[ns][2] = ch.rmax.z; code[ns++] = __float_as_int(ch.lmax.w);
+    (void)parent;
+    float lo[4][3], hi[4][3]; int code[4]; int ns = 2;
+    {
+        const BvhNode nd = nodes[i];
+        lo[0][0] = nd.lmin.x; lo[0][1] = nd.lmin.y; lo[0][2] = nd.lmin.z; hi[0][0] = nd.lmax.x; hi[0][1] = nd.lmax.y; hi[0][2] = nd.lmax.z;
+        lo[1][0] = nd.rmin.x; lo[1][1] = nd.rmin.y; lo[1][2] = nd.rmin.z; hi[1][0] = nd.rmax.x; hi[1][1] = nd.rmax.y; hi[1][2] = nd.rmax.z;
+        code[0] = __float_as_int(nd.lmin.w); code[1] = __float_as_int(nd.lmax.w);
+    }
+    for (int round = 0; round < 2; ++round) {
+        int s = -1; float best = -1.0f;
+        for (int c = 0; c < ns; ++c)
+            if (code[c] >= 0) { const float ar = box_area(lo[c], hi[c]); if (ar > best) { best = ar; s = c; } }   // ties: lowest slot
+        if (s < 0) break;
+        for (int c = ns; c > s + 1; --c) {                               // make room at s + 1
+            code[c] = code[c - 1];
+            for (int k = 0; k < 3; ++k) { lo[c][k] = lo[c - 1][k]; hi[c][k] = hi[c - 1][k]; }
         }
+        const BvhNode ch = nodes[code[s]];
+        lo[s][0] = ch.lmin.x; lo[s][1] = ch.lmin.y; lo[s][2] = ch.lmin.z; hi[s][0] = ch.lmax.x; hi[s][1] = ch.lmax.y; hi[s][2] = ch.lmax.z;
+        lo[s + 1][0] = ch.rmin.x; lo[s + 1][1] = ch.rmin.y; lo[s + 1][2] = ch.rmin.z;
+        hi[s + 1][0] = ch.rmax.x; hi[s + 1][1] = ch.rmax.y; hi[s + 1][2] = ch.rmax.z;
+        code[s] = __float_as_int(ch.lmin.w); code[s + 1] = __float_as_int(ch.lmax.w);
+        ++ns;
     }
     WideNode w;
     float org[3], sc[3];

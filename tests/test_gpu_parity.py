@@ -147,7 +147,7 @@ def test_wide_nodes_equal_two_child_bvh(ctx, oracle, gold, name):
         osc = oracle.scene(sd)
         ow, valid = osc.get_wide()
         gw = ctx.debug_wide()
-        assert valid[0] and 0.3 < valid.mean() < 0.8
+        assert valid.all()                                 # greedy collapse: every internal node has a record
         assert np.array_equal(gw[valid], ow[valid]), "wide nodes: origin, scales, child codes, quantised boxes"
         cnt = np.zeros(2, np.uint64)
         owide = osc.trace_batch(rays, use_bvh=2, counters=cnt)

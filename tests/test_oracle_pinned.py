@@ -206,13 +206,27 @@ def test_oracle_wide_nodes_walk_equals_two_child_and_brute(oracle, make):
     nb, ch = lb["node_bounds"], lb["node_children"]
     for i in np.flatnonzero(valid)[:2000]:
         org = w[i, 0:3].view(np.float32); step = np.array([w[i, 3], w[i, 14], w[i, 15]], np.uint32).view(np.float32) / 32768.0
-        boxes = []                                     # true child boxes in slot order
-        for side in range(2):
-            c = ch[i, side]
-            if c < 0:
-                boxes.append(nb[i, 6 * side:6 * side + 6])
-            else:
-                boxes += [nb[c, 0:6], nb[c, 6:12]]
+        # true child boxes in slot order: the greedy collapse restated (start from the two children, twice open the internal
+        # slot with the largest surface area, ties to the lowest slot; its two children take its place)
+        sl = [(int(ch[i, 0]), nb[i, 0:6]), (int(ch[i, 1]), nb[i, 6:12])]
+        for _ in range(2):
+            s_best, a_best = -1, np.float32(-1.0)
+            for k, (c, b) in enumerate(sl):
+                if c >= 0:
+                    d = (b[3:6] - b[0:3]).astype(np.float32)
+                    ar = np.float32(np.float32(np.float32(d[0] * d[1]) + np.float32(d[1] * d[2])) + np.float32(d[2] * d[0]))
+                    if ar > a_best:
+                        s_best, a_best = k, ar
+            if s_best < 0:
+                break
+            c = sl[s_best][0]
+            sl[s_best:s_best + 1] = [(int(ch[c, 0]), nb[c, 0:6]), (int(ch[c, 1]), nb[c, 6:12])]
+        boxes = [b for _, b in sl]
+        for slot in range(len(sl), 4):                 # unused slots: inverted box, never hit
+            assert all(((w[i, 8 + k] >> (8 * slot)) & 255) == 255 and ((w[i, 11 + k] >> (8 * slot)) & 255) == 0 for k in range(3))
+        for slot, (c, _) in enumerate(sl):
+            if c >= 0:
+                assert int(w[i, 4 + slot]) == c
         for slot, b in enumerate(boxes):
             qlo = np.array([(w[i, 8 + k] >> (8 * slot)) & 255 for k in range(3)], np.float64)
             qhi = np.array([(w[i, 11 + k] >> (8 * slot)) & 255 for k in range(3)], np.float64)

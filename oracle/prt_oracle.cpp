@@ -6,7 +6,7 @@
  * pieces the reference does not have.  Only tests/, __graft_entry__.smoke() and bench.py's
  * cpu_baseline / --impl reference legs may load it; the product (libprt_b200.so) never does.
  *
- * Parity status: PINNED — tests/test_oracle_vs_reference.py checks every function below
+ * Parity status: PINNED — tests/test_oracle_pinned.py checks every function below
  * against the reference's own compiled code (oracle/_ref/libprt_ref.so, built from the
  * sources under /root/reference by oracle/Makefile) and against golden vectors generated from
  * it (tests/golden/, generator tests/golden/make_golden.py).  The reference ships no tests or

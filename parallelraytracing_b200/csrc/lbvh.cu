@@ -5,7 +5,7 @@
 // The reference has no acceleration structure: PrimitiveList::Intersect loops over every
 // primitive (src/core/primitive.cpp:26). This build is what makes that loop O(log n).
 // Integer outputs (Morton codes, sorted order, topology) are bit-exact against the CPU
-// restatement in oracle/prt_oracle.cpp (tests/test_lbvh_gpu.py).
+// restatement in oracle/prt_oracle.cpp (tests/test_gpu_parity.py::test_lbvh_bit_exact).
 #include "prt_internal.h"
 
 namespace prt {

@@ -9,7 +9,8 @@ src/core types (Rickyeeeeee/ParallelRayTracing) as flat POD arrays for the C ABI
 
 All arithmetic that decides bits downstream (camera basis, transforms) is done in float32 in the
 same operation order as glm so that the arrays equal what host/flatten.h produces from the
-reference's own objects (tests/test_scene_flatten.py checks this against oracle/_ref).
+reference's own objects (tests/test_oracle_pinned.py::test_presets_equal_reference_flatten and test_camera_equals_reference check
+this against the vectors generated through oracle/_ref).
 """
 import enum
 import math

@@ -3,7 +3,6 @@
 // (src/backend/cuda_wavefront/renderer.cu:351-370, soa.cpp:37-114), SetCamera (:534-547)
 // and ProgressiveRender's driver loop (:372-433).
 #include "prt_internal.h"
-#include <cstdlib>
 #include <cstring>
 #include <cstdio>
 
@@ -104,12 +103,6 @@ int prt_create(prt_ctx** out, int device) {
         cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess) {
         delete h;
         return set_err(nullptr, PRT_ERR_CUDA, "stream/event creation failed");
-    }
-    // measurement knob (LBVH build): the L2 fetch granularity hint, 32 / 64 / 128 bytes; unset = driver default
-    if (const char* g = getenv("PRT_L2_FETCH_GRANULARITY")) {
-        int v = atoi(g);
-        if (v == 32 || v == 64 || v == 128) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)v);
-        cudaGetLastError();
     }
     *out = h;
     return PRT_OK;

@@ -54,8 +54,8 @@ __global__ void k_prim_bounds(const SphereRec* __restrict__ spheres, int ns,
             lo[1] = fminf(fminf(v0.y, v1.y), v2.y); hi[1] = fmaxf(fmaxf(v0.y, v1.y), v2.y);
             lo[2] = fminf(fminf(v0.z, v1.z), v2.z); hi[2] = fmaxf(fmaxf(v0.z, v1.z), v2.z);
         }
-        amin[q] = make_float4(lo[0], lo[1], lo[2], 0.f);
-        amax[q] = make_float4(hi[0], hi[1], hi[2], 0.f);
+        amin[2 * q] = make_float4(lo[0], lo[1], lo[2], 0.f);            // {min, max} interleaved: one 32-byte sector per box
+        amax[2 * q] = make_float4(hi[0], hi[1], hi[2], 0.f);
     }
     // block reduction of the scene bounds and of the bounds of the box centres (min/max are exact, so order does not matter)
     __shared__ float s_lo[6][8], s_hi[6][8];
@@ -103,7 +103,7 @@ __global__ void k_morton(const float4* __restrict__ amin, const float4* __restri
     if (q >= n) return;
     float lx = ord2f(bounds[0]), ly = ord2f(bounds[1]), lz = ord2f(bounds[2]);
     float hx = ord2f(bounds[3]), hy = ord2f(bounds[4]), hz = ord2f(bounds[5]);
-    float4 a = amin[q], b = amax[q];
+    float4 a = amin[2 * q], b = amax[2 * q];
     float cx = (a.x + b.x) * 0.5f, cy = (a.y + b.y) * 0.5f, cz = (a.z + b.z) * 0.5f;
     uint32_t code = (expand10(quant10(cx, lx, hx)) << 2) | (expand10(quant10(cy, ly, hy)) << 1) |
                     expand10(quant10(cz, lz, hz));
@@ -342,8 +342,8 @@ __global__ void k_refit(int n, const uint32_t* __restrict__ sorted_prim, const f
 #pragma unroll
         for (int k = 0; k < 2; ++k) {
             int c = children[2 * node + k];
-            if (c < 0) { uint32_t q = sorted_prim[~c]; mn[k] = amin[q]; mx[k] = amax[q]; code[k] = leaf_code(~c, q, ns, nq); }
-            else { mn[k] = __ldcg(&node_min[c]); mx[k] = __ldcg(&node_max[c]); code[k] = c; }
+            if (c < 0) { uint32_t q = sorted_prim[~c]; mn[k] = amin[2 * q]; mx[k] = amax[2 * q]; code[k] = leaf_code(~c, q, ns, nq); }
+            else { mn[k] = __ldcg(&node_min[2 * c]); mx[k] = __ldcg(&node_max[2 * c]); code[k] = c; }
         }
         BvhNode nd;
         nd.lmin = make_float4(mn[0].x, mn[0].y, mn[0].z, __int_as_float(code[0]));
@@ -351,8 +351,8 @@ __global__ void k_refit(int n, const uint32_t* __restrict__ sorted_prim, const f
         nd.rmin = make_float4(mn[1].x, mn[1].y, mn[1].z, 0.f);
         nd.rmax = make_float4(mx[1].x, mx[1].y, mx[1].z, 0.f);
         nodes[node] = nd;
-        __stcg(&node_min[node], make_float4(fminf(mn[0].x, mn[1].x), fminf(mn[0].y, mn[1].y), fminf(mn[0].z, mn[1].z), 0.f));
-        __stcg(&node_max[node], make_float4(fmaxf(mx[0].x, mx[1].x), fmaxf(mx[0].y, mx[1].y), fmaxf(mx[0].z, mx[1].z), 0.f));
+        __stcg(&node_min[2 * node], make_float4(fminf(mn[0].x, mn[1].x), fminf(mn[0].y, mn[1].y), fminf(mn[0].z, mn[1].z), 0.f));
+        __stcg(&node_max[2 * node], make_float4(fmaxf(mx[0].x, mx[1].x), fmaxf(mx[0].y, mx[1].y), fmaxf(mx[0].z, mx[1].z), 0.f));
         node = parent[node];
     }
 }
@@ -461,12 +461,12 @@ int lbvh_build(Ctx* c) {
         return PRT_OK;
     }
     const size_t nn = (size_t)n;
-    if ((rc = dev_reserve(c, c->aabb_min, nn * 16)) || (rc = dev_reserve(c, c->aabb_max, nn * 16)) ||
+    if ((rc = dev_reserve(c, c->aabb_min, nn * 32)) ||
         (rc = dev_reserve(c, c->morton, nn * 4)) ||
         (rc = dev_reserve(c, c->keys[0], nn * 4)) || (rc = dev_reserve(c, c->keys[1], nn * 4)) ||
         (rc = dev_reserve(c, c->vals[0], nn * 4)) || (rc = dev_reserve(c, c->vals[1], nn * 4)) ||
         (rc = dev_reserve(c, c->children, nn * 8)) || (rc = dev_reserve(c, c->parent, nn * 8)) ||
-        (rc = dev_reserve(c, c->node_min, nn * 16)) || (rc = dev_reserve(c, c->node_max, nn * 16)) ||
+        (rc = dev_reserve(c, c->node_min, nn * 32)) ||
         (rc = dev_reserve(c, c->flags, nn * 4)) || (rc = dev_reserve(c, c->nodes, nn * sizeof(BvhNode))) ||
         (rc = dev_reserve(c, c->tri_v, nn * 48)) || (rc = dev_reserve(c, c->tri_n, nn * 48)))
         return rc;
@@ -481,8 +481,8 @@ int lbvh_build(Ctx* c) {
     const int T = 256, G = (n + T - 1) / T;
     k_prim_bounds<<<G, T, 0, st>>>((const SphereRec*)c->spheres.p, ns, (const QuadRec*)c->quads.p, nq,
                                    (const float4*)c->tri_in_v.p, nt, (float4*)c->aabb_min.p,
-                                   (float4*)c->aabb_max.p, (int*)c->scene_bounds.p);
-    k_morton<<<G, T, 0, st>>>((const float4*)c->aabb_min.p, (const float4*)c->aabb_max.p, n,
+                                   (float4*)c->aabb_min.p + 1, (int*)c->scene_bounds.p);
+    k_morton<<<G, T, 0, st>>>((const float4*)c->aabb_min.p, (const float4*)c->aabb_min.p + 1, n,
                               (const int*)c->scene_bounds.p + (c->morton_centroid ? 6 : 0), (uint32_t*)c->keys[0].p,
                               (uint32_t*)c->vals[0].p, (uint32_t*)c->morton.p);
     int cur = 0;
@@ -505,9 +505,9 @@ int lbvh_build(Ctx* c) {
     if (n > 1) {
         PRT_CUDA(c, cudaMemsetAsync(c->flags.p, 0, nn * 4, st));
         k_karras<<<G, T, 0, st>>>(skeys, n, (int*)c->children.p, parent, leaf_parent);
-        k_refit<<<G, T, 0, st>>>(n, sprim, (const float4*)c->aabb_min.p, (const float4*)c->aabb_max.p,
+        k_refit<<<G, T, 0, st>>>(n, sprim, (const float4*)c->aabb_min.p, (const float4*)c->aabb_min.p + 1,
                                  (const int*)c->children.p, parent, leaf_parent,
-                                 (float4*)c->node_min.p, (float4*)c->node_max.p, (int*)c->flags.p, ns, nq, (BvhNode*)c->nodes.p);
+                                 (float4*)c->node_min.p, (float4*)c->node_min.p + 1, (int*)c->flags.p, ns, nq, (BvhNode*)c->nodes.p);
         if (want_wide) {
             k_emit_wide<<<G, T, 0, st>>>(n - 1, parent, (const BvhNode*)c->nodes.p, (WideNode*)c->wnodes.p);
             c->wide_built = true;

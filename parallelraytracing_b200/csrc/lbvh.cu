@@ -394,6 +394,23 @@ __device__ __forceinline__ float box_area(const float* lo, const float* hi) {
     return (dx * dy + dy * dz) + dz * dx;
 }
 
+// slot S of a wide node under construction is replaced by the two children `ch` of the node it held; the slots behind
+// it move up by one. S is a template parameter so that every array index is a compile-time constant (registers).
+template <int S>
+__device__ __forceinline__ void open_slot(float (&lo)[4][3], float (&hi)[4][3], int (&code)[4], int ns, const BvhNode& ch) {
+#pragma unroll
+    for (int c = 3; c > S + 1; --c)
+        if (c <= ns) {
+            code[c] = code[c - 1];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) { lo[c][k] = lo[c - 1][k]; hi[c][k] = hi[c - 1][k]; }
+        }
+    lo[S][0] = ch.lmin.x; lo[S][1] = ch.lmin.y; lo[S][2] = ch.lmin.z; hi[S][0] = ch.lmax.x; hi[S][1] = ch.lmax.y; hi[S][2] = ch.lmax.z;
+    lo[S + 1][0] = ch.rmin.x; lo[S + 1][1] = ch.rmin.y; lo[S + 1][2] = ch.rmin.z;
+    hi[S + 1][0] = ch.rmax.x; hi[S + 1][1] = ch.rmax.y; hi[S + 1][2] = ch.rmax.z;
+    code[S] = __float_as_int(ch.lmin.w); code[S + 1] = __float_as_int(ch.lmax.w);
+}
+
 __global__ void k_emit_wide(int n_internal, const int* __restrict__ parent, const BvhNode* __restrict__ nodes,
                             WideNode* __restrict__ wide) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -406,30 +423,33 @@ __global__ void k_emit_wide(int n_internal, const int* __restrict__ parent, cons
         lo[1][0] = nd.rmin.x; lo[1][1] = nd.rmin.y; lo[1][2] = nd.rmin.z; hi[1][0] = nd.rmax.x; hi[1][1] = nd.rmax.y; hi[1][2] = nd.rmax.z;
         code[0] = __float_as_int(nd.lmin.w); code[1] = __float_as_int(nd.lmax.w);
     }
+    // every slot index below is a compile-time constant (open_slot<S>), so the four boxes stay in registers - indexed by
+    // the chosen slot they lived in a 112-byte local-memory frame (12 GB of L2-level traffic on 10 M triangles)
+#pragma unroll
     for (int round = 0; round < 2; ++round) {
         int s = -1; float best = -1.0f;
-        for (int c = 0; c < ns; ++c)
-            if (code[c] >= 0) { const float ar = box_area(lo[c], hi[c]); if (ar > best) { best = ar; s = c; } }   // ties: lowest slot
-        if (s < 0) break;
-        for (int c = ns; c > s + 1; --c) {                               // make room at s + 1
-            code[c] = code[c - 1];
-            for (int k = 0; k < 3; ++k) { lo[c][k] = lo[c - 1][k]; hi[c][k] = hi[c - 1][k]; }
+#pragma unroll
+        for (int c = 0; c < 3; ++c)
+            if (c < ns && code[c] >= 0) { const float ar = box_area(lo[c], hi[c]); if (ar > best) { best = ar; s = c; } }   // ties: lowest slot
+        if (s >= 0) {
+            const int cs = s == 0 ? code[0] : s == 1 ? code[1] : code[2];
+            const BvhNode ch = nodes[cs];
+            if (s == 0) open_slot<0>(lo, hi, code, ns, ch);
+            else if (s == 1) open_slot<1>(lo, hi, code, ns, ch);
+            else open_slot<2>(lo, hi, code, ns, ch);
+            ++ns;
         }
-        const BvhNode ch = nodes[code[s]];
-        lo[s][0] = ch.lmin.x; lo[s][1] = ch.lmin.y; lo[s][2] = ch.lmin.z; hi[s][0] = ch.lmax.x; hi[s][1] = ch.lmax.y; hi[s][2] = ch.lmax.z;
-        lo[s + 1][0] = ch.rmin.x; lo[s + 1][1] = ch.rmin.y; lo[s + 1][2] = ch.rmin.z;
-        hi[s + 1][0] = ch.rmax.x; hi[s + 1][1] = ch.rmax.y; hi[s + 1][2] = ch.rmax.z;
-        code[s] = __float_as_int(ch.lmin.w); code[s + 1] = __float_as_int(ch.lmax.w);
-        ++ns;
     }
     WideNode w;
     float org[3], sc[3];
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         float mn = lo[0][k], mx = hi[0][k];
-        for (int c = 1; c < ns; ++c) { mn = fminf(mn, lo[c][k]); mx = fmaxf(mx, hi[c][k]); }
+#pragma unroll
+        for (int c = 1; c < 4; ++c) if (c < ns) { mn = fminf(mn, lo[c][k]); mx = fmaxf(mx, hi[c][k]); }
         org[k] = mn; sc[k] = pow2_ceil_scale(mx - mn);
         uint32_t ql = 0, qh = 0;
+#pragma unroll
         for (int c = 0; c < 4; ++c) {
             uint32_t a = 255u, b = 0u;                                  // empty slot: inverted box
             if (c < ns) {

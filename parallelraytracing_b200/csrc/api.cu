@@ -39,25 +39,25 @@ void dev_free(DevBuf& b) { if (b.p) cudaFree(b.p); b.p = nullptr; b.bytes = 0; }
 // reads. (Doing this on the host cost 2 s per Init for 10 M triangles: a 960 MB staging vector and a scalar loop.)
 // Flat normal when none is given: cross(v1 - v0, v2 - v0), unnormalised (the shading normalises it).
 __global__ void k_expand_tris(int n, const float* __restrict__ v, const float* __restrict__ nrm, const int* __restrict__ mat,
-                              int mat_default, float4* __restrict__ out_v, float4* __restrict__ out_n, int* __restrict__ out_mat) {
+                              int mat_default, float4* __restrict__ out_v, float4* __restrict__ out_n) {
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n) return;
     float a[9];
 #pragma unroll
     for (int k = 0; k < 9; ++k) a[k] = v[9 * (size_t)t + k];
 #pragma unroll
-    for (int k = 0; k < 3; ++k) out_v[3 * (size_t)t + k] = make_float4(a[3 * k], a[3 * k + 1], a[3 * k + 2], 0.f);
+    for (int k = 0; k < 3; ++k)                                        // 96-byte record {v0, v1 | material, v2, n0, n1, n2}
+        out_v[6 * (size_t)t + k] = make_float4(a[3 * k], a[3 * k + 1], a[3 * k + 2], k == 1 ? __int_as_float(mat ? mat[t] : mat_default) : 0.f);
     if (nrm) {
 #pragma unroll
         for (int k = 0; k < 3; ++k)
-            out_n[3 * (size_t)t + k] = make_float4(nrm[9 * (size_t)t + 3 * k], nrm[9 * (size_t)t + 3 * k + 1], nrm[9 * (size_t)t + 3 * k + 2], 0.f);
+            out_n[6 * (size_t)t + k] = make_float4(nrm[9 * (size_t)t + 3 * k], nrm[9 * (size_t)t + 3 * k + 1], nrm[9 * (size_t)t + 3 * k + 2], 0.f);
     } else {
         float e1x = a[3] - a[0], e1y = a[4] - a[1], e1z = a[5] - a[2], e2x = a[6] - a[0], e2y = a[7] - a[1], e2z = a[8] - a[2];
         float nx = e1y * e2z - e2y * e1z, ny = e1z * e2x - e2z * e1x, nz = e1x * e2y - e2x * e1y;
 #pragma unroll
-        for (int k = 0; k < 3; ++k) out_n[3 * (size_t)t + k] = make_float4(nx, ny, nz, 0.f);
+        for (int k = 0; k < 3; ++k) out_n[6 * (size_t)t + k] = make_float4(nx, ny, nz, 0.f);
     }
-    out_mat[t] = mat ? mat[t] : mat_default;
 }
 
 static int upload(Ctx* c, DevBuf& b, const void* host, size_t bytes) {
@@ -186,12 +186,10 @@ int prt_set_scene(prt_ctx* ctx, const prt_sphere* spheres, int n_spheres, const 
         rc = upload(c, raw_v, tri_verts, nt * 36);
         if (!rc && tri_normals) rc = upload(c, raw_n, tri_normals, nt * 36);
         if (!rc && tri_material) rc = upload(c, raw_m, tri_material, nt * 4);
-        if (!rc) rc = dev_reserve(c, c->tri_in_v, nt * 48);
-        if (!rc) rc = dev_reserve(c, c->tri_in_n, nt * 48);
-        if (!rc) rc = dev_reserve(c, c->tri_in_mat, nt * 4);
+        if (!rc) rc = dev_reserve(c, c->tri_in_v, nt * 96);
         if (!rc) {
             k_expand_tris<<<(unsigned)((nt + 255) / 256), 256, 0, c->stream>>>(n_tris, (const float*)raw_v.p, (const float*)raw_n.p,
-                (const int*)raw_m.p, tri_material_default, (float4*)c->tri_in_v.p, (float4*)c->tri_in_n.p, (int*)c->tri_in_mat.p);
+                (const int*)raw_m.p, tri_material_default, (float4*)c->tri_in_v.p, (float4*)c->tri_in_v.p + 3);
         }
         cudaError_t e = cudaStreamSynchronize(c->stream);
         dev_free(raw_v); dev_free(raw_n); dev_free(raw_m);

@@ -49,7 +49,7 @@ __global__ void k_prim_bounds(const SphereRec* __restrict__ spheres, int ns,
             }
         } else {
             int t = q - ns - nq;
-            float4 v0 = tri_v[3 * t], v1 = tri_v[3 * t + 1], v2 = tri_v[3 * t + 2];
+            float4 v0 = tri_v[6 * (size_t)t], v1 = tri_v[6 * (size_t)t + 1], v2 = tri_v[6 * (size_t)t + 2];
             lo[0] = fminf(fminf(v0.x, v1.x), v2.x); hi[0] = fmaxf(fmaxf(v0.x, v1.x), v2.x);
             lo[1] = fminf(fminf(v0.y, v1.y), v2.y); hi[1] = fmaxf(fmaxf(v0.y, v1.y), v2.y);
             lo[2] = fminf(fminf(v0.z, v1.z), v2.z); hi[2] = fmaxf(fmaxf(v0.z, v1.z), v2.z);
@@ -360,16 +360,17 @@ __global__ void k_refit(int n, const uint32_t* __restrict__ sorted_prim, const f
 // triangle planes in leaf-slot order so a leaf code indexes them directly
 __global__ void k_gather_tris(int n, int ns, int nq, int tri_prim_base, const uint32_t* __restrict__ sorted_prim,
                               const float4* __restrict__ in_v, const float4* __restrict__ in_n,
-                              const int* __restrict__ in_mat, float4* __restrict__ out_v, float4* __restrict__ out_n) {
+                              float4* __restrict__ out_v, float4* __restrict__ out_n) {
     int pos = blockIdx.x * blockDim.x + threadIdx.x;
     if (pos >= n) return;
     int q = (int)sorted_prim[pos];
     if (q < ns + nq) return;
     int t = q - ns - nq;
-    float4 a = in_v[3 * t], b = in_v[3 * t + 1], c = in_v[3 * t + 2];
-    a.w = __int_as_float(tri_prim_base + t); b.w = __int_as_float(in_mat[t]); c.w = 0.f;
+    // one 96-byte input record per triangle (positions, material in v1.w, normals): one random gather instead of three
+    float4 a = in_v[6 * (size_t)t], b = in_v[6 * (size_t)t + 1], c = in_v[6 * (size_t)t + 2];
+    a.w = __int_as_float(tri_prim_base + t); c.w = 0.f;
     out_v[3 * pos] = a; out_v[3 * pos + 1] = b; out_v[3 * pos + 2] = c;
-    out_n[3 * pos] = in_n[3 * t]; out_n[3 * pos + 1] = in_n[3 * t + 1]; out_n[3 * pos + 2] = in_n[3 * t + 2];
+    out_n[3 * pos] = in_n[6 * (size_t)t]; out_n[3 * pos + 1] = in_n[6 * (size_t)t + 1]; out_n[3 * pos + 2] = in_n[6 * (size_t)t + 2];
 }
 
 // ------------------------------------------------------------------ 4-wide quantised nodes
@@ -540,7 +541,7 @@ int lbvh_build(Ctx* c) {
     }
     if (nt > 0)
         k_gather_tris<<<G, T, 0, st>>>(n, ns, nq, c->tri_prim_base, sprim, (const float4*)c->tri_in_v.p,
-                                       (const float4*)c->tri_in_n.p, (const int*)c->tri_in_mat.p,
+                                       (const float4*)c->tri_in_v.p + 3,
                                        (float4*)c->tri_v.p, (float4*)c->tri_n.p);
     PRT_CUDA(c, cudaEventRecord(c->ev1, st));
     PRT_CUDA(c, cudaStreamSynchronize(st));

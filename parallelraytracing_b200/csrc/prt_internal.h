@@ -23,7 +23,7 @@ struct Ctx {
     int n_spheres = 0, n_quads = 0, n_tris = 0, n_prims = 0, n_mats = 0;
     int tri_prim_base = 0;
     DevBuf spheres, quads, quad_mat, mats;
-    DevBuf tri_in_v, tri_in_n, tri_in_mat;     // input order: 3 float4 / tri (w unused), 3 float4 / tri, int / tri
+    DevBuf tri_in_v, tri_in_n, tri_in_mat;     // tri_in_v, input order: 6 float4 / tri {v0, v1 (w = material), v2, n0, n1, n2}; the other two unused
     DevBuf prim_id_of_q;                        // int per q: reference list index
     float sky[3] = {0.4f, 0.3f, 0.6f};
     bool scene_set = false;

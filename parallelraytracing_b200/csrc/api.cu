@@ -114,7 +114,7 @@ void prt_destroy(prt_ctx* ctx) {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     DevBuf* bufs[] = {&c->spheres, &c->quads, &c->quad_mat, &c->mats, &c->tri_in_v, &c->tri_in_n, &c->tri_in_mat,
-                      &c->prim_id_of_q, &c->aabb_min, &c->aabb_max, &c->scene_bounds, &c->keys[0], &c->keys[1],
+                      &c->prim_id_of_q, &c->aabb_min, &c->leaf_box, &c->scene_bounds, &c->keys[0], &c->keys[1],
                       &c->vals[0], &c->vals[1], &c->block_hist, &c->children, &c->parent, &c->node_min, &c->node_max,
                       &c->flags, &c->nodes, &c->wnodes, &c->tri_v, &c->tri_n, &c->morton, &c->accum_own, &c->display,
                       &c->q_o[0], &c->q_o[1], &c->q_d[0], &c->q_d[1], &c->q_b[0], &c->q_b[1], &c->hits, &c->contrib,

@@ -327,6 +327,7 @@ __device__ __forceinline__ int leaf_code(int pos, uint32_t q, int ns, int nq) {
 
 // bottom-up refit: the second thread to reach a node merges the child boxes and, having both child boxes
 // in registers, writes the 64-byte traversal node as well (no separate emit pass)
+// amin / amax: the leaf boxes in sorted (leaf-slot) order, {min, max} pairs written by k_gather_tris
 __global__ void k_refit(int n, const uint32_t* __restrict__ sorted_prim, const float4* __restrict__ amin,
                         const float4* __restrict__ amax, const int* __restrict__ children,
                         const int* __restrict__ parent, const int* __restrict__ leaf_parent,
@@ -342,7 +343,7 @@ __global__ void k_refit(int n, const uint32_t* __restrict__ sorted_prim, const f
 #pragma unroll
         for (int k = 0; k < 2; ++k) {
             int c = children[2 * node + k];
-            if (c < 0) { uint32_t q = sorted_prim[~c]; mn[k] = amin[2 * q]; mx[k] = amax[2 * q]; code[k] = leaf_code(~c, q, ns, nq); }
+            if (c < 0) { uint32_t q = sorted_prim[~c]; mn[k] = amin[2 * (size_t)~c]; mx[k] = amax[2 * (size_t)~c]; code[k] = leaf_code(~c, q, ns, nq); }
             else { mn[k] = __ldcg(&node_min[2 * c]); mx[k] = __ldcg(&node_max[2 * c]); code[k] = c; }
         }
         BvhNode nd;
@@ -360,14 +361,19 @@ __global__ void k_refit(int n, const uint32_t* __restrict__ sorted_prim, const f
 // triangle planes in leaf-slot order so a leaf code indexes them directly
 __global__ void k_gather_tris(int n, int ns, int nq, int tri_prim_base, const uint32_t* __restrict__ sorted_prim,
                               const float4* __restrict__ in_v, const float4* __restrict__ in_n,
-                              float4* __restrict__ out_v, float4* __restrict__ out_n) {
+                              float4* __restrict__ out_v, float4* __restrict__ out_n,
+                              const float4* __restrict__ prim_box, float4* __restrict__ leaf_box) {
     int pos = blockIdx.x * blockDim.x + threadIdx.x;
     if (pos >= n) return;
     int q = (int)sorted_prim[pos];
-    if (q < ns + nq) return;
+    // leaf boxes in SORTED order for the refit (written coalesced here, where all 32 lanes work, instead of gathered there
+    // at 5-6 live lanes per warp); a triangle's box comes from the vertices this thread loads anyway - same min/max as k_prim_bounds
+    if (q < ns + nq) { leaf_box[2 * (size_t)pos] = prim_box[2 * (size_t)q]; leaf_box[2 * (size_t)pos + 1] = prim_box[2 * (size_t)q + 1]; return; }
     int t = q - ns - nq;
     // one 96-byte input record per triangle (positions, material in v1.w, normals): one random gather instead of three
     float4 a = in_v[6 * (size_t)t], b = in_v[6 * (size_t)t + 1], c = in_v[6 * (size_t)t + 2];
+    leaf_box[2 * (size_t)pos] = make_float4(fminf(fminf(a.x, b.x), c.x), fminf(fminf(a.y, b.y), c.y), fminf(fminf(a.z, b.z), c.z), 0.f);
+    leaf_box[2 * (size_t)pos + 1] = make_float4(fmaxf(fmaxf(a.x, b.x), c.x), fmaxf(fmaxf(a.y, b.y), c.y), fmaxf(fmaxf(a.z, b.z), c.z), 0.f);
     a.w = __int_as_float(tri_prim_base + t); c.w = 0.f;
     out_v[3 * pos] = a; out_v[3 * pos + 1] = b; out_v[3 * pos + 2] = c;
     out_n[3 * pos] = in_n[6 * (size_t)t]; out_n[3 * pos + 1] = in_n[6 * (size_t)t + 1]; out_n[3 * pos + 2] = in_n[6 * (size_t)t + 2];
@@ -482,7 +488,7 @@ int lbvh_build(Ctx* c) {
         return PRT_OK;
     }
     const size_t nn = (size_t)n;
-    if ((rc = dev_reserve(c, c->aabb_min, nn * 32)) ||
+    if ((rc = dev_reserve(c, c->aabb_min, nn * 32)) || (rc = dev_reserve(c, c->leaf_box, nn * 32)) ||
         (rc = dev_reserve(c, c->morton, nn * 4)) ||
         (rc = dev_reserve(c, c->keys[0], nn * 4)) || (rc = dev_reserve(c, c->keys[1], nn * 4)) ||
         (rc = dev_reserve(c, c->vals[0], nn * 4)) || (rc = dev_reserve(c, c->vals[1], nn * 4)) ||
@@ -526,7 +532,10 @@ int lbvh_build(Ctx* c) {
     if (n > 1) {
         PRT_CUDA(c, cudaMemsetAsync(c->flags.p, 0, nn * 4, st));
         k_karras<<<G, T, 0, st>>>(skeys, n, (int*)c->children.p, parent, leaf_parent);
-        k_refit<<<G, T, 0, st>>>(n, sprim, (const float4*)c->aabb_min.p, (const float4*)c->aabb_min.p + 1,
+        k_gather_tris<<<G, T, 0, st>>>(n, ns, nq, c->tri_prim_base, sprim, (const float4*)c->tri_in_v.p,
+                                       (const float4*)c->tri_in_v.p + 3, (float4*)c->tri_v.p, (float4*)c->tri_n.p,
+                                       (const float4*)c->aabb_min.p, (float4*)c->leaf_box.p);
+        k_refit<<<G, T, 0, st>>>(n, sprim, (const float4*)c->leaf_box.p, (const float4*)c->leaf_box.p + 1,
                                  (const int*)c->children.p, parent, leaf_parent,
                                  (float4*)c->node_min.p, (float4*)c->node_min.p + 1, (int*)c->flags.p, ns, nq, (BvhNode*)c->nodes.p);
         if (want_wide) {
@@ -539,10 +548,10 @@ int lbvh_build(Ctx* c) {
         uint32_t payload = ns ? PRT_MAKE_LEAF(0, 0) : nq ? PRT_MAKE_LEAF(1, 0) : PRT_MAKE_LEAF(2, 0);
         c->root_code = ~(int)payload;
     }
-    if (nt > 0)
+    if (n == 1 && nt > 0)                                                 // n > 1: launched before the refit, above
         k_gather_tris<<<G, T, 0, st>>>(n, ns, nq, c->tri_prim_base, sprim, (const float4*)c->tri_in_v.p,
-                                       (const float4*)c->tri_in_v.p + 3,
-                                       (float4*)c->tri_v.p, (float4*)c->tri_n.p);
+                                       (const float4*)c->tri_in_v.p + 3, (float4*)c->tri_v.p, (float4*)c->tri_n.p,
+                                       (const float4*)c->aabb_min.p, (float4*)c->leaf_box.p);
     PRT_CUDA(c, cudaEventRecord(c->ev1, st));
     PRT_CUDA(c, cudaStreamSynchronize(st));
     PRT_CUDA(c, cudaGetLastError());

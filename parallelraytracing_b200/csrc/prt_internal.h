@@ -29,7 +29,7 @@ struct Ctx {
     bool scene_set = false;
 
     // ---- LBVH ----
-    DevBuf aabb_min, aabb_max;                  // aabb_min: {min, max} float4 pairs per q (32 B, one sector per gather); aabb_max unused
+    DevBuf aabb_min, leaf_box;                  // {min, max} float4 pairs (32 B per box): per q in input order / per leaf slot in sorted order
     DevBuf scene_bounds;                        // 6 ordered-int floats
     DevBuf keys[2], vals[2];                    // radix sort ping-pong
     DevBuf block_hist;                          // digit-major per-block histograms

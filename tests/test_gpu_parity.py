@@ -421,6 +421,14 @@ def test_edge_cases(ctx):
     ctx.clear_accum(); ctx.render(3, 0, seed=1)                          # depth 0: TraceRay returns 0
     assert not ctx.read_accum().any() and ctx.accum_spp() == 3
     assert len(ctx.trace_batch(np.zeros(0, util.ray_dt))) == 0
+    # ONE triangle: the root is the leaf, no refit - the triangle planes (and the material in v1.w) must still be gathered
+    b = S.SceneBuilder("one_tri"); m = b.emissive((5, 6, 7))
+    b.add_triangles(np.array([[[-1, -1, 0], [1, -1, 0], [0, 1, 0]]], np.float32), None, m)
+    ctx.set_scene(b.build()); ctx.build_bvh()
+    rays = np.zeros(2, util.ray_dt)
+    rays["oz"] = 3.0; rays["dz"] = -1.0; rays["ox"][1] = 5.0            # ray 0 through the centre, ray 1 past it
+    h = ctx.trace_batch(rays)
+    assert h["prim_id"][0] == 0 and abs(h["t"][0] - 3.0) < 1e-5 and h["material"][0] == m and h["prim_id"][1] < 0
     with pytest.raises(PrtError):
         ctx.render(1, 99)
 

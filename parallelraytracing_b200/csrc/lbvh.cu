@@ -336,13 +336,17 @@ __global__ void k_refit(int n, const uint32_t* __restrict__ sorted_prim, const f
     if (pos >= n) return;
     int node = leaf_parent[pos];
     while (node >= 0) {
+        // topology (written by k_karras, read-only here) is fetched BEFORE the fence/atomic so that its latency overlaps
+        // theirs: per level the dependent chain is atomic -> child boxes, not atomic -> children -> boxes -> parent
+        const int2 ch = __ldg(reinterpret_cast<const int2*>(children) + node);
+        const int up = __ldg(&parent[node]);
         __threadfence();
         if (atomicAdd(&flags[node], 1) == 0) return;
         __threadfence();
         float4 mn[2], mx[2]; int code[2];
 #pragma unroll
         for (int k = 0; k < 2; ++k) {
-            int c = children[2 * node + k];
+            int c = k ? ch.y : ch.x;
             if (c < 0) { uint32_t q = sorted_prim[~c]; mn[k] = amin[2 * (size_t)~c]; mx[k] = amax[2 * (size_t)~c]; code[k] = leaf_code(~c, q, ns, nq); }
             else { mn[k] = __ldcg(&node_min[2 * c]); mx[k] = __ldcg(&node_max[2 * c]); code[k] = c; }
         }
@@ -354,7 +358,7 @@ __global__ void k_refit(int n, const uint32_t* __restrict__ sorted_prim, const f
         nodes[node] = nd;
         __stcg(&node_min[2 * node], make_float4(fminf(mn[0].x, mn[1].x), fminf(mn[0].y, mn[1].y), fminf(mn[0].z, mn[1].z), 0.f));
         __stcg(&node_max[2 * node], make_float4(fmaxf(mx[0].x, mx[1].x), fmaxf(mx[0].y, mx[1].y), fmaxf(mx[0].z, mx[1].z), 0.f));
-        node = parent[node];
+        node = up;
     }
 }
 

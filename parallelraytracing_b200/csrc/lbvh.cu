@@ -335,14 +335,22 @@ __global__ void k_refit(int n, const uint32_t* __restrict__ sorted_prim, const f
     int pos = blockIdx.x * blockDim.x + threadIdx.x;
     if (pos >= n) return;
     int node = leaf_parent[pos];
+    bool first = true;
     while (node >= 0) {
         // topology (written by k_karras, read-only here) is fetched BEFORE the fence/atomic so that its latency overlaps
         // theirs: per level the dependent chain is atomic -> child boxes, not atomic -> children -> boxes -> parent
         const int2 ch = __ldg(reinterpret_cast<const int2*>(children) + node);
         const int up = __ldg(&parent[node]);
-        __threadfence();
-        if (atomicAdd(&flags[node], 1) == 0) return;
-        __threadfence();
+        if (first && (ch.x & ch.y) < 0) {
+            // both children are leaves (only possible on a thread's first level): the left leaf's thread merges, the right
+            // one stops - no counter, no fences, the leaf boxes were written by an earlier kernel
+            if (pos == ~ch.y) return;
+        } else {
+            if (!first) __threadfence();                                // publish the box this thread wrote one level below
+            if (atomicAdd(&flags[node], 1) == 0) return;
+            __threadfence();
+        }
+        first = false;
         float4 mn[2], mx[2]; int code[2];
 #pragma unroll
         for (int k = 0; k < 2; ++k) {

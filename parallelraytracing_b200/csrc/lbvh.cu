@@ -467,12 +467,13 @@ __global__ void k_emit_wide(int n_internal, const int* __restrict__ parent, cons
 #pragma unroll
         for (int c = 1; c < 4; ++c) if (c < ns) { mn = fminf(mn, lo[c][k]); mx = fmaxf(mx, hi[c][k]); }
         org[k] = mn; sc[k] = pow2_ceil_scale(mx - mn);
+        const float rs = 1.0f / sc[k];                                  // sc is a power of two in [2^-60, 2^121]: x * rs == x / sc bit for bit
         uint32_t ql = 0, qh = 0;
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
             uint32_t a = 255u, b = 0u;                                  // empty slot: inverted box
             if (c < ns) {
-                float fl = floorf((lo[c][k] - mn) / sc[k] - 0.015625f), fh = ceilf((hi[c][k] - mn) / sc[k] + 0.015625f);
+                float fl = floorf((lo[c][k] - mn) * rs - 0.015625f), fh = ceilf((hi[c][k] - mn) * rs + 0.015625f);
                 a = (uint32_t)fminf(fmaxf(fl, 0.0f), 255.0f); b = (uint32_t)fminf(fmaxf(fh, 0.0f), 255.0f);
             }
             ql |= a << (8 * c); qh |= b << (8 * c);

@@ -125,6 +125,10 @@ typedef struct prt_stats {
     int32_t  n_prims;
     int32_t  n_nodes;
     int32_t  primary_launches;            /* bounce-0 kernel launches (= waves) of the last prt_render */
+    int32_t  bvh_builder;                 /* hierarchy of the last prt_build_bvh: 1 PLOC, 0 Karras (LBVH; also the fallback) */
+    int32_t  bvh_height;                  /* height of the PLOC tree (0 for Karras: bounded by the key width instead)     */
+    int32_t  ploc_rounds;                 /* clustering rounds the PLOC build took                                         */
+    int32_t  _padi;
 } prt_stats;
 
 /* ---- life cycle --------------------------------------------------------------------
@@ -153,7 +157,9 @@ int  prt_set_scene(prt_ctx* ctx,
                    const float sky_rgb[3]);
 
 /* GPU LBVH build over the current scene: primitive AABBs -> scene bounds -> 30-bit Morton
- * codes -> stable LSD radix sort -> Karras hierarchy -> bottom-up refit.
+ * codes -> stable LSD radix sort -> hierarchy over the sorted leaves: PLOC (locally-ordered agglomerative clustering,
+ * the tree-quality pass of SURVEY 8f-4; option bvh_builder=1, default) or the Karras hierarchy + bottom-up refit
+ * (bvh_builder=0; also the automatic fallback when PLOC does not converge or its tree is too deep for the stack).
  * The reference has no acceleration structure (primitive.cpp:26 loops over every
  * primitive); this replaces that loop. */
 int  prt_build_bvh(prt_ctx* ctx);
@@ -219,6 +225,14 @@ int  prt_resolve_display(prt_ctx* ctx, float exposure, float gamma, uint8_t* hos
  * quantised nodes the render path uses (same hits, fewer node visits). */
 int  prt_trace_batch(prt_ctx* ctx, const prt_ray* rays, int n, prt_hit* out, int use_bvh);
 
+/* MaterialHandle::{Emit,Scatter} known answers (src/core/material.h:11-161, math.h:10-50) through the device function the
+ * render path shades with. Record k: material mats[k], incoming unit direction in_dirs[3k..], hit normal facing the ray
+ * normals[3k..], IsFrontFace fronts[k], RNG stream of (seed, pixel = keys[3k], sample = keys[3k+1], bounce = keys[3k+2]).
+ * out: n x 10 floats {scattered (0/1), attenuation rgb, scattered direction (normalised; 0 when the path ends), emission rgb}.
+ * Host buffers. The reference's own answers for 600 such records are in tests/golden (made by oracle/ref_harness.cpp). */
+int  prt_debug_scatter(prt_ctx* ctx, const prt_material* mats, const float* in_dirs, const float* normals,
+                       const int32_t* fronts, const uint32_t* keys, uint64_t seed, int n, float* out);
+
 /* LBVH internals for the bit-exact integer checks. Any pointer may be NULL.
  *   morton[n_prims]        30-bit code per primitive, input order
  *   sorted_prim[n_prims]   primitive index (input order) at each sorted position
@@ -241,7 +255,7 @@ int  prt_enable_counters(prt_ctx* ctx, int on);
 int  prt_get_stats(prt_ctx* ctx, prt_stats* out);
 
 /* Tuning knobs (all optional): "wave_paths" (paths in flight per wave), "ctas_per_sm", "fused", "fused_max_prims",
- * "brute_max_prims", "persistent", "pt_refill", "pt_refill_wide", "bvh_wide", "wide_min_prims", "overlap",
+ * "brute_max_prims", "persistent", "pt_refill", "pt_refill_wide", "bvh_wide", "wide_min_prims", "bvh_builder", "ploc_radius", "overlap",
  * "stage_timing", "rr_start", "firefly_clamp_milli", and for small waves (one sample per call, the reference's
  * ProgressiveRender granularity) "tail_bounce" (0 = one launch per bounce always), "tail_adaptive", "tail_rays", "tail_rays_staged",
  * "tail_max_paths": bounces from the tail start on run inside one kernel; "sort_rays", "sort_key_bits",

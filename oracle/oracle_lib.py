@@ -38,6 +38,8 @@ class Oracle:
         lib.po_build_lbvh.argtypes = [vp]
         lib.po_get_lbvh.argtypes = [vp] * 7
         lib.po_get_wide.argtypes = [vp, vp, vp]
+        lib.po_set_builder.argtypes = [vp, i32, i32]
+        lib.po_ploc_rounds.argtypes = [vp]; lib.po_bvh_height.argtypes = [vp]; lib.po_builder_used.argtypes = [vp]
         lib.po_set_estimator.argtypes = [vp, i32, C.c_float]
         lib.po_trace_batch.argtypes = [vp, vp, i32, vp, i32, vp, i32]
         lib.po_camera_dirs.argtypes = [C.POINTER(CCamera), vp]
@@ -46,6 +48,7 @@ class Oracle:
         lib.po_trace_pixel.argtypes = [vp, C.POINTER(CCamera), i32, i32, i32, i32, u64, i32, vp]
         lib.po_rng_stream.argtypes = [u64, u32, u32, u32, i32, vp]
         lib.po_resolve_display.argtypes = [vp, i32, f32, f32, f32, vp]
+        lib.po_scatter.argtypes = [vp, vp, vp, i32, u64, u32, u32, u32, vp]
 
     def scene(self, sd):
         return OracleScene(self, sd)
@@ -54,6 +57,14 @@ class Oracle:
         c = cam.to_c()
         out = np.empty((cam.height, cam.width, 3), np.float32)
         self.lib.po_camera_dirs(C.byref(c), _ptr(out))
+        return out
+
+    def scatter(self, mat, in_dir, normal, front, seed, pixel, sample, bounce):
+        """One MaterialHandle::Scatter/Emit record -> 10 floats {ok, atten.rgb, out_dir.xyz, emit.rgb}."""
+        m = np.zeros(1, material_dt); m[0] = mat
+        i_, n_ = (np.ascontiguousarray(x, np.float32) for x in (in_dir, normal))
+        out = np.zeros(10, np.float32)
+        self.lib.po_scatter(_ptr(m), _ptr(i_), _ptr(n_), int(front), seed, pixel, sample, bounce, _ptr(out))
         return out
 
     def rng_stream(self, seed, pixel, sample, bounce, n):
@@ -86,6 +97,15 @@ class OracleScene:
             self.lib.po_scene_destroy(self.h)
         except Exception:
             pass
+
+    def set_builder(self, builder=1, radius=4):
+        """Hierarchy over the sorted leaves: 1 = PLOC (device default; falls back to Karras like lbvh.cu), 0 = Karras (plain LBVH)."""
+        self.lib.po_set_builder(self.h, int(builder), int(radius))
+        self.built = False
+
+    def build_info(self):
+        self.build_lbvh()
+        return dict(builder=self.lib.po_builder_used(self.h), height=self.lib.po_bvh_height(self.h), rounds=self.lib.po_ploc_rounds(self.h))
 
     def build_lbvh(self):
         if not self.built:

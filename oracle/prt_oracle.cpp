@@ -102,6 +102,8 @@ struct Scene {
     std::vector<WNode> wide;            /* indexed like the internal nodes; only even-depth entries are meaningful */
     std::vector<uint8_t> wide_valid;
     bool built = false;
+    int ploc_rounds = 0, height = 0, builder_used = 0;
+    int builder = 1, ploc_radius = 4;   /* 0: Karras hierarchy over the sorted codes (LBVH); 1: PLOC over the same sorted order */
     int rr_start = -1; float clamp = INFINITY;      /* estimator options of the device path (default off), po_set_estimator */
     int n_prims() const { return (int)(spheres.size() + quads.size() + tris.size()); }
 };
@@ -265,6 +267,64 @@ void prim_bounds(const Scene& sc, int q, V3& lo, V3& hi) {
     }
 }
 
+/* PLOC - parallel locally-ordered clustering (Meister & Bittner 2018) over the Morton-sorted leaves; restatement of
+ * lbvh.cu:k_ploc. Every round, each cluster i looks at the clusters within `radius` positions of it in the current
+ * (Morton-ordered) array and picks the one whose union box has the smallest half-area (ties: position i^1 if it is among them - so that runs of identical boxes pair up instead of
+ * forming a chain -, else the lowest position; either way the globally closest pair is mutual, so every round merges); mutual
+ * nearest neighbours merge into a new internal node that takes the place of the lower position; the array is compacted,
+ * order kept. Node indices are handed out from the top (n-2) downwards in merge order (by round, then by position), so
+ * the last merge - the root - is node 0, like the Karras numbering. Returns false when the clustering does not converge
+ * within PLOC_MAX_ROUNDS rounds or the tree is deeper than PLOC_MAX_HEIGHT (the device stack bound): the caller then
+ * builds the Karras hierarchy instead, exactly like lbvh.cu. The reference has no counterpart (it has no BVH). */
+const int PLOC_MAX_ROUNDS = 192, PLOC_MAX_HEIGHT = 84;
+bool build_ploc(Scene& sc) {
+    const int n = sc.n_prims(), R = sc.ploc_radius;
+    sc.ploc_rounds = 0; sc.height = 0;
+    if (n < 2) return true;
+    std::vector<int> code(n), code2(n), hgt(n, 0), hgt2(n);  /* code >= 0 internal node, < 0 = ~leaf position */
+    std::vector<V3> lo(n), hi(n), lo2(n), hi2(n);
+    for (int p = 0; p < n; ++p) { code[p] = ~p; uint32_t q = sc.sorted_prim[p]; lo[p] = sc.amin[q]; hi[p] = sc.amax[q]; }
+    std::vector<int> nn(n);
+    int c = n, next = n - 1;                               /* the k-th merge from now on gets id next - 1 - k */
+    while (c > 1) {
+        if (sc.ploc_rounds >= PLOC_MAX_ROUNDS) return false;
+        for (int i = 0; i < c; ++i) {
+            float best = INFINITY; int bj = -1;
+            const int j0 = std::max(0, i - R), j1 = std::min(c - 1, i + R);
+            for (int j = j0; j <= j1; ++j) {
+                if (j == i) continue;
+                const float dx = fmaxf(hi[i].x, hi[j].x) - fminf(lo[i].x, lo[j].x);
+                const float dy = fmaxf(hi[i].y, hi[j].y) - fminf(lo[i].y, lo[j].y);
+                const float dz = fmaxf(hi[i].z, hi[j].z) - fminf(lo[i].z, lo[j].z);
+                const float a = (dx * dy + dy * dz) + dz * dx;
+                if (a < best || (a == best && j == (i ^ 1))) { best = a; bj = j; }   /* ties: the partner i^1, else the lowest position */
+            }
+            nn[i] = bj;
+        }
+        int out = 0;
+        for (int i = 0; i < c; ++i) {
+            const int j = nn[i];
+            if (nn[j] == i) {
+                if (i > j) continue;                       /* absorbed by position j < i */
+                const int id = --next;
+                sc.children[2 * id] = code[i]; sc.children[2 * id + 1] = code[j];
+                if (code[i] >= 0) sc.parent[code[i]] = id; else sc.leaf_parent[~code[i]] = id;
+                if (code[j] >= 0) sc.parent[code[j]] = id; else sc.leaf_parent[~code[j]] = id;
+                V3 mn = mk(fminf(lo[i].x, lo[j].x), fminf(lo[i].y, lo[j].y), fminf(lo[i].z, lo[j].z));
+                V3 mx = mk(fmaxf(hi[i].x, hi[j].x), fmaxf(hi[i].y, hi[j].y), fmaxf(hi[i].z, hi[j].z));
+                sc.node_min[id] = mn; sc.node_max[id] = mx;
+                code2[out] = id; lo2[out] = mn; hi2[out] = mx; hgt2[out] = std::max(hgt[i], hgt[j]) + 1; ++out;
+            } else { code2[out] = code[i]; lo2[out] = lo[i]; hi2[out] = hi[i]; hgt2[out] = hgt[i]; ++out; }
+        }
+        code.swap(code2); lo.swap(lo2); hi.swap(hi2); hgt.swap(hgt2);
+        c = out;
+        ++sc.ploc_rounds;
+    }
+    sc.parent[0] = -1;
+    sc.height = hgt[0];
+    return sc.height <= PLOC_MAX_HEIGHT;
+}
+
 void build_lbvh(Scene& sc) {
     int n = sc.n_prims();
     sc.amin.resize(n); sc.amax.resize(n); sc.morton.resize(n); sc.sorted_prim.resize(n); sc.sorted_key.resize(n);
@@ -294,6 +354,9 @@ void build_lbvh(Scene& sc) {
     int ni = n > 1 ? n - 1 : 0;
     sc.children.assign(2 * (size_t)ni, 0); sc.parent.assign(ni, -1); sc.leaf_parent.assign(n, -1);
     sc.node_min.resize(ni); sc.node_max.resize(ni);
+    sc.builder_used = 0;
+    if (sc.builder == 1 && build_ploc(sc)) { sc.builder_used = 1; sc.built = true; return; }
+    sc.children.assign(2 * (size_t)ni, 0); sc.parent.assign(ni, -1); sc.leaf_parent.assign(n, -1);
     const std::vector<uint32_t>& k = sc.sorted_key;
     for (int i = 0; i < ni; ++i) {                       /* Karras 2012, one internal node per i */
         int d = (delta(k, n, i, i + 1) - delta(k, n, i, i - 1)) >= 0 ? 1 : -1;
@@ -346,6 +409,11 @@ inline void child_box(const Scene& sc, int ch, V3& mn, V3& mx) {
     else { mn = sc.node_min[ch]; mx = sc.node_max[ch]; }
 }
 
+/* deepest traversal stack any ray needed since the last reset, in entries of the DEVICE stack (its DONE sentinel included):
+ * the device kernels hold PRT stack entries in shared + local memory (wavefront.cu: STACK_SMEM + STACK_LOCAL) */
+std::atomic<int> g_max_stack{0};
+inline void note_stack(int entries) { int cur = g_max_stack.load(std::memory_order_relaxed); while (entries > cur && !g_max_stack.compare_exchange_weak(cur, entries)) {} }
+
 /* stack traversal, near child first; same visiting order as the device kernel so the
  * node / primitive counters are comparable */
 Hit closest_bvh(const Scene& sc, V3 o, V3 d, uint64_t* n_nodes, uint64_t* n_tests) {
@@ -355,7 +423,7 @@ Hit closest_bvh(const Scene& sc, V3 o, V3 d, uint64_t* n_nodes, uint64_t* n_test
     V3 inv = mk(safe_inv(d.x), safe_inv(d.y), safe_inv(d.z));
     Shear rs = make_shear(d);
     V3 dn = normalize(d);
-    int stack[128]; int sp = 0;
+    int stack[512]; int sp = 0;
     int cur = n > 1 ? 0 : ~0;
     for (;;) {
         bool descend = false;
@@ -369,7 +437,7 @@ Hit closest_bvh(const Scene& sc, V3 o, V3 d, uint64_t* n_nodes, uint64_t* n_test
             if (tl >= 0.0f && tr >= 0.0f) {
                 int nearc = cl, farc = cr;
                 if (tr < tl) { nearc = cr; farc = cl; }
-                stack[sp++] = farc; cur = nearc; descend = true;
+                stack[sp++] = farc; note_stack(sp + 1); cur = nearc; descend = true;
             } else if (tl >= 0.0f) { cur = cl; descend = true; }
             else if (tr >= 0.0f) { cur = cr; descend = true; }
         } else {
@@ -392,10 +460,14 @@ inline int dev_leaf_code(const Scene& sc, int pos) {
     uint32_t payload = q < ns ? q : q < ns + nq ? ((1u << 28) | (q - ns)) : ((2u << 28) | (uint32_t)pos);
     return ~(int)payload;
 }
-inline float pow2_ceil_scale(float ext) {
-    float s = 8.673617379884035e-19f;                                   /* 2^-60 */
-    if (ext > 0.0f) { int e; frexpf(ext * (1.0f / 254.0f), &e); e = e < -60 ? -60 : e; s = ldexpf(1.0f, e); }
-    return s;
+/* grid step of a wide node on one axis: the smallest power of two s with ext / s <= 253 (one step below the boxes is
+ * kept free, see build_wide), at least 2 ulp of the larger bound (so that origin = mn - s is a different float) and >= 2^-60 */
+inline float pow2_ceil_scale(float ext, float mn, float mx) {
+    int e = -60;
+    if (ext > 0.0f) { int e1; frexpf(ext * (1.0f / 253.0f), &e1); e = e1 > e ? e1 : e; }
+    const float m = fmaxf(fabsf(mn), fabsf(mx));
+    if (m > 0.0f) { int e2; frexpf(m, &e2); e2 -= 23; e = e2 > e ? e2 : e; }
+    return ldexpf(1.0f, e);
 }
 void build_wide(Scene& sc) {
     int n = sc.n_prims(), ni = n > 1 ? n - 1 : 0;
@@ -428,17 +500,21 @@ void build_wide(Scene& sc) {
         for (int k = 0; k < 3; ++k) {
             float mn = comp(lo[0], k), mx = comp(hi[0], k);
             for (int c = 1; c < ns; ++c) { mn = fminf(mn, comp(lo[c], k)); mx = fmaxf(mx, comp(hi[c], k)); }
-            float sc_k = pow2_ceil_scale(mx - mn);
+            float sc_k = pow2_ceil_scale(mx - mn, mn, mx);
+            /* The grid starts ONE STEP BELOW the lowest box: the floor of a box that starts at the node's own minimum then
+             * lands on step 0 with a margin of >= half a step instead of being clamped there with none (the fused decode
+             * in the walk rounds by up to 2^-9 step; a low face without margin lost corner-grazing hits). */
+            const float org = mn - sc_k;
             uint32_t ql = 0, qh = 0;
             for (int c = 0; c < 4; ++c) {
                 uint32_t a = 255u, b = 0u;
                 if (c < ns) {
-                    float fl = floorf((comp(lo[c], k) - mn) / sc_k - 0.015625f), fh = ceilf((comp(hi[c], k) - mn) / sc_k + 0.015625f);
+                    float fl = floorf((comp(lo[c], k) - org) / sc_k - 0.015625f), fh = ceilf((comp(hi[c], k) - org) / sc_k + 0.015625f);
                     a = (uint32_t)fminf(fmaxf(fl, 0.0f), 255.0f); b = (uint32_t)fminf(fmaxf(fh, 0.0f), 255.0f);
                 }
                 ql |= a << (8 * c); qh |= b << (8 * c);
             }
-            w.org[k] = mn; w.scale[k] = sc_k * 32768.0f; w.qlo[k] = ql; w.qhi[k] = qh;
+            w.org[k] = org; w.scale[k] = sc_k * 32768.0f; w.qlo[k] = ql; w.qhi[k] = qh;
         }
         for (int c = 0; c < 4; ++c) w.code[c] = c < ns ? code[c] : code[0];
         sc.wide_valid[i] = 1;
@@ -488,6 +564,7 @@ Hit closest_wide(const Scene& sc, V3 o, V3 d, uint64_t* n_nodes, uint64_t* n_tes
             uint32_t kmin = std::min(std::min(key[0], key[1]), std::min(key[2], key[3]));
             if (kmin != 0xffffffffu) {
                 for (int k = 0; k < 4; ++k) if (hit[k] && key[k] > kmin) stack.push_back(w.code[k]);
+                note_stack((int)stack.size() + 1);
                 cur = w.code[kmin & 3u];
                 continue;
             }
@@ -663,6 +740,12 @@ void po_scene_destroy(void* s) { delete (Scene*)s; }
 void po_set_estimator(void* s, int rr_start, float clamp) { Scene& sc = *(Scene*)s; sc.rr_start = rr_start; sc.clamp = clamp > 0.f ? clamp : INFINITY; }
 int po_num_prims(void* s) { return ((Scene*)s)->n_prims(); }
 
+void po_set_builder(void* s, int builder, int radius) { Scene& sc = *(Scene*)s; sc.builder = builder; sc.ploc_radius = radius; }
+int po_ploc_rounds(void* s) { return ((Scene*)s)->ploc_rounds; }
+int po_bvh_height(void* s) { return ((Scene*)s)->height; }
+int po_builder_used(void* s) { return ((Scene*)s)->builder_used; }
+void po_reset_max_stack(void) { g_max_stack.store(0); }
+int po_get_max_stack(void) { return g_max_stack.load(); }
 void po_build_lbvh(void* s) { build_lbvh(*(Scene*)s); build_wide(*(Scene*)s); }
 
 /* 4-wide nodes in the device layout: 16 words per internal node {ox,oy,oz,sx, code[4], qlo[3], qhi[3], sy,sz}; valid[i] = even depth */
@@ -774,6 +857,21 @@ void po_trace_pixel(void* s, const prt_camera* cam, int x, int y, int sample, in
     V3 d0 = camera_dir(c, (float)x + 0.5f, (float)y + 0.5f);
     V3 L = trace_path(sc, c.pos, d0, path_key(seed, (uint32_t)(y * c.W + x), (uint32_t)sample), max_depth, use_bvh != 0, &rays);
     out_rgb[0] = L.x; out_rgb[1] = L.y; out_rgb[2] = L.z;
+}
+
+/* MaterialHandle::{Emit,Scatter} known answers (material.h:139-161), one record: the hit normal already faces the ray,
+ * the RNG is the (seed, pixel, sample, bounce) stream; out = {ok, atten.rgb, out_dir.xyz (0 when the path ends), emit.rgb}.
+ * Same record layout as oracle/ref_harness.cpp:ref_scatter and prt_debug_scatter. */
+void po_scatter(const prt_material* m, const float* in_dir, const float* normal, int front, uint64_t seed, uint32_t pixel,
+                uint32_t sample, uint32_t bounce, float* out10) {
+    Scene sc; sc.mats.assign(m, m + 1);
+    Surface sf; sf.p = mk(0.f, 0.f, 0.f); sf.n = mk(normal[0], normal[1], normal[2]); sf.front = front != 0; sf.mat = 0;
+    Rng rng = rng_for_bounce(path_key(seed, pixel, sample), bounce);
+    V3 atten = mk(0.f, 0.f, 0.f), od = mk(0.f, 0.f, 0.f), emit;
+    bool ok = scatter(sc, 0, mk(in_dir[0], in_dir[1], in_dir[2]), sf, rng, atten, od, emit);
+    if (!ok) od = mk(0.f, 0.f, 0.f);
+    out10[0] = ok ? 1.f : 0.f; out10[1] = atten.x; out10[2] = atten.y; out10[3] = atten.z;
+    out10[4] = od.x; out10[5] = od.y; out10[6] = od.z; out10[7] = emit.x; out10[8] = emit.y; out10[9] = emit.z;
 }
 
 /* the RNG stream of (seed, pixel, sample, bounce): first n rand() values (31 bit) */

@@ -25,12 +25,26 @@ def nvcc_path():
     raise RuntimeError("nvcc not found")
 
 
+def source_hash():
+    """sha256 over the compiler flags and every source / header the library is built from."""
+    import hashlib
+    h = hashlib.sha256(" ".join(NVCC_FLAGS).encode())
+    for d in SOURCES + HEADERS:
+        with open(os.path.join(CSRC, d), "rb") as f:
+            h.update(d.encode()); h.update(f.read())
+    return h.hexdigest()
+
+
+STAMP = OUT + ".srchash"
+
+
 def needs_build():
-    if not os.path.exists(OUT):
+    """True when libprt_b200.so is missing or was built from other sources / flags than the ones in the tree (content hash,
+    not mtimes: the tree is copied to the GPU box)."""
+    if not os.path.exists(OUT) or not os.path.exists(STAMP):
         return True
-    t = os.path.getmtime(OUT)
-    deps = [os.path.join(CSRC, s) for s in SOURCES + HEADERS]
-    return any(os.path.getmtime(d) > t for d in deps)
+    with open(STAMP) as f:
+        return f.read().strip() != source_hash()
 
 
 def build(force=False, verbose=False):
@@ -42,6 +56,8 @@ def build(force=False, verbose=False):
         print(r.stdout, r.stderr)
     if r.returncode != 0:
         raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
+    with open(STAMP, "w") as f:
+        f.write(source_hash())
     return OUT
 
 

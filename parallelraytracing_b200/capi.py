@@ -36,7 +36,8 @@ class CStats(C.Structure):
                 ("nodes_visited", C.c_uint64), ("prims_tested", C.c_uint64),
                 ("render_ms", C.c_float), ("extend_ms", C.c_float), ("shade_ms", C.c_float), ("build_ms", C.c_float),
                 ("primary_ms", C.c_float), ("_padf", C.c_float),
-                ("kernel_launches", C.c_int32), ("n_prims", C.c_int32), ("n_nodes", C.c_int32), ("primary_launches", C.c_int32)]
+                ("kernel_launches", C.c_int32), ("n_prims", C.c_int32), ("n_nodes", C.c_int32), ("primary_launches", C.c_int32),
+                ("bvh_builder", C.c_int32), ("bvh_height", C.c_int32), ("ploc_rounds", C.c_int32), ("_padi", C.c_int32)]
 
 
 class PrtError(RuntimeError):
@@ -47,7 +48,7 @@ EXPORTS = [
     "prt_create", "prt_destroy", "prt_last_error", "prt_version", "prt_set_scene", "prt_build_bvh",
     "prt_set_camera", "prt_render", "prt_render_fresh", "prt_render_region", "prt_clear_accum", "prt_scale_accum", "prt_accum_device_ptr",
     "prt_set_accum_buffer", "prt_read_accum", "prt_accum_spp", "prt_set_accum_spp", "prt_resolve_display", "prt_trace_batch",
-    "prt_debug_lbvh", "prt_debug_wide", "prt_num_prims", "prt_enable_counters", "prt_get_stats", "prt_set_option",
+    "prt_debug_lbvh", "prt_debug_wide", "prt_debug_scatter", "prt_num_prims", "prt_enable_counters", "prt_get_stats", "prt_set_option",
 ]
 
 _lib = None
@@ -63,9 +64,13 @@ def load_library():
     if _lib is not None:
         return _lib
     p = lib_path()
-    if not os.path.exists(p):
-        raise PrtError(f"{p} not found: run `python -m parallelraytracing_b200.build` (needs nvcc). "
-                       "There is no CPU fallback.")
+    from . import build as _build
+    if _build.needs_build():                       # missing, or built from other sources than the tree holds: never run a stale .so
+        try:
+            _build.build()
+        except Exception as e:  # noqa: BLE001
+            raise PrtError(f"{p} is missing or older than its sources and could not be rebuilt ({e}); run "
+                           "`python -m parallelraytracing_b200.build` (needs nvcc). There is no CPU fallback.")
     lib = C.CDLL(p)
     vp, i32, u64, f32 = C.c_void_p, C.c_int, C.c_uint64, C.c_float
     lib.prt_create.argtypes = [C.POINTER(vp), i32]
@@ -89,6 +94,7 @@ def load_library():
     lib.prt_trace_batch.argtypes = [vp, vp, i32, vp, i32]
     lib.prt_debug_lbvh.argtypes = [vp, vp, vp, vp, vp, vp, vp]
     lib.prt_debug_wide.argtypes = [vp, vp]
+    lib.prt_debug_scatter.argtypes = [vp, vp, vp, vp, vp, vp, u64, i32, vp]
     lib.prt_num_prims.argtypes = [vp]
     lib.prt_enable_counters.argtypes = [vp, i32]
     lib.prt_get_stats.argtypes = [vp, C.POINTER(CStats)]
@@ -217,6 +223,16 @@ class Context:
         w = np.zeros((max(self.num_prims() - 1, 0), 16), np.uint32)
         self._check(self.lib.prt_debug_wide(self.h, _ptr(w)), "prt_debug_wide")
         return w
+
+    def debug_scatter(self, mats, in_dirs, normals, fronts, keys, seed=1):
+        """n MaterialHandle::Scatter/Emit records on the device -> (n, 10) float32 {ok, atten.rgb, out_dir.xyz, emit.rgb}."""
+        mats = np.ascontiguousarray(mats, material_dt)
+        i_, n_ = np.ascontiguousarray(in_dirs, np.float32), np.ascontiguousarray(normals, np.float32)
+        f_, k_ = np.ascontiguousarray(fronts, np.int32), np.ascontiguousarray(keys, np.uint32)
+        out = np.zeros((len(mats), 10), np.float32)
+        self._check(self.lib.prt_debug_scatter(self.h, _ptr(mats), _ptr(i_), _ptr(n_), _ptr(f_), _ptr(k_), seed, len(mats), _ptr(out)),
+                    "prt_debug_scatter")
+        return out
 
     def enable_counters(self, on=True):
         self._check(self.lib.prt_enable_counters(self.h, 1 if on else 0), "prt_enable_counters")

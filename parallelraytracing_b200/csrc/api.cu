@@ -121,7 +121,7 @@ void prt_destroy(prt_ctx* ctx) {
                       &c->q2_o[0], &c->q2_o[1], &c->q2_d[0], &c->q2_d[1], &c->q2_b[0], &c->q2_b[1], &c->hits2, &c->contrib2,
                       &c->qcount2, &c->qcount, &c->stats_dev, &c->ray_keys[0][0], &c->ray_keys[0][1], &c->ray_keys[1][0],
                       &c->ray_keys[1][1], &c->ray_vals[0][0], &c->ray_vals[0][1], &c->ray_vals[1][0], &c->ray_vals[1][1],
-                      &c->ray_hist[0], &c->ray_hist[1]};
+                      &c->ray_hist[0], &c->ray_hist[1], &c->ploc_code, &c->ploc_box, &c->ploc_status, &c->ploc_ctl};
     for (DevBuf* b : bufs) dev_free(*b);
     if (c->stats_host) cudaFreeHost(c->stats_host);
     for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
@@ -350,6 +350,14 @@ int prt_trace_batch(prt_ctx* ctx, const prt_ray* rays, int n, prt_hit* out, int 
     return wavefront_trace_batch(c, rays, n, out, use_bvh);
 }
 
+int prt_debug_scatter(prt_ctx* ctx, const prt_material* mats, const float* in_dirs, const float* normals, const int32_t* fronts,
+                      const uint32_t* keys, uint64_t seed, int n, float* out) {
+    if (!ctx || n < 0 || (n > 0 && (!mats || !in_dirs || !normals || !fronts || !keys || !out)))
+        return set_err(ctx ? &ctx->c : nullptr, PRT_ERR_INVALID, "prt_debug_scatter: NULL argument or negative count");
+    PRT_CUDA(&ctx->c, cudaSetDevice(ctx->c.device));
+    return wavefront_debug_scatter(&ctx->c, mats, in_dirs, normals, fronts, keys, seed, n, out);
+}
+
 int prt_num_prims(const prt_ctx* ctx) { return ctx ? ctx->c.n_prims : 0; }
 
 int prt_debug_lbvh(prt_ctx* ctx, uint32_t* morton, uint32_t* sorted_prim, int32_t* node_children,
@@ -403,6 +411,7 @@ int prt_get_stats(prt_ctx* ctx, prt_stats* out) {
     ctx->c.stats.build_ms = ctx->c.build_ms;
     ctx->c.stats.n_prims = ctx->c.n_prims;
     ctx->c.stats.n_nodes = ctx->c.n_prims > 1 ? ctx->c.n_prims - 1 : 0;
+    ctx->c.stats.bvh_builder = ctx->c.builder_used; ctx->c.stats.bvh_height = ctx->c.bvh_height; ctx->c.stats.ploc_rounds = ctx->c.ploc_rounds;
     *out = ctx->c.stats;
     return PRT_OK;
 }
@@ -426,6 +435,8 @@ int prt_set_option(prt_ctx* ctx, const char* key, int64_t value) {
     else if (!strcmp(key, "brute_max_prims")) c->brute_max_prims = (int)value;
     else if (!strcmp(key, "bvh_wide")) c->bvh_wide = value < 0 ? -1 : (value ? 1 : 0);   // takes effect at the next prt_build_bvh
     else if (!strcmp(key, "wide_min_prims")) c->wide_min_prims = (int)value;
+    else if (!strcmp(key, "bvh_builder")) c->bvh_builder = value ? 1 : 0;                        // takes effect at the next prt_build_bvh
+    else if (!strcmp(key, "ploc_radius")) { if (value < 1 || value > 8) return set_err(c, PRT_ERR_INVALID, "ploc_radius out of range (1..8)"); c->ploc_radius = (int)value; }
     else if (!strcmp(key, "overlap")) c->overlap = value ? 1 : 0;
     else if (!strcmp(key, "persistent")) c->persistent = value ? 1 : 0;
     else if (!strcmp(key, "pt_refill")) { if (value < 0 || value > 32) return set_err(c, PRT_ERR_INVALID, "pt_refill out of range"); c->pt_refill = (int)value; }

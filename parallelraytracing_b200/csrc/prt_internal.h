@@ -44,6 +44,10 @@ struct Ctx {
     int bvh_wide = -1;                          // 4-wide quantised nodes for the staged extend: 1 always, 0 never, -1 by scene size
     int wide_min_prims = 4096;                  // auto: below this the two-child tree is L1-resident and its cheaper node step wins
     bool wide_built = false;
+    DevBuf ploc_code, ploc_box, ploc_status, ploc_ctl;   // PLOC scratch: cluster codes (2 x n), boxes (the other half is node_min), tile status, control words
+    int bvh_builder = 1;                        // hierarchy over the sorted leaves: 1 PLOC (falls back to Karras when it fails), 0 Karras (plain LBVH)
+    int ploc_radius = 4;                        // neighbours searched on either side (1..8); 4 measured best (oracle counters: dragon, 809 spheres)
+    int builder_used = 0, bvh_height = 0, ploc_rounds = 0;
     DevBuf tri_v, tri_n;                        // leaf-slot order (3 float4 per slot)
     DevBuf morton;                              // per q (kept for prt_debug_lbvh)
     int sorted_slot = 0;                        // which of keys/vals holds the sorted result
@@ -117,6 +121,8 @@ int sort_ray_queue(Ctx* c, cudaStream_t st, int set, int64_t capacity, const uin
 int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_begin, int64_t pixel_begin, int64_t pixel_count, bool fresh = false);
 int wavefront_trace_batch(Ctx* c, const prt_ray* rays, int n, prt_hit* out, int use_bvh);
 int film_resolve_display(Ctx* c, float exposure, float gamma, uint8_t* host_rgba);
+int wavefront_debug_scatter(Ctx* c, const prt_material* mats, const float* in_dirs, const float* normals, const int32_t* fronts,
+                            const uint32_t* keys, uint64_t seed, int n, float* out);
 int film_scale_accum(Ctx* c, float s);
 
 }  // namespace prt

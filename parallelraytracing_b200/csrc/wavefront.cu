@@ -20,7 +20,13 @@ namespace prt {
 
 constexpr int WF_THREADS = 256;
 constexpr int STACK_SMEM = 24;    // entries per thread held in shared memory
-constexpr int STACK_LOCAL = 40;   // overflow entries (Karras tree height <= 62 for 2^28 prims)
+// Overflow entries in local memory (touched only by the rare deep walk; an untouched local array costs nothing).
+// Sized for the worst case, not the typical one: a Karras tree over 30-bit codes + 28-bit index tie-breaks is at most 58
+// levels deep; the two-child walk pushes <= 1 entry per level, the 4-wide walk pushes <= 3 per wide node and a wide node
+// may descend only ONE binary level (slots [L, RLL, RLR, RR]), so 3 * 58 + 1 sentinel = 175 entries can be needed
+// (advisor finding, round 1: 85 entries measured on an adversarial 1 M-triangle scene with the old 64). 256 in total.
+constexpr int STACK_TOTAL = 256;
+constexpr int STACK_LOCAL = STACK_TOTAL - STACK_SMEM;
 
 // queue entry: O = {o.xyz, bits(slot<<5 | bounce)}, D = {d.xyz, bits(path_key)}, B = {beta.rgb, 0}
 __device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
@@ -88,7 +94,7 @@ __device__ __forceinline__ Best traverse(const SceneView& sc, V3 o, V3 d, int* _
     if (sc.n_tris > 0) rs = make_shear(d);            // per-ray triangle-test constants: only if there are triangles
     else { rs.kx = 0; rs.ky = 1; rs.kz = 2; rs.sx = rs.sy = rs.sz = 0.f; }
     if (sc.n_spheres > 0) dn = normalize(d);          // Circle's local direction (primitive.cpp:30): only if there are spheres
-    int lstack[STACK_LOCAL + STACK_SMEM - SS];
+    int lstack[STACK_TOTAL - SS];
     int sp = 0;
     int cur = sc.root_code;
     for (;;) {
@@ -388,7 +394,7 @@ __device__ __forceinline__ Best traverse_wide(const SceneView& sc, V3 o, V3 d, i
     if (sc.n_tris > 0) rs = make_shear(d);
     const V3 dn = sc.n_spheres > 0 ? normalize(d) : d;
     const bool nx = inv.x < 0.0f, ny = inv.y < 0.0f, nz = inv.z < 0.0f;
-    int lstack[STACK_LOCAL + STACK_SMEM - SS];
+    int lstack[STACK_TOTAL - SS];
     int cur = sc.root_code, sp = 1;
     st[0] = PRT_DONE;
     while (cur != PRT_DONE) {
@@ -1159,6 +1165,53 @@ int wavefront_trace_batch(Ctx* c, const prt_ray* rays, int n, prt_hit* out, int 
     if (e != cudaSuccess) return set_err(c, PRT_ERR_CUDA, std::string("trace_batch: ") + cudaGetErrorString(e));
     c->stats.nodes_visited = h[PRT_MAX_DEPTH]; c->stats.prims_tested = h[PRT_MAX_DEPTH + 1];
     c->stats.rays_total = h[0];
+    return PRT_OK;
+}
+
+// ------------------------------------------------------------------ material known answers (parity entry)
+// MaterialHandle::{Emit,Scatter} (material.h:139-161) for n independent records through the SAME device function the
+// render path calls (prt_device.cuh:scatter): the reference's 600 known answers (tests/golden) are checked against it.
+__global__ void k_debug_scatter(const prt_material* __restrict__ mats, const float* __restrict__ in_dirs, const float* __restrict__ normals,
+                                const int* __restrict__ fronts, const uint32_t* __restrict__ keys, uint32_t seed_lo, uint32_t seed_hi,
+                                int n, float* __restrict__ out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const prt_material pm = mats[i];
+    MatRec m; m.a = make_float4(pm.r, pm.g, pm.b, pm.param); m.b = make_float4(__int_as_float(pm.type), 0.f, 0.f, 0.f);
+    Surface sf; sf.p = mk(0.f, 0.f, 0.f); sf.n = mk(normals[3 * i], normals[3 * i + 1], normals[3 * i + 2]); sf.front = fronts[i] != 0; sf.mat = 0;
+    Rng rng = rng_for_bounce(path_key(seed_lo, seed_hi, keys[3 * i], keys[3 * i + 1]), keys[3 * i + 2]);
+    V3 atten = mk(0.f, 0.f, 0.f), od = mk(0.f, 0.f, 0.f), emit;
+    const bool ok = scatter(m, mk(in_dirs[3 * i], in_dirs[3 * i + 1], in_dirs[3 * i + 2]), sf, rng, atten, od, emit);
+    if (!ok) od = mk(0.f, 0.f, 0.f);
+    float* o = out + 10 * (size_t)i;
+    o[0] = ok ? 1.f : 0.f; o[1] = atten.x; o[2] = atten.y; o[3] = atten.z; o[4] = od.x; o[5] = od.y; o[6] = od.z;
+    o[7] = emit.x; o[8] = emit.y; o[9] = emit.z;
+}
+
+int wavefront_debug_scatter(Ctx* c, const prt_material* mats, const float* in_dirs, const float* normals, const int32_t* fronts,
+                            const uint32_t* keys, uint64_t seed, int n, float* out) {
+    if (n <= 0) return PRT_OK;
+    DevBuf dm, di, dn, df, dk, dout;
+    int rc = 0;
+    const size_t N = (size_t)n;
+    if ((rc = dev_reserve(c, dm, N * sizeof(prt_material))) || (rc = dev_reserve(c, di, N * 12)) || (rc = dev_reserve(c, dn, N * 12)) ||
+        (rc = dev_reserve(c, df, N * 4)) || (rc = dev_reserve(c, dk, N * 12)) || (rc = dev_reserve(c, dout, N * 40))) {
+        for (DevBuf* b : {&dm, &di, &dn, &df, &dk, &dout}) dev_free(*b);
+        return rc;
+    }
+    cudaStream_t st = c->stream;
+    cudaMemcpyAsync(dm.p, mats, N * sizeof(prt_material), cudaMemcpyHostToDevice, st);
+    cudaMemcpyAsync(di.p, in_dirs, N * 12, cudaMemcpyHostToDevice, st);
+    cudaMemcpyAsync(dn.p, normals, N * 12, cudaMemcpyHostToDevice, st);
+    cudaMemcpyAsync(df.p, fronts, N * 4, cudaMemcpyHostToDevice, st);
+    cudaMemcpyAsync(dk.p, keys, N * 12, cudaMemcpyHostToDevice, st);
+    k_debug_scatter<<<(n + 127) / 128, 128, 0, st>>>((const prt_material*)dm.p, (const float*)di.p, (const float*)dn.p, (const int*)df.p,
+                                                     (const uint32_t*)dk.p, (uint32_t)seed, (uint32_t)(seed >> 32), n, (float*)dout.p);
+    cudaMemcpyAsync(out, dout.p, N * 40, cudaMemcpyDeviceToHost, st);
+    cudaError_t e = cudaStreamSynchronize(st);
+    if (e == cudaSuccess) e = cudaGetLastError();
+    for (DevBuf* b : {&dm, &di, &dn, &df, &dk, &dout}) dev_free(*b);
+    if (e != cudaSuccess) return set_err(c, PRT_ERR_CUDA, std::string("debug_scatter: ") + cudaGetErrorString(e));
     return PRT_OK;
 }
 

@@ -381,6 +381,34 @@ def load_ply(path):
     return verts, normals, faces
 
 
+def write_ply(path, verts, normals, faces, comment=None):
+    """Binary little-endian PLY (x y z [nx ny nz] + uchar/uint face lists): the layout load_ply and the reference's tinyply
+    loader (mesh.cpp:23-184) both read back exactly (float32 in, float32 out)."""
+    v = np.ascontiguousarray(verts, f32)
+    f = np.ascontiguousarray(faces, np.uint32).reshape(-1, 3)
+    props = "property float x\nproperty float y\nproperty float z\n"
+    body = v
+    if normals is not None:
+        props += "property float nx\nproperty float ny\nproperty float nz\n"
+        body = np.concatenate([v, np.ascontiguousarray(normals, f32)], axis=1)
+    rec = np.zeros(len(f), dtype=[("k", "u1"), ("i", "<u4", (3,))])
+    rec["k"] = 3; rec["i"] = f
+    with open(path, "wb") as fh:
+        fh.write(("ply\nformat binary_little_endian 1.0\n" + ("comment %s\n" % comment if comment else "") +
+                  "element vertex %d\n%selement face %d\nproperty list uchar uint vertex_indices\nend_header\n"
+                  % (len(v), props, len(f))).encode())
+        fh.write(body.astype("<f4").tobytes())
+        fh.write(rec.tobytes())
+
+
+ASSETS = os.path.join(os.path.dirname(os.path.abspath(__file__)), "assets")
+
+
+def bundled_mesh(name="dragon"):
+    """(verts, normals, faces) of a mesh shipped with the package (assets/<name>.ply)."""
+    return load_ply(os.path.join(ASSETS, name + ".ply"))
+
+
 def subdivide(verts, normals, faces, levels):
     """Midpoint subdivision (x4 triangles per level); normals are averaged, not re-normalised
     (the hit normal is normalised at shading time like primitive.cpp:39)."""

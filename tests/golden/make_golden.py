@@ -93,6 +93,9 @@ def main():
         if n is not None:
             out["mesh_%s_n" % m] = n
     v, n, f = out["mesh_dragon_v"], out["mesh_dragon_n"], out["mesh_dragon_f"]
+    # the mesh the bench workloads are built from ships with the package (bench.py must not depend on a test fixture)
+    S.write_ply(os.path.join(S.ASSETS, "dragon.ply"), v, n, f,
+                comment="arrays the reference's own Mesh loader returns for its assets/models/dragon.ply (10000 vertices, 20000 faces)")
     rs = ref.new_scene()
     lam = (MAT_LAMBERTIAN, 0.8, 0.3, 0.3, 0.0, (0, 0, 0))
     rs.add_quad(20, 20, (MAT_LAMBERTIAN, 0.5, 0.5, 0.5, 0.0, (0, 0, 0)), trans=(0, -1, 0))

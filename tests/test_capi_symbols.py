@@ -35,7 +35,7 @@ def test_struct_sizes_match_header():
     assert ctypes.sizeof(capi.CCamera) == 4 * 13 + 8
     assert capi.sphere_dt.itemsize == 32 and capi.quad_dt.itemsize == 80 and capi.material_dt.itemsize == 32
     assert capi.hit_dt.itemsize == 48 and capi.ray_dt.itemsize == 24
-    assert ctypes.sizeof(capi.CStats) == 8 + 8 * 32 + 8 * 3 + 4 * 6 + 4 * 4
+    assert ctypes.sizeof(capi.CStats) == 8 + 8 * 32 + 8 * 3 + 4 * 6 + 4 * 8
 
 
 def test_fails_loudly_without_device():

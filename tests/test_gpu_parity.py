@@ -42,25 +42,81 @@ SCENES = {
 
 
 # ---------------------------------------------------------------- LBVH: integer work bit-exact
+@pytest.mark.parametrize("builder", [1, 0])
 @pytest.mark.parametrize("name", sorted(SCENES))
-def test_lbvh_bit_exact(ctx, oracle, gold, name):
+def test_lbvh_bit_exact(ctx, oracle, gold, name, builder):
+    """builder 1 = PLOC over the sorted leaves (default; radius 4 and, on one scene, 1 and 8), 0 = Karras hierarchy + refit."""
     sd = SCENES[name](gold)
+    for radius in ((4, 1, 8) if builder == 1 and name == "dragon3" else (4,)):
+        ctx.set_option("bvh_builder", builder); ctx.set_option("ploc_radius", radius)
+        ctx.set_scene(sd); ctx.build_bvh()
+        ctx.set_option("bvh_builder", 1); ctx.set_option("ploc_radius", 4)
+        g = ctx.debug_lbvh()
+        osc = oracle.scene(sd); osc.set_builder(builder, radius)
+        o = osc.get_lbvh()
+        assert np.array_equal(g["scene_bounds"], o["scene_bounds"])
+        assert np.array_equal(g["morton"], o["morton"]), "Morton codes"
+        assert np.array_equal(g["sorted_prim"], o["sorted_prim"]), "sorted primitive order (stable radix sort)"
+        assert np.array_equal(g["node_children"], o["node_children"]), "topology (PLOC merges / Karras splits)"
+        assert np.array_equal(g["node_parent"], o["node_parent"])
+        assert np.array_equal(g["node_bounds"], o["node_bounds"]), "node boxes"
+        st, info = ctx.stats(), osc.build_info()
+        if sd.n_prims > 2:
+            assert (st.bvh_builder, st.bvh_height, st.ploc_rounds) == (info["builder"], info["height"], info["rounds"])
+
+
+def test_ploc_fallback_and_adversarial_scenes(ctx, oracle):
+    """GPU mirror of tests/test_bvh_quality.py: (1) nested boxes - PLOC gives up at its round limit and the Karras hierarchy is
+    built instead, same bits as the oracle's fallback; (2) the deep lopsided scene, both builders - hit records through the
+    two-child and the 4-wide walk equal the oracle's and brute force (the wide walk needs more stack entries than the 64 the
+    kernels had in round 1); (3) corner-grazing rays on the 4-wide quantised nodes equal brute force."""
+    sd = util.nested_scene(300)
     ctx.set_scene(sd); ctx.build_bvh()
-    g = ctx.debug_lbvh()
-    o = oracle.scene(sd).get_lbvh()
-    assert np.array_equal(g["scene_bounds"], o["scene_bounds"])
-    assert np.array_equal(g["morton"], o["morton"]), "Morton codes"
-    assert np.array_equal(g["sorted_prim"], o["sorted_prim"]), "sorted primitive order (stable radix sort)"
-    assert np.array_equal(g["node_children"], o["node_children"]), "Karras topology"
-    assert np.array_equal(g["node_parent"], o["node_parent"])
-    assert np.array_equal(g["node_bounds"], o["node_bounds"]), "refit bounds"
+    st = ctx.stats()
+    assert st.bvh_builder == 0 and st.ploc_rounds == 192
+    g, o = ctx.debug_lbvh(), oracle.scene(sd).get_lbvh()
+    for k in g:
+        assert np.array_equal(g[k], o[k]), k
+    ctx.set_option("bvh_wide", 1)
+    try:
+        sd = util.deep_scene(); rays = util.rays_from_point((0.45, 0.45, 0.45), 20000)
+        for builder in (0, 1):
+            ctx.set_option("bvh_builder", builder)
+            ctx.set_scene(sd); ctx.build_bvh()
+            osc = oracle.scene(sd); osc.set_builder(builder, 4)
+            brute = ctx.trace_batch(rays, use_bvh=0)
+            ctx.enable_counters(True)
+            for mode in (1, 2):
+                cnt = np.zeros(2, np.uint64)
+                want = osc.trace_batch(rays, use_bvh=mode, counters=cnt)
+                got = ctx.trace_batch(rays, use_bvh=mode); stt = ctx.stats()
+                assert np.array_equal(got, want) and np.array_equal(got, brute), (builder, mode)
+                assert (stt.nodes_visited, stt.prims_tested) == (int(cnt[0]), int(cnt[1]))
+            ctx.enable_counters(False)
+            # the same rays as a render: one camera in the middle of all boxes, in-thread tail walk included
+            cam = S.Camera(pos=(0.45, 0.45, 0.45), front=(0.0, 0.0, -1.0), width=64, height=48)
+            ctx.set_camera(cam); ctx.clear_accum(); ctx.render(2, 6, seed=3)
+            want_img, _ = osc.render(cam, 2, 6, seed=3)
+            assert np.array_equal(ctx.read_accum(), want_img)
+        ctx.set_option("bvh_builder", 1)
+        sd, tv = util.grazing_scene(); rays = util.grazing_rays(tv, 400000)
+        ctx.set_scene(sd); ctx.build_bvh()
+        brute = ctx.trace_batch(rays, use_bvh=0)
+        assert np.array_equal(ctx.trace_batch(rays, use_bvh=2), brute) and np.array_equal(ctx.trace_batch(rays, use_bvh=1), brute)
+        assert np.array_equal(brute, oracle.scene(sd).trace_batch(rays, use_bvh=0))
+    finally:
+        ctx.set_option("bvh_wide", -1); ctx.set_option("bvh_builder", 1)
 
 
-def test_lbvh_large_properties(ctx):
+@pytest.mark.parametrize("builder", [1, 0])
+def test_lbvh_large_properties(ctx, builder):
     """1M-triangle soup (oracle too slow for a full compare in the GPU suite): size-independent
-    properties — sorted keys, permutation, every node's box contains its children, one root."""
+    properties — sorted keys, permutation, every node's box contains its children, one root. Both hierarchies."""
     sd = S.random_triangle_soup(1_000_000)
+    ctx.set_option("bvh_builder", builder)
     ctx.set_scene(sd); ctx.build_bvh()
+    ctx.set_option("bvh_builder", 1)
+    assert ctx.stats().bvh_builder == builder
     g = ctx.debug_lbvh()
     n = sd.n_prims
     keys = g["morton"][g["sorted_prim"]]
@@ -202,8 +258,43 @@ def test_image_vs_reference_vectors(ctx, gold, name):
     ctx.set_scene(sd); ctx.build_bvh(); ctx.set_camera(S.Camera(width=W, height=H)); ctx.clear_accum()
     ctx.render(spp, depth, seed=seed)
     m = util.image_metrics(gold["img_%s" % name] / spp, ctx.read_accum() / spp)
-    assert m["flips"] <= (0.02 if name == "cornell" else 0.002) * m["n"], m
+    assert m["flips"] <= (0.01 if name == "cornell" else 0.002) * m["n"], m      # Cornell: 0.6 % measured (coplanar walls)
     assert m["rmse_nonflip"] <= 1e-3 and m["max_rel_nonflip"] <= 1e-2, m
+
+
+def test_scatter_known_answers(ctx, oracle, gold):
+    """The reference's 600 MaterialHandle::Scatter / Emit known answers (tests/golden/make_golden.py section 5) through the
+    device function the render path shades with (prt_debug_scatter -> prt_device.cuh:scatter): equal to the reference's
+    compiled material code bit for bit, every branch (metal rejection, total internal reflection, ior < 1, emissive)."""
+    mats, ins, nrm, fr, want = (gold["scatter_" + k] for k in ("mats", "in", "n", "front", "out"))
+    from parallelraytracing_b200.capi import material_dt
+    m = np.zeros(len(mats), material_dt)
+    m["type"], m["r"], m["g"], m["b"], m["param"] = mats[:, 0].astype(np.int32), mats[:, 1], mats[:, 2], mats[:, 3], mats[:, 4]
+    k = np.arange(len(mats), dtype=np.uint32)
+    keys = np.stack([k, k // 7, k % 5], 1).astype(np.uint32)
+    got = ctx.debug_scatter(m, ins, nrm, fr, keys, seed=1)
+    assert np.array_equal(got[:, 0], want[:, 0]), "scattered / absorbed decision"
+    assert np.array_equal(got, want), np.abs(got - want).max()
+    orc = np.stack([oracle.scatter(tuple(m[i].tolist()), ins[i], nrm[i], int(fr[i]), 1, int(k[i]), int(k[i]) // 7, int(k[i]) % 5) for i in range(len(m))])
+    assert np.array_equal(got, orc)
+
+
+def test_c1_full_size(ctx, oracle):
+    """BASELINE.json configs[0] IN FULL: reference CORNELL, 512 x 512, 16 spp, depth 8, seed 1. GPU == oracle
+    bit for bit, and - where oracle/_ref exists - within the SURVEY tolerances of the reference's own tier-2 render."""
+    sd = S.cornell(); cam = S.Camera(width=512, height=512)
+    ctx.set_scene(sd); ctx.build_bvh(); ctx.set_camera(cam); ctx.clear_accum()
+    ctx.render(16, 8, seed=1)
+    got, st = ctx.read_accum(), ctx.stats()
+    want, rays = oracle.scene(sd).render(cam, 16, 8, seed=1)
+    assert np.array_equal(got, want) and st.rays_total == rays
+    import oracle_lib
+    ref = oracle_lib.load_ref()
+    if ref is not None:
+        rimg, ref_rays = ref.preset(int(S.ScenePreset.CORNELL)).render(cam, 16, 8, seed=1)
+        m = util.image_metrics(rimg / 16, got / 16)
+        assert m["flips"] <= 0.01 * m["n"] and m["rmse_nonflip"] <= 1e-3 and m["max_rel_nonflip"] <= 1e-2, m
+        assert abs(st.rays_total - ref_rays) <= 0.01 * ref_rays
 
 
 def test_sample_ranges_compose(ctx, gold):
@@ -582,11 +673,62 @@ def test_full_size_1080p_properties(ctx):
     assert a.max() <= 6 * 15.0 + 1e-3                                                                  # no pixel brighter than the light
 
 
-def test_full_size_10m_triangles_wide_equals_two_child():
-    """configs[4] geometry (10 M random triangles, depth 16): brute force is out of reach, so the two traversal
-    structures check each other - the image through the 4-wide quantised nodes equals the image through the two-child
-    LBVH bit for bit, with about half the node visits."""
-    sd = S.random_triangle_soup(10_000_000)
+@pytest.fixture(scope="module")
+def big_scenes():
+    """BASELINE.json's mesh configs at FULL size, built once: C3 = dragon x 3 x 16 = 960 K triangles + ground quad, C5 = 10 M
+    random triangles; each with its bench camera."""
+    import bench
+    out = {}
+    for key, wl in (("dragon960k", "dragon960k_1080p_64spp_d8"), ("soup10m", "soup10m_1080p_16spp_d16")):
+        sd, cam, w = bench.make_workload(wl)
+        out[key] = (sd, cam, w)
+        bench._scene_cache.clear()                       # keep both alive here, not in the cache
+    return out
+
+
+@pytest.mark.parametrize("name", ["dragon960k", "soup10m"])
+def test_full_size_mesh_vs_oracle(oracle, big_scenes, name):
+    """The big scenes against the ORACLE's own BVH (not the GPU against itself): GPU BVH build == oracle build (integer
+    outputs and node boxes, bit for bit, 960 K / 10 M primitives), closest hits of a 65 536-ray fixed batch + 16 384
+    incoherent rays through the two-child AND the 4-wide walk == the oracle's records, traversal counters equal, and a
+    64-row band of the bench frame (depth 8 / 16) == the oracle's image with the same number of rays."""
+    sd, cam, w = big_scenes[name]
+    osc = oracle.scene(sd)
+    o = osc.get_lbvh()
+    lo, hi = util.scene_bounds(sd)
+    rays = np.concatenate([util.fixed_ray_batch(sd, 65536, seed=1, clamp_extent=60.0),
+                           util.incoherent_rays(16384, float(min(50.0, np.abs(np.concatenate([lo, hi])).max())))])
+    with Context(0) as c:
+        c.set_scene(sd); c.build_bvh()
+        g = c.debug_lbvh()
+        for k in ("scene_bounds", "morton", "sorted_prim", "node_children", "node_parent", "node_bounds"):
+            assert np.array_equal(g[k], o[k]), k
+        st, info = c.stats(), osc.build_info()
+        assert (st.bvh_builder, st.bvh_height, st.ploc_rounds) == (info["builder"], info["height"], info["rounds"])
+        c.enable_counters(True)
+        for mode in (1, 2):
+            cnt = np.zeros(2, np.uint64)
+            want = osc.trace_batch(rays, use_bvh=mode, n_threads=16, counters=cnt)
+            got = c.trace_batch(rays, use_bvh=mode); stt = c.stats()
+            assert np.array_equal(got["prim_id"], want["prim_id"]) and np.array_equal(got["t"], want["t"]), mode
+            assert np.array_equal(got, want), mode
+            assert (stt.nodes_visited, stt.prims_tested) == (int(cnt[0]), int(cnt[1])), mode
+            assert (got["prim_id"] >= 0).mean() > 0.05
+        c.enable_counters(False)
+        band = S.Camera(pos=tuple(cam.pos), front=tuple(cam.front), width=cam.width, height=cam.height)
+        y0 = cam.height // 2 - 32
+        c.set_camera(band); c.clear_accum()
+        c.render_region(1, w["depth"], seed=3, pixel_begin=y0 * cam.width, pixel_count=64 * cam.width)
+        got = c.read_accum()[y0:y0 + 64]
+        want, orays = osc.render(band, 1, w["depth"], seed=3, n_threads=16, y_begin=y0, y_end=y0 + 64)
+        assert np.array_equal(got, want[y0:y0 + 64]) and c.stats().rays_total == orays
+        assert got.max() > 0
+
+
+def test_full_size_10m_triangles_wide_equals_two_child(big_scenes):
+    """configs[4] geometry (10 M random triangles, depth 16) as an IMAGE: the render through the 4-wide quantised nodes
+    equals the render through the two-child tree bit for bit, with about half the node visits."""
+    sd = big_scenes["soup10m"][0]
     cam = S.Camera(pos=(0.0, 0.0, 150.0), front=(0.0, 0.0, -1.0), width=640, height=360)
     out = []
     with Context(0) as c:

@@ -92,3 +92,98 @@ def scene_to_npz(d, prefix, sd):
     if sd.n_tris:
         d[prefix + "_tri_verts"], d[prefix + "_tri_normals"], d[prefix + "_tri_material"] = sd.tri_verts, sd.tri_normals, sd.tri_material
     d[prefix + "_tri_prim_base"] = np.int64(sd.tri_prim_base)
+
+
+# ---------------------------------------------------------------- adversarial scenes for the traversal structures
+def _tri_with_box(c, r):
+    """A triangle whose AABB is exactly [c - r, c + r] (its centre, which the Morton code is taken from, is c)."""
+    c = np.asarray(c, np.float64); r = np.asarray(r, np.float64)
+    return [c + (-r[0], -r[1], -r[2]), c + (r[0], -r[1], r[2]), c + (0.0, r[1], 0.0)]
+
+
+def _tri_scene(name, tris):
+    b = S.SceneBuilder(name)
+    b.add_triangles(np.array(tris, np.float32), None, b.lambertian((0.5, 0.5, 0.5)))
+    return b.build()
+
+
+def grazing_scene():
+    """Three long triangles whose x-min vertex is also the y-max corner of their box, node extent ~100 in x (grid step 0.5
+    of the 4-wide quantised nodes): rays that clip that corner found the low face of the quantised box without margin
+    (advisor finding, round 1). Returns (scene, triangle vertices)."""
+    tv = np.array([[[0.0, 1.0, 0.0], [100.0, 0.0, 0.3], [60.0, 0.2, -0.4]],
+                   [[3.0, 5.0, 1.0], [90.0, 4.0, 1.5], [50.0, 4.5, 0.7]],
+                   [[-7.0, -3.0, 2.0], [80.0, -4.0, 2.5], [40.0, -3.5, 1.7]]], np.float32)
+    return _tri_scene("graze", tv), tv
+
+
+def grazing_rays(tv, n, seed=1):
+    """Steep rays that hit within ~3e-4 of the corner vertex of a triangle of grazing_scene()."""
+    rng = np.random.default_rng(seed)
+    k = rng.integers(0, len(tv), n)
+    vert = tv[k, 0].astype(np.float64)
+    w = rng.random((n, 2)) * 3e-6
+    tgt = vert + w[:, :1] * (tv[k, 1] - vert) + w[:, 1:] * (tv[k, 2] - vert)
+    d = np.stack([-(0.01 + 0.05 * rng.random(n)), -(0.2 + rng.random(n)) * 4, 0.3 * rng.standard_normal(n)], 1)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    o = tgt - d * (5.0 + 10 * rng.random((n, 1)))
+    r = np.zeros(n, ray_dt)
+    r["ox"], r["oy"], r["oz"] = o.astype(np.float32).T
+    r["dx"], r["dy"], r["dz"] = d.astype(np.float32).T
+    return r
+
+
+def deep_scene(n_center=4096):
+    """Deep, lopsided hierarchy: n_center co-centred triangles in ONE Morton cell (identical codes: Karras splits them by
+    index) + for every code bit 3..29 three triangles in neighbouring cells whose boxes all contain the point (0.45,
+    0.45, 0.45) and grow with the bit. From that point every box is entered at t = 0, so the walks push every sibling."""
+    tris = [_tri_with_box((0.5, 0.5, 0.5), (0.3, 0.3, 0.3)) for _ in range(n_center)]
+    for b in range(3, 30):
+        for low in (0, 1, 2):
+            cell = [0, 0, 0]
+            cell[2 - b % 3] = 1 << (b // 3)
+            if low == 1: cell[2] |= 1
+            if low == 2: cell[1] |= 1
+            tris.append(_tri_with_box([k + 0.5 for k in cell], [k + 0.5 - 0.45 + 0.05 * (1 + low) for k in cell]))
+    tris.append(_tri_with_box((1024.0, 1024.0, 1024.0), (0.2, 0.2, 0.2)))
+    return _tri_scene("deep", tris)
+
+
+def nested_scene(n=300):
+    """n concentric triangles with geometrically growing boxes (identical Morton code): every cluster's best partner is a
+    smaller one, so PLOC merges ONE pair per round and gives up after its round limit - the Karras fallback must take over."""
+    return _tri_scene("nested", [_tri_with_box((1.0, 2.0, 3.0), (0.1 * 1.05 ** i,) * 3) for i in range(n)])
+
+
+def rays_from_point(p, n, seed=1):
+    rng = np.random.default_rng(seed)
+    g = rng.standard_normal((n, 3)); g /= np.linalg.norm(g, axis=1, keepdims=True)
+    r = np.zeros(n, ray_dt)
+    r["ox"], r["oy"], r["oz"] = p
+    r["dx"], r["dy"], r["dz"] = g.astype(np.float32).T
+    return r
+
+
+def incoherent_rays(n, extent, seed=3):
+    """Origins uniform in [-extent, extent]^3, directions uniform on the sphere (what a diffuse bounce inside a soup looks like)."""
+    rng = np.random.default_rng(seed)
+    o = (rng.random((n, 3)) * 2 - 1) * extent
+    g = rng.standard_normal((n, 3)); g /= np.linalg.norm(g, axis=1, keepdims=True)
+    r = np.zeros(n, ray_dt)
+    r["ox"], r["oy"], r["oz"] = o.astype(np.float32).T
+    r["dx"], r["dy"], r["dz"] = g.astype(np.float32).T
+    return r
+
+
+def bounce_rays(hits, seed=5):
+    """Diffuse-like secondary rays from the hit records of a traced batch (origin = hit point, direction = n + unit vector)."""
+    m = hits["prim_id"] >= 0
+    rng = np.random.default_rng(seed)
+    nrm = np.stack([hits["nx"], hits["ny"], hits["nz"]], 1)[m].astype(np.float64)
+    p = np.stack([hits["px"], hits["py"], hits["pz"]], 1)[m]
+    g = rng.standard_normal(p.shape); g /= np.linalg.norm(g, axis=1, keepdims=True)
+    d = nrm + 0.999 * g; d /= np.linalg.norm(d, axis=1, keepdims=True)
+    r = np.zeros(len(p), ray_dt)
+    r["ox"], r["oy"], r["oz"] = p.astype(np.float32).T
+    r["dx"], r["dy"], r["dz"] = d.astype(np.float32).T
+    return r

@@ -270,8 +270,10 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def measure(args, name, steps, warmup, with_clocks=False):
-    """Device-timed and end-to-end measurement of ONE workload on this rank's GPU (+ the NCCL reduce with N > 1)."""
+def measure(args, name, steps, warmup, with_clocks=False, devices=None):
+    """Device-timed and end-to-end measurement of ONE workload on this rank's GPU (+ the NCCL reduce with N > 1).
+    devices = [0..N-1]: ONE process drives N GPUs through a multi-device context (prt_create_multi: the split and the NCCL
+    reduce happen inside libprt_b200.so); no torch.distributed on that path."""
     import torch
     import torch.distributed as dist
     from parallelraytracing_b200.capi import Context
@@ -279,12 +281,15 @@ def measure(args, name, steps, warmup, with_clocks=False):
 
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    n_dev = 1
+    if devices:
+        rank, world, n_dev = 0, 1, len(devices)
     sd, cam, w = make_workload(name)
     W, H, depth = w["W"], w["H"], w["depth"]
     tiles = args.partition == "tiles"
     if tiles and not w.get("strong"):
         raise SystemExit("bench.py: --partition tiles needs a fixed-total-work workload (dragon960k_4k_*)")
-    spp = spp_per_gpu(w, world, tiles)
+    spp = spp_per_gpu(w, world, tiles) if (w.get("strong") or not devices) else w["spp"] * n_dev   # weak scaling in one process: N x the samples in one call
     pix_begin, pix_count = pixel_range(rank, world, W * H, W) if tiles else (0, W * H)
 
     def render(seed):
@@ -292,7 +297,9 @@ def measure(args, name, steps, warmup, with_clocks=False):
             ctx.render_region(spp, depth, seed=seed, sample_begin=0, pixel_begin=pix_begin, pixel_count=pix_count)
         else:
             ctx.render(spp, depth, seed=seed, sample_begin=rank * spp)
-    ctx = Context(local)
+    ctx = Context(list(devices) if devices else local)
+    if devices and tiles:
+        ctx.set_option("multi_partition", 1)
     for kv in args.opt:
         k, v = kv.split("=")
         ctx.set_option(k, int(v))
@@ -327,7 +334,7 @@ def measure(args, name, steps, warmup, with_clocks=False):
         clocks.start()
     # ---- timed region: device time of prt_render (CUDA events on the context's own stream, read back
     # through prt_get_stats) + the reduce (torch events on torch's stream), max over ranks
-    rays = 0; launches = 0; render_ms = 0.0; ext_ms = 0.0; shd_ms = 0.0; red_ms = 0.0; prim_ms = 0.0
+    rays = 0; launches = 0; render_ms = 0.0; ext_ms = 0.0; shd_ms = 0.0; red_ms = 0.0; prim_ms = 0.0; red_in_ms = 0.0
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sync_all()
     t_wall = time.perf_counter()
@@ -339,7 +346,7 @@ def measure(args, name, steps, warmup, with_clocks=False):
         render(100 + i)                                                   # synchronous, like ProgressiveRender
         st = ctx.stats()
         rays += st.rays_total; launches += st.kernel_launches
-        render_ms += st.render_ms; ext_ms += st.extend_ms; shd_ms += st.shade_ms; prim_ms += st.primary_ms
+        render_ms += st.render_ms; ext_ms += st.extend_ms; shd_ms += st.shade_ms; prim_ms += st.primary_ms; red_in_ms += st.reduce_ms
         if world > 1:
             e0.record(); dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM); e1.record(); torch.cuda.synchronize()
             red_ms += e0.elapsed_time(e1)
@@ -347,7 +354,7 @@ def measure(args, name, steps, warmup, with_clocks=False):
     wall_ms = 1e3 * (time.perf_counter() - t_wall)
     clk = clocks.stop() if (rank == 0 and with_clocks) else None
     dev_ms = render_ms + red_ms
-    if world > 1:
+    if world > 1 and not devices:
         t = torch.tensor([dev_ms, float(rays), float(launches)], dtype=torch.float64, device="cuda")
         tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
@@ -355,12 +362,16 @@ def measure(args, name, steps, warmup, with_clocks=False):
     else:
         dev_ms_max, rays_all, launches_all = dev_ms, float(rays), launches
 
-    # ---- e2e: the call a user makes (Renderer interface, HOST scene in, HOST image out), every step
+    # ---- e2e: the call a user makes (Renderer interface, HOST scene in, HOST image out), every step; the step's inputs
+    # (the host scene arrays) sit in page-locked host memory, as the contract asks
     from parallelraytracing_b200 import B200Renderer, Film
-    film, r = Film(W, H), B200Renderer(device=local, max_depth=depth, samples_per_call=spp, seed=1)
+    sd.pin()
+    film, r = Film(W, H), B200Renderer(device=list(devices) if devices else local, max_depth=depth, samples_per_call=spp, seed=1)
     r.ctx = ctx                                                          # same device context (allocations stay warm)
     ctx.set_accum_buffer(None)
     e2e_rays = 0; init_s = 0.0
+    from parallelraytracing_b200.capi import pinned_copy
+    host_img = pinned_copy(np.zeros((H, W, 3), np.float32))             # D2H target in page-locked memory
     sync_all()
     t0 = time.perf_counter()
     for i in range(steps):
@@ -373,17 +384,21 @@ def measure(args, name, steps, warmup, with_clocks=False):
             ctx.render_region(spp, depth, seed=200 + i, sample_begin=0, pixel_begin=pix_begin, pixel_count=pix_count)
         else:
             r.ProgressiveRender()
-        img = film.ReadAccum()                # D2H of the float image
+        img = film.ReadAccum(host_img)        # D2H of the float image
         e2e_rays += r.Stats().rays_total
     e2e_s = time.perf_counter() - t0
-    if world > 1:
+    if world > 1 and not devices:
         t = torch.tensor([e2e_s, float(e2e_rays)], dtype=torch.float64, device="cuda")
         tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
         e2e_s, e2e_rays = float(tmax[0]), float(tsum[1])
-    R = dict(rank=rank, world=world, ctx=ctx, sd=sd, cam=cam, w=w, name=name, steps=steps, warmup=warmup, rays_all=rays_all,
+    paths_step = pix_count * spp
+    if devices:                                  # one process, N devices: report as an N-GPU line; the reduce ran inside prt_render
+        world, red_ms = n_dev, red_in_ms         # (render_ms already contains it: root ev0 -> end of the reduce)
+        spp = spp // n_dev if not tiles else spp
+    R = dict(rank=rank, world=world, inproc=bool(devices), ctx=ctx, sd=sd, cam=cam, w=w, name=name, steps=steps, warmup=warmup, rays_all=rays_all,
              dev_ms_max=dev_ms_max, launches_all=launches_all, ext_ms=ext_ms, shd_ms=shd_ms, prim_ms=prim_ms, render_ms=render_ms,
-             red_ms=red_ms, rays=rays, spp=spp, tiles=tiles, paths_step=pix_count * spp, clk=clk, e2e_s=e2e_s, e2e_rays=e2e_rays,
+             red_ms=red_ms, rays=rays, spp=spp, tiles=tiles, paths_step=paths_step, clk=clk, e2e_s=e2e_s, e2e_rays=e2e_rays,
              init_ms=1e3 * init_s / steps, build_ms=build_ms, builder=builder, height=height, wall_ms=wall_ms, img_mean=float(img.mean()))
     out = result_json(args, R) if rank == 0 else None
     ctx.close()
@@ -403,8 +418,9 @@ def result_json(args, R):
     ctx.enable_counters(False)
     n_node = st.nodes_visited / max(1, st.rays_total)
     n_leaf = st.prims_tested / max(1, st.rays_total)
-    rays_step = R["rays"] / steps                      # this rank
-    paths_step = R["paths_step"]                       # this rank
+    per = R["world"] if R.get("inproc") else 1         # one process driving N devices: per-device averages for the roofline
+    rays_step = R["rays"] / steps / per                # this rank (device)
+    paths_step = R["paths_step"] / per                 # this rank (device)
     cont = rays_step - paths_step                      # segments that continued into another bounce
     fused = R["shd_ms"] == 0.0
     # ALGORITHMIC bytes: B_ray = B_queue + B_shade + 64*n_node + 48*n_leaf.
@@ -468,10 +484,12 @@ def result_json(args, R):
            "rays_per_path": rays_step / paths_step,
            "e2e": {"value": R["e2e_rays"] / R["e2e_s"] / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": scene_bytes(sd) + 64,
                    "d2h_bytes_per_step": W * H * 12, "init_ms_per_step": R["init_ms"],
-                   "what": "B200Renderer.Init(host scene)+ProgressiveRender+Film.ReadAccum per step, wall clock"},
+                   "what": "B200Renderer.Init(host scene in page-locked memory: H2D + GPU BVH build)+ProgressiveRender+Film.ReadAccum per step, wall clock"},
            "gpu_launches": R["launches_all"], "bvh_build_ms": R["build_ms"],
            "bvh_builder": "ploc" if R["builder"] == 1 else "karras", "bvh_height": R["height"],
            "bvh_build_mprims_per_s": (sd.n_prims / (R["build_ms"] * 1e-3) / 1e6) if R["build_ms"] > 0 else None,
+           "multi_gpu": ("one process, prt_create_multi: split + NCCL reduce inside libprt_b200.so" if R.get("inproc") else
+                         "one process per GPU (torchrun), torch.distributed NCCL reduce") if R["world"] > 1 else None,
            "reduce_ms_per_step": R["red_ms"] / steps, "wall_ms_per_step": R["wall_ms"] / steps, "clocks": R["clk"], "roofline": roof}
     if name == "cornell_1080p_256spp_d8":
         out["parity_note"] = ("reference CORNELL is the one preset with a documented deviation: its three wall quads are coplanar "
@@ -500,6 +518,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extra", action="store_true", help="default run without the extra mesh workloads")
     ap.add_argument("--extra-steps", type=int, default=5, help="timed steps of each extra workload (<= --steps)")
+    ap.add_argument("--inproc-gpus", type=int, default=0, help="ONE process drives this many GPUs through prt_create_multi (no torchrun)")
     ap.add_argument("--partition", default="samples", choices=["samples", "tiles"],
                     help="multi-GPU split: sample ranges (default) or bands of rows (strong-scaling workloads only)")
     ap.add_argument("--opt", action="append", default=[], help="prt_set_option key=value (e.g. fused=0, wave_paths=8388608)")
@@ -520,6 +539,13 @@ def main():
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    gloo = None
+    if world > 1:
+        gloo = dist.new_group(backend="gloo")                            # CPU-side barrier for the in-process leg below
+    if args.inproc_gpus > 1:                                             # manual: one process drives N GPUs, nothing else
+        out = measure(args, args.workload, args.steps, args.warmup, with_clocks=True, devices=list(range(args.inproc_gpus)))
+        emit(json.dumps(out), out_fd)
+        return 0
     out = measure(args, args.workload, args.steps, args.warmup, with_clocks=True)
     if default_run and not args.no_extra and args.partition == "samples":
         extra = {}
@@ -531,6 +557,16 @@ def main():
             o = measure(args, name, k, 3)
             if rank == 0:
                 extra[name] = o
+        if world > 1:
+            # the same strong-scaling workload with ONE process driving all N GPUs through the C ABI (prt_create_multi): what a
+            # maintainer who adds B200Renderer to main.cpp gets. The other ranks have released their contexts and wait on the CPU.
+            name = EXTRA_WORKLOADS_MULTI[0]
+            if rank == 0:
+                try:
+                    extra[name]["inproc"] = measure(args, name, 3, 3, devices=list(range(world)))
+                except Exception as e:  # noqa: BLE001
+                    extra[name]["inproc"] = {"error": str(e)[:300]}
+            dist.barrier(group=gloo)
         if rank == 0:
             out["workloads"] = extra
     if rank == 0:

@@ -16,6 +16,7 @@
 #ifndef PRT_H
 #define PRT_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -41,8 +42,10 @@ extern "C" {
 #define PRT_SHAPE_QUAD      1
 #define PRT_SHAPE_TRIANGLE  2
 
-/* Sample partition of prt_render (multi-GPU sharding). */
-#define PRT_PARTITION_SAMPLES 0  /* this rank renders samples [sample_begin, sample_begin+spp) */
+/* How a multi-device context (prt_create_multi) splits one prt_render call over its devices; option
+ * "multi_partition". Either way every device renders into its own buffer and ONE sum-reduce lands the frame on device 0. */
+#define PRT_PARTITION_SAMPLES 0  /* device d renders its share of the sample range [sample_begin, sample_begin+spp) of every pixel */
+#define PRT_PARTITION_TILES   1  /* device d renders all samples of its band of rows                                             */
 
 typedef struct prt_ctx prt_ctx;
 
@@ -120,7 +123,7 @@ typedef struct prt_stats {
     float    shade_ms;
     float    build_ms;                    /* device time of the last prt_build_bvh             */
     float    primary_ms;                  /* part of extend_ms spent in the bounce-0 kernels   */
-    float    _padf;
+    float    reduce_ms;                   /* multi-device context: device time of the sum-reduce (incl. waiting for the slowest device) */
     int32_t  kernel_launches;             /* kernels launched by the last prt_render           */
     int32_t  n_prims;
     int32_t  n_nodes;
@@ -128,13 +131,22 @@ typedef struct prt_stats {
     int32_t  bvh_builder;                 /* hierarchy of the last prt_build_bvh: 1 PLOC, 0 Karras (LBVH; also the fallback) */
     int32_t  bvh_height;                  /* height of the PLOC tree (0 for Karras: bounded by the key width instead)     */
     int32_t  ploc_rounds;                 /* clustering rounds the PLOC build took                                         */
-    int32_t  _padi;
+    int32_t  n_devices;                   /* devices of this context (prt_create: 1)                                        */
 } prt_stats;
 
 /* ---- life cycle --------------------------------------------------------------------
  * Replaces a backend's ctor/dtor + the allocation half of Init
  * (cuda_wavefront/renderer.cu:351-370, 436-487). device = CUDA ordinal. */
 int  prt_create(prt_ctx** out, int device);
+/* ONE context over n_devices GPUs of this process (SURVEY 8b export list / 8e: single process, one stream per device,
+ * ncclCommInitAll). device_ids[0] is the root: its accumulation buffer is the one every other entry point reads. The scene,
+ * the BVH (built on every device, identical bits) and the camera are replicated; prt_render* split the call over the devices
+ * (option "multi_partition": PRT_PARTITION_SAMPLES default, PRT_PARTITION_TILES), enqueue every device's waves and, behind
+ * them on the same streams with no host synchronisation in between, ONE float sum-reduce to the root: ncclReduce over
+ * NVLink (libnccl.so.2 is loaded at run time; option "multi_reduce" = 1), or a peer-to-peer kernel on the root that reads
+ * the other devices' buffers through NVLink peer mappings (= 2; also the fallback when NCCL cannot be loaded; 0 = auto).
+ * The image equals the one-device image up to fp32 summation order (same samples: the RNG is keyed by pixel and sample). */
+int  prt_create_multi(prt_ctx** out, const int* device_ids, int n_devices);
 void prt_destroy(prt_ctx* ctx);
 const char* prt_last_error(const prt_ctx* ctx);   /* ctx may be NULL: last global error */
 const char* prt_version(void);
@@ -155,6 +167,11 @@ int  prt_set_scene(prt_ctx* ctx,
                    int n_tris, int tri_prim_base,
                    const prt_material* materials, int n_materials,
                    const float sky_rgb[3]);
+
+/* Page-locked host memory (cudaHostAlloc) for the big input arrays: prt_set_scene copies from such memory with plain
+ * asynchronous DMA (~50 GB/s over PCIe 5); pageable arrays go through the context's own staging ring instead. Optional. */
+void* prt_host_alloc(size_t bytes);
+void  prt_host_free(void* p);
 
 /* GPU LBVH build over the current scene: primitive AABBs -> scene bounds -> 30-bit Morton
  * codes -> stable LSD radix sort -> hierarchy over the sorted leaves: PLOC (locally-ordered agglomerative clustering,
@@ -256,7 +273,7 @@ int  prt_get_stats(prt_ctx* ctx, prt_stats* out);
 
 /* Tuning knobs (all optional): "wave_paths" (paths in flight per wave), "ctas_per_sm", "fused", "fused_max_prims",
  * "brute_max_prims", "persistent", "pt_refill", "pt_refill_wide", "bvh_wide", "wide_min_prims", "bvh_builder", "ploc_radius", "overlap",
- * "stage_timing", "rr_start", "firefly_clamp_milli", and for small waves (one sample per call, the reference's
+ * "stage_timing", "rr_start", "firefly_clamp_milli", "multi_partition", "multi_reduce" (multi-device contexts), and for small waves (one sample per call, the reference's
  * ProgressiveRender granularity) "tail_bounce" (0 = one launch per bounce always), "tail_adaptive", "tail_rays", "tail_rays_staged",
  * "tail_max_paths": bounces from the tail start on run inside one kernel; "sort_rays", "sort_key_bits",
  * "sort_min_rays": re-sort the ray queue of every bounce by origin cell and direction octant (staged pipeline, off). None of them changes the image except

@@ -36,6 +36,11 @@ int main(int argc, char** argv)
 
     auto backend = std::make_shared<B200Renderer>();
     backend->SetMaxDepth(depth); backend->SetSamplesPerCall(spp); backend->SetSeed(seed);
+    if (const char* devs = std::getenv("PRT_SHIM_DEVICES")) {              // e.g. "0,1": one Renderer over several GPUs (SetDevices)
+        std::vector<int> ids;
+        for (const char* p = devs; *p;) { ids.push_back(std::atoi(p)); while (*p && *p != ',') ++p; if (*p == ',') ++p; }
+        backend->SetDevices(ids);
+    }
     std::vector<std::unique_ptr<Mesh>> meshes;
     for (int a = 9; a + 8 < argc; a += 9) {
         meshes.emplace_back(new Mesh(argv[a]));

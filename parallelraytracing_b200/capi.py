@@ -35,9 +35,9 @@ class CStats(C.Structure):
     _fields_ = [("rays_total", C.c_uint64), ("rays_per_bounce", C.c_uint64 * PRT_MAX_DEPTH), ("paths", C.c_uint64),
                 ("nodes_visited", C.c_uint64), ("prims_tested", C.c_uint64),
                 ("render_ms", C.c_float), ("extend_ms", C.c_float), ("shade_ms", C.c_float), ("build_ms", C.c_float),
-                ("primary_ms", C.c_float), ("_padf", C.c_float),
+                ("primary_ms", C.c_float), ("reduce_ms", C.c_float),
                 ("kernel_launches", C.c_int32), ("n_prims", C.c_int32), ("n_nodes", C.c_int32), ("primary_launches", C.c_int32),
-                ("bvh_builder", C.c_int32), ("bvh_height", C.c_int32), ("ploc_rounds", C.c_int32), ("_padi", C.c_int32)]
+                ("bvh_builder", C.c_int32), ("bvh_height", C.c_int32), ("ploc_rounds", C.c_int32), ("n_devices", C.c_int32)]
 
 
 class PrtError(RuntimeError):
@@ -45,10 +45,10 @@ class PrtError(RuntimeError):
 
 
 EXPORTS = [
-    "prt_create", "prt_destroy", "prt_last_error", "prt_version", "prt_set_scene", "prt_build_bvh",
+    "prt_create", "prt_create_multi", "prt_destroy", "prt_last_error", "prt_version", "prt_set_scene", "prt_build_bvh",
     "prt_set_camera", "prt_render", "prt_render_fresh", "prt_render_region", "prt_clear_accum", "prt_scale_accum", "prt_accum_device_ptr",
     "prt_set_accum_buffer", "prt_read_accum", "prt_accum_spp", "prt_set_accum_spp", "prt_resolve_display", "prt_trace_batch",
-    "prt_debug_lbvh", "prt_debug_wide", "prt_debug_scatter", "prt_num_prims", "prt_enable_counters", "prt_get_stats", "prt_set_option",
+    "prt_debug_lbvh", "prt_debug_wide", "prt_debug_scatter", "prt_host_alloc", "prt_host_free", "prt_num_prims", "prt_enable_counters", "prt_get_stats", "prt_set_option",
 ]
 
 _lib = None
@@ -74,6 +74,7 @@ def load_library():
     lib = C.CDLL(p)
     vp, i32, u64, f32 = C.c_void_p, C.c_int, C.c_uint64, C.c_float
     lib.prt_create.argtypes = [C.POINTER(vp), i32]
+    lib.prt_create_multi.argtypes = [C.POINTER(vp), C.POINTER(C.c_int), i32]
     lib.prt_destroy.argtypes = [vp]; lib.prt_destroy.restype = None
     lib.prt_last_error.argtypes = [vp]; lib.prt_last_error.restype = C.c_char_p
     lib.prt_version.restype = C.c_char_p
@@ -95,12 +96,40 @@ def load_library():
     lib.prt_debug_lbvh.argtypes = [vp, vp, vp, vp, vp, vp, vp]
     lib.prt_debug_wide.argtypes = [vp, vp]
     lib.prt_debug_scatter.argtypes = [vp, vp, vp, vp, vp, vp, u64, i32, vp]
+    lib.prt_host_alloc.argtypes = [C.c_size_t]; lib.prt_host_alloc.restype = vp
+    lib.prt_host_free.argtypes = [vp]; lib.prt_host_free.restype = None
     lib.prt_num_prims.argtypes = [vp]
     lib.prt_enable_counters.argtypes = [vp, i32]
     lib.prt_get_stats.argtypes = [vp, C.POINTER(CStats)]
     lib.prt_set_option.argtypes = [vp, C.c_char_p, C.c_int64]
     _lib = lib
     return lib
+
+
+class _PinnedBlock:
+    """Owner of one prt_host_alloc block (freed when the last numpy view of it goes away)."""
+
+    def __init__(self, lib, nbytes):
+        self.lib, self.p = lib, lib.prt_host_alloc(nbytes)
+        if not self.p:
+            raise PrtError("prt_host_alloc(%d) failed" % nbytes)
+
+    def __del__(self):
+        try:
+            self.lib.prt_host_free(self.p)
+        except Exception:
+            pass
+
+
+def pinned_copy(a):
+    """A copy of numpy array `a` in page-locked host memory (prt_host_alloc): prt_set_scene then uploads it by plain DMA."""
+    a = np.ascontiguousarray(a)
+    blk = _PinnedBlock(load_library(), a.nbytes)
+    buf = (C.c_char * max(1, a.nbytes)).from_address(blk.p)
+    buf._owner = blk                            # numpy keeps `buf` alive through the buffer protocol, `buf` keeps the block
+    out = np.frombuffer(buf, dtype=a.dtype, count=a.size).reshape(a.shape)
+    out[...] = a
+    return out
 
 
 def _ptr(a):
@@ -111,9 +140,15 @@ class Context:
     """Thin RAII wrapper of prt_ctx; every method maps 1:1 to a C-ABI call."""
 
     def __init__(self, device=0):
+        """device: a CUDA ordinal, or a list of ordinals for ONE context over several GPUs of this process
+        (prt_create_multi: the first one is the root that holds the frame)."""
         self.lib = load_library()
         h = C.c_void_p()
-        rc = self.lib.prt_create(C.byref(h), device)
+        if isinstance(device, (list, tuple)):
+            ids = (C.c_int * len(device))(*[int(d) for d in device])
+            rc = self.lib.prt_create_multi(C.byref(h), ids, len(device))
+        else:
+            rc = self.lib.prt_create(C.byref(h), device)
         if rc != 0:
             raise PrtError(f"prt_create failed ({rc}): {self.lib.prt_last_error(None).decode()}")
         self.h = h

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <string>
+#include <utility>
 #include <vector>
 #include "../../include/prt.h"
 #include "prt_device.cuh"
@@ -23,6 +24,9 @@ struct Ctx {
     int n_spheres = 0, n_quads = 0, n_tris = 0, n_prims = 0, n_mats = 0;
     int tri_prim_base = 0;
     DevBuf spheres, quads, quad_mat, mats;
+    DevBuf raw_v, raw_n, raw_m;                 // the caller's packed triangle arrays as uploaded (kept: no allocation per prt_set_scene)
+    void* stage[2] = {nullptr, nullptr};        // ring of two page-locked 32 MB buffers for pageable sources (upload_large)
+    cudaEvent_t stage_ev[2] = {nullptr, nullptr};
     DevBuf tri_in_v, tri_in_n, tri_in_mat;     // tri_in_v, input order: 6 float4 / tri {v0, v1 (w = material), v2, n0, n1, n2}; the other two unused
     DevBuf prim_id_of_q;                        // int per q: reference list index
     float sky[3] = {0.4f, 0.3f, 0.6f};
@@ -97,6 +101,8 @@ struct Ctx {
     float firefly_clamp = 0.f;                  // reference's estimator stays checkable: Russian roulette / radiance clamp
     int stage_timing = 1;                       // CUDA-event pairs around the hot kernels
     std::vector<cudaEvent_t> ev_pool;
+    std::vector<std::pair<size_t, int>> pend_spans;   // a render that is enqueued but not finished yet (wavefront_finish)
+    int pend_launches = 0; uint64_t pend_paths = 0; bool pend_active = false;
     prt_stats stats{};
 
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -118,7 +124,9 @@ int lbvh_build(Ctx* c);
 int sort_ray_queue(Ctx* c, cudaStream_t st, int set, int64_t capacity, const uint32_t* n_dev, const float4* so, const float4* sd,
                    const float4* sb, float4* to, float4* td, float4* tb);
 // wavefront.cu
-int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_begin, int64_t pixel_begin, int64_t pixel_count, bool fresh = false);
+int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_begin, int64_t pixel_begin, int64_t pixel_count, bool fresh = false,
+                     bool defer_finish = false);
+int wavefront_finish(Ctx* c);
 int wavefront_trace_batch(Ctx* c, const prt_ray* rays, int n, prt_hit* out, int use_bvh);
 int film_resolve_display(Ctx* c, float exposure, float gamma, uint8_t* host_rgba);
 int wavefront_debug_scatter(Ctx* c, const prt_material* mats, const float* in_dirs, const float* normals, const int32_t* fronts,
@@ -127,4 +135,15 @@ int film_scale_accum(Ctx* c, float s);
 
 }  // namespace prt
 
-struct prt_ctx { prt::Ctx c; };
+// A context handle. `c` is the context of the one device (prt_create) or of the ROOT device (prt_create_multi);
+// a multi-device context owns one more handle per additional device.
+struct prt_ctx {
+    prt::Ctx c;
+    std::vector<prt_ctx*> peers;            // multi-device: contexts of device_ids[1..]
+    std::vector<void*> comms;               // ncclComm_t per device (root first); empty = NCCL not in use
+    int reduce_mode = 0;                    // 0 auto (NCCL when libnccl.so.2 loads, else peer-to-peer kernel), 1 NCCL, 2 peer-to-peer
+    int partition = PRT_PARTITION_SAMPLES;
+    bool p2p_enabled = false;
+    cudaEvent_t evr0 = nullptr, evr1 = nullptr;
+    std::vector<cudaEvent_t> ev_peer;       // peer-to-peer reduce: "this device's waves are done", one per peer
+};

@@ -924,7 +924,7 @@ static int ensure_wave_buffers(Ctx* c, int64_t paths, bool second_set = false) {
     return PRT_OK;
 }
 
-int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_begin, int64_t pixel_begin, int64_t pixel_count, bool fresh) {
+int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_begin, int64_t pixel_begin, int64_t pixel_count, bool fresh, bool defer_finish) {
     const int64_t P = pixel_count;                                   // pixels [pixel_begin, pixel_begin + P) of the frame
     int64_t cap = c->wave_paths_opt > 0 ? c->wave_paths_opt : (int64_t)64 << 20;   // 64 Mi paths: 8.6 GB of queues per set
     cap = std::min<int64_t>(cap, (int64_t)1 << 26);                  // slot must fit 27 bits
@@ -964,7 +964,8 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
 
     // per-stage device timing: pooled events, one pair per kernel of the two hot stages
     size_t ev_used = 0;
-    std::vector<std::pair<size_t, int>> spans;                       // (first event index, stage)
+    std::vector<std::pair<size_t, int>>& spans = c->pend_spans;      // (first event index, stage)
+    spans.clear();
     auto stamp = [&](cudaStream_t s) -> size_t {
         if (ev_used == c->ev_pool.size()) { cudaEvent_t e; cudaEventCreate(&e); c->ev_pool.push_back(e); }
         cudaEventRecord(c->ev_pool[ev_used], s);
@@ -1084,9 +1085,22 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
     // counters come back through pinned memory behind the last kernel: one host wake-up per call, not two
     if (!c->stats_host) PRT_CUDA(c, cudaHostAlloc((void**)&c->stats_host, (PRT_MAX_DEPTH + 4) * 8, cudaHostAllocDefault));
     PRT_CUDA(c, cudaMemcpyAsync(c->stats_host, dstats, (PRT_MAX_DEPTH + 4) * 8, cudaMemcpyDeviceToHost, st));
+    c->pend_launches = launches; c->pend_paths = paths; c->pend_active = true;
+    c->accum_spp = (fresh ? 0 : c->accum_spp) + spp;
+    if (defer_finish) return PRT_OK;         // multi-device: the caller enqueues the reduce behind this, then finishes every device
+    return wavefront_finish(c);
+}
+
+// Second half of a render: wait for the stream, read the counters back. Split from the enqueue half so that a multi-device
+// context can enqueue every device's waves and the reduce behind them before the host waits for anything.
+int wavefront_finish(Ctx* c) {
+    if (!c->pend_active) return PRT_OK;
+    c->pend_active = false;
+    cudaStream_t st = c->stream;
     PRT_CUDA(c, cudaStreamSynchronize(st));
     PRT_CUDA(c, cudaGetLastError());
-    c->accum_spp = (fresh ? 0 : c->accum_spp) + spp;
+    const int launches = c->pend_launches; const uint64_t paths = c->pend_paths;
+    std::vector<std::pair<size_t, int>>& spans = c->pend_spans;
 
     const unsigned long long* h = c->stats_host;
     prt_stats& s = c->stats;

@@ -11,7 +11,8 @@ B200Renderer::~B200Renderer() { prt_destroy(m_Ctx); }
 void B200Renderer::Init(Film& film, const Scene& scene, const Camera& camera)
 {
     m_Film = &film; m_Scene = &scene; m_Ok = false;
-    if (!m_Ctx && prt_create(&m_Ctx, m_Device) != PRT_OK) {
+    if (!m_Ctx && (m_Devices.size() > 1 ? prt_create_multi(&m_Ctx, m_Devices.data(), (int)m_Devices.size())
+                                        : prt_create(&m_Ctx, m_Device)) != PRT_OK) {
         std::fprintf(stderr, "[B200Renderer] %s\n", prt_last_error(nullptr));
         return;
     }

@@ -23,7 +23,11 @@ public:
     void SetMaxDepth(int depth) { m_Depth = depth; }
     void SetSamplesPerCall(int spp) { m_SamplesPerCall = spp < 1 ? 1 : spp; }
     void SetSeed(uint64_t seed) { m_Seed = seed; }
-    void SetDevice(int device) { m_Device = device; }
+    void SetDevice(int device) { m_Device = device; m_Devices.clear(); }
+    // Several GPUs of this process behind the one Renderer: prt_create_multi - the scene and BVH are replicated,
+    // every ProgressiveRender splits its samples over the devices and one NCCL sum-reduce lands the sample buffer on
+    // devices[0], which must be the device the caller's Film lives on (Film::AddSampleBufferGPU reads it there). Before Init.
+    void SetDevices(const std::vector<int>& devices) { m_Devices = devices; if (!devices.empty()) m_Device = devices[0]; }
     // Mesh -> scene glue: the reference Scene cannot hold a Mesh; meshes registered here BEFORE Init are appended
     // to the flattened scene as world-space triangles (after the Scene's own primitives). The Mesh must outlive Init.
     void AddMesh(const Mesh& mesh, const prt_material& material, float tx = 0.f, float ty = 0.f, float tz = 0.f)
@@ -38,6 +42,7 @@ private:
     prt_ctx* m_Ctx = nullptr;
     bool m_Ok = false;
     int m_Device = 0;
+    std::vector<int> m_Devices;    // empty: one device (m_Device)
     int m_Depth = 20;              // m_Depth of the reference backends
     int m_SamplesPerCall = 1;
     int m_NextSample = 0;

@@ -37,9 +37,10 @@ class Film:
     def Weight(self):
         return 0 if self._ctx is None else self._ctx.accum_spp()
 
-    def ReadAccum(self):
-        """Raw float sum (H, W, 3): the reference keeps this private (film.h:50); tests need it."""
-        return self._ctx.read_accum()
+    def ReadAccum(self, out=None):
+        """Raw float sum (H, W, 3): the reference keeps this private (film.h:50); tests need it. `out`: reuse this array
+        (e.g. one in page-locked memory, capi.pinned_copy) instead of allocating."""
+        return self._ctx.read_accum(out)
 
     def UpdateDisplay(self, exposure=1.0, gamma=2.2):   # film.cu:101-132 / 134-194
         return self._ctx.resolve_display(exposure, gamma)
@@ -47,6 +48,7 @@ class Film:
 
 class B200Renderer:
     def __init__(self, device=0, max_depth=20, samples_per_call=1, seed=1):
+        # device: a CUDA ordinal, or a list of ordinals = ONE renderer over several GPUs of this process (prt_create_multi)
         self.m_Device, self.m_Depth = device, max_depth       # depth 20 = cpu/renderer.h:34
         self.m_SamplesPerCall, self.m_Seed = max(1, samples_per_call), seed
         self.m_NextSample = 0

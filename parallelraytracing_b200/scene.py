@@ -59,6 +59,16 @@ class SceneData:
     def n_prims(self):
         return len(self.spheres) + len(self.quads) + self.n_tris
 
+    def pin(self):
+        """Move the triangle arrays into page-locked host memory (prt_host_alloc), in place: B200Renderer.Init / prt_set_scene
+        then upload them by plain asynchronous DMA instead of through the staging ring. Needs the CUDA library. Returns self."""
+        if self.n_tris and not getattr(self, "_pinned", False):
+            from .capi import pinned_copy
+            self.tri_verts, self.tri_normals = pinned_copy(self.tri_verts), pinned_copy(self.tri_normals)
+            self.tri_material = pinned_copy(self.tri_material)
+            self._pinned = True
+        return self
+
 
 # ---------------------------------------------------------------- float32 glm helpers
 def _v3(x, y, z):

@@ -265,6 +265,9 @@ int  prt_debug_lbvh(prt_ctx* ctx, uint32_t* morton, uint32_t* sorted_prim,
  * the two-child nodes; every internal node has a record (greedy collapse by surface area, 2..4 slots). Returns
  * PRT_ERR_INVALID if not built. */
 int  prt_debug_wide(prt_ctx* ctx, uint32_t* words);
+/* Round trace of the last PLOC build: counts[r] = clusters at the start of round r, ns[r] = device %globaltimer (low 32 bits,
+ * nanoseconds) at that moment; returns the number of entries written (rounds + 1, <= max_rounds) or < 0. Profiling aid. */
+int  prt_debug_ploc_trace(prt_ctx* ctx, int32_t* counts, uint32_t* ns, int max_rounds);
 int  prt_num_prims(const prt_ctx* ctx);
 
 /* Enable per-ray traversal counters (nodes fetched / primitives tested); costs speed. */

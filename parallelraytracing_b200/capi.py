@@ -48,7 +48,7 @@ EXPORTS = [
     "prt_create", "prt_create_multi", "prt_destroy", "prt_last_error", "prt_version", "prt_set_scene", "prt_build_bvh",
     "prt_set_camera", "prt_render", "prt_render_fresh", "prt_render_region", "prt_clear_accum", "prt_scale_accum", "prt_accum_device_ptr",
     "prt_set_accum_buffer", "prt_read_accum", "prt_accum_spp", "prt_set_accum_spp", "prt_resolve_display", "prt_trace_batch",
-    "prt_debug_lbvh", "prt_debug_wide", "prt_debug_scatter", "prt_host_alloc", "prt_host_free", "prt_num_prims", "prt_enable_counters", "prt_get_stats", "prt_set_option",
+    "prt_debug_lbvh", "prt_debug_wide", "prt_debug_scatter", "prt_debug_ploc_trace", "prt_host_alloc", "prt_host_free", "prt_num_prims", "prt_enable_counters", "prt_get_stats", "prt_set_option",
 ]
 
 _lib = None
@@ -96,6 +96,7 @@ def load_library():
     lib.prt_debug_lbvh.argtypes = [vp, vp, vp, vp, vp, vp, vp]
     lib.prt_debug_wide.argtypes = [vp, vp]
     lib.prt_debug_scatter.argtypes = [vp, vp, vp, vp, vp, vp, u64, i32, vp]
+    lib.prt_debug_ploc_trace.argtypes = [vp, vp, vp, i32]
     lib.prt_host_alloc.argtypes = [C.c_size_t]; lib.prt_host_alloc.restype = vp
     lib.prt_host_free.argtypes = [vp]; lib.prt_host_free.restype = None
     lib.prt_num_prims.argtypes = [vp]
@@ -268,6 +269,14 @@ class Context:
         self._check(self.lib.prt_debug_scatter(self.h, _ptr(mats), _ptr(i_), _ptr(n_), _ptr(f_), _ptr(k_), seed, len(mats), _ptr(out)),
                     "prt_debug_scatter")
         return out
+
+    def ploc_trace(self):
+        """(clusters at the start of each PLOC round, microseconds each round took) of the last build."""
+        cnt, ns = np.zeros(200, np.int32), np.zeros(200, np.uint32)
+        n = self.lib.prt_debug_ploc_trace(self.h, _ptr(cnt), _ptr(ns), 200)
+        if n <= 0:
+            return cnt[:0], np.zeros(0)
+        return cnt[:n], np.diff(ns[:n]).astype(np.uint32).astype(np.float64) * 1e-3
 
     def enable_counters(self, on=True):
         self._check(self.lib.prt_enable_counters(self.h, 1 if on else 0), "prt_enable_counters")

@@ -38,32 +38,6 @@ int dev_reserve(Ctx* c, DevBuf& b, size_t bytes) {
 
 void dev_free(DevBuf& b) { if (b.p) cudaFree(b.p); b.p = nullptr; b.bytes = 0; }
 
-// Triangle ingest on the device: the caller's packed arrays (9 floats per triangle, optional 9 floats of vertex
-// normals, optional material index) are copied as they are and expanded here into the 16-byte planes the build
-// reads. (Doing this on the host cost 2 s per Init for 10 M triangles: a 960 MB staging vector and a scalar loop.)
-// Flat normal when none is given: cross(v1 - v0, v2 - v0), unnormalised (the shading normalises it).
-__global__ void k_expand_tris(int n, const float* __restrict__ v, const float* __restrict__ nrm, const int* __restrict__ mat,
-                              int mat_default, float4* __restrict__ out_v, float4* __restrict__ out_n) {
-    int t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= n) return;
-    float a[9];
-#pragma unroll
-    for (int k = 0; k < 9; ++k) a[k] = v[9 * (size_t)t + k];
-#pragma unroll
-    for (int k = 0; k < 3; ++k)                                        // 96-byte record {v0, v1 | material, v2, n0, n1, n2}
-        out_v[6 * (size_t)t + k] = make_float4(a[3 * k], a[3 * k + 1], a[3 * k + 2], k == 1 ? __int_as_float(mat ? mat[t] : mat_default) : 0.f);
-    if (nrm) {
-#pragma unroll
-        for (int k = 0; k < 3; ++k)
-            out_n[6 * (size_t)t + k] = make_float4(nrm[9 * (size_t)t + 3 * k], nrm[9 * (size_t)t + 3 * k + 1], nrm[9 * (size_t)t + 3 * k + 2], 0.f);
-    } else {
-        float e1x = a[3] - a[0], e1y = a[4] - a[1], e1z = a[5] - a[2], e2x = a[6] - a[0], e2y = a[7] - a[1], e2z = a[8] - a[2];
-        float nx = e1y * e2z - e2y * e1z, ny = e1z * e2x - e2z * e1x, nz = e1x * e2y - e2x * e1y;
-#pragma unroll
-        for (int k = 0; k < 3; ++k) out_n[6 * (size_t)t + k] = make_float4(nx, ny, nz, 0.f);
-    }
-}
-
 static int upload(Ctx* c, DevBuf& b, const void* host, size_t bytes) {
     int rc = dev_reserve(c, b, bytes);
     if (rc) return rc;
@@ -402,7 +376,7 @@ void prt_destroy(prt_ctx* ctx) {
                       &c->q2_o[0], &c->q2_o[1], &c->q2_d[0], &c->q2_d[1], &c->q2_b[0], &c->q2_b[1], &c->hits2, &c->contrib2,
                       &c->qcount2, &c->qcount, &c->stats_dev, &c->ray_keys[0][0], &c->ray_keys[0][1], &c->ray_keys[1][0],
                       &c->ray_keys[1][1], &c->ray_vals[0][0], &c->ray_vals[0][1], &c->ray_vals[1][0], &c->ray_vals[1][1],
-                      &c->ray_hist[0], &c->ray_hist[1], &c->ploc_code, &c->ploc_box, &c->ploc_status, &c->ploc_ctl, &c->raw_v, &c->raw_n, &c->raw_m};
+                      &c->ray_hist[0], &c->ray_hist[1], &c->ploc_code, &c->ploc_box, &c->ploc_status, &c->ploc_ctl, &c->raw_v, &c->raw_n, &c->raw_m, &c->tri_bounds};
     for (DevBuf* b : bufs) dev_free(*b);
     if (c->stats_host) cudaFreeHost(c->stats_host);
     for (int k = 0; k < 2; ++k) { if (c->stage[k]) cudaFreeHost(c->stage[k]); if (c->stage_ev[k]) cudaEventDestroy(c->stage_ev[k]); }
@@ -468,11 +442,10 @@ int prt_set_scene(prt_ctx* ctx, const prt_sphere* spheres, int n_spheres, const 
         rc = upload_large(c, c->raw_v, tri_verts, nt * 36);
         if (!rc && tri_normals) rc = upload_large(c, c->raw_n, tri_normals, nt * 36);
         if (!rc && tri_material) rc = upload_large(c, c->raw_m, tri_material, nt * 4);
-        if (!rc) rc = dev_reserve(c, c->tri_in_v, nt * 96);
         if (rc) return rc;
-        k_expand_tris<<<(unsigned)((nt + 255) / 256), 256, 0, c->stream>>>(n_tris, (const float*)c->raw_v.p, tri_normals ? (const float*)c->raw_n.p : nullptr,
-            tri_material ? (const int*)c->raw_m.p : nullptr, tri_material_default, (float4*)c->tri_in_v.p, (float4*)c->tri_in_v.p + 3);
     }
+    // records the build gathers + every triangle's box and their share of the bounds (k_ingest_tris)
+    if ((rc = lbvh_ingest_tris(c, n_spheres, n_quads, n_tris, tri_normals != nullptr, tri_material != nullptr, tri_material_default))) return rc;
     PRT_CUDA(c, cudaStreamSynchronize(c->stream));                 // the caller's arrays (and the records above) are free again
     PRT_CUDA(c, cudaGetLastError());
     c->n_spheres = n_spheres; c->n_quads = n_quads; c->n_tris = n_tris; c->n_mats = n_materials;
@@ -691,6 +664,14 @@ int prt_debug_lbvh(prt_ctx* ctx, uint32_t* morton, uint32_t* sorted_prim, int32_
         }
     }
     return PRT_OK;
+}
+
+int prt_debug_ploc_trace(prt_ctx* ctx, int32_t* counts, uint32_t* ns, int max_rounds) {
+    if (!ctx || !counts || !ns) return set_err(ctx ? &ctx->c : nullptr, PRT_ERR_INVALID, "prt_debug_ploc_trace: NULL argument");
+    const Ctx* c = &ctx->c;
+    const int n = std::min(max_rounds, c->ploc_rounds + 1);
+    for (int r = 0; r < n; ++r) { counts[r] = c->ploc_trace[16 + 2 * r]; ns[r] = (uint32_t)c->ploc_trace[16 + 2 * r + 1]; }
+    return n;
 }
 
 int prt_debug_wide(prt_ctx* ctx, uint32_t* words) {

@@ -23,13 +23,45 @@ __global__ void k_init_bounds(int* b) {
     if (threadIdx.x < 12) b[threadIdx.x] = (threadIdx.x % 6) < 3 ? 0x7fffffff : (int)0x80000000;   // min = +max ordered, max = lowest
 }
 
+// Block reduction of the scene bounds (bounds[0..5]) and of the bounds of the box centres (bounds[6..11]) over the boxes of
+// one block's threads, then one ordered-int atomic per value and block (min/max are exact, so the order does not matter).
+__device__ __forceinline__ void reduce_bounds(const float (&lo)[3], const float (&hi)[3], bool valid, int* __restrict__ bounds) {
+    __shared__ float s_lo[6][8], s_hi[6][8];
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        float a = lo[k % 3], b = hi[k % 3];
+        if (k >= 3) { a = valid ? (lo[k - 3] + hi[k - 3]) * 0.5f : a; b = valid ? a : b; }      // centre, as k_morton computes it
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            a = fminf(a, __shfl_xor_sync(0xffffffffu, a, o));
+            b = fmaxf(b, __shfl_xor_sync(0xffffffffu, b, o));
+        }
+        if (lane == 0) { s_lo[k][w] = a; s_hi[k][w] = b; }
+    }
+    __syncthreads();
+    if (threadIdx.x < 6) {
+        int k = threadIdx.x;
+        float a = s_lo[k][0], b = s_hi[k][0];
+        for (int i = 1; i < (int)(blockDim.x >> 5); ++i) { a = fminf(a, s_lo[k][i]); b = fmaxf(b, s_hi[k][i]); }
+        const int at = k < 3 ? k : 6 + (k - 3);
+        if (a <= b) { atomicMin(&bounds[at], f2ord(a)); atomicMax(&bounds[at + 3], f2ord(b)); }
+    }
+}
+
 // AABB of primitive q (input order: spheres, quads, triangles). The exact expression
 // order is part of the bit-exact contract with the oracle.
+// Triangles: their boxes (and their share of the two bounds, tri_bounds) were written when the scene was ingested
+// (k_ingest_tris had the vertices in registers), so this pass runs over the spheres and quads only.
 __global__ void k_prim_bounds(const SphereRec* __restrict__ spheres, int ns,
                               const QuadRec* __restrict__ quads, int nq,
-                              const float4* __restrict__ tri_v, int nt,
+                              const float4* __restrict__ tri_v, int nt, const int* __restrict__ tri_bounds,
                               float4* __restrict__ amin, float4* __restrict__ amax,
                               int* __restrict__ bounds) {
+    if (tri_bounds && blockIdx.x == 0 && threadIdx.x < 12) {
+        const int k = threadIdx.x, v = tri_bounds[k];
+        if ((k % 6) < 3) atomicMin(&bounds[k], v); else atomicMax(&bounds[k], v);
+    }
     int n = ns + nq + nt;
     int q = blockIdx.x * blockDim.x + threadIdx.x;
     float lo[3] = {__int_as_float(0x7f800000), __int_as_float(0x7f800000), __int_as_float(0x7f800000)};
@@ -51,7 +83,7 @@ __global__ void k_prim_bounds(const SphereRec* __restrict__ spheres, int ns,
                 lo[k] = fminf(fminf(p0, p1), fminf(p2, p3));
                 hi[k] = fmaxf(fmaxf(p0, p1), fmaxf(p2, p3));
             }
-        } else {
+        } else {                                                         // only without an ingest pass (never on the product path)
             int t = q - ns - nq;
             float4 v0 = tri_v[6 * (size_t)t], v1 = tri_v[6 * (size_t)t + 1], v2 = tri_v[6 * (size_t)t + 2];
             lo[0] = fminf(fminf(v0.x, v1.x), v2.x); hi[0] = fmaxf(fmaxf(v0.x, v1.x), v2.x);
@@ -61,28 +93,57 @@ __global__ void k_prim_bounds(const SphereRec* __restrict__ spheres, int ns,
         amin[2 * q] = make_float4(lo[0], lo[1], lo[2], 0.f);            // {min, max} interleaved: one 32-byte sector per box
         amax[2 * q] = make_float4(hi[0], hi[1], hi[2], 0.f);
     }
-    // block reduction of the scene bounds and of the bounds of the box centres (min/max are exact, so order does not matter)
-    __shared__ float s_lo[6][8], s_hi[6][8];
-    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    reduce_bounds(lo, hi, q < n, bounds);
+}
+
+// Triangle ingest (prt_set_scene): the caller's packed arrays (9 floats per triangle, optional 9 floats of vertex normals,
+// optional material index) are copied to the device as they are and expanded here into the 96-byte records the build
+// gathers {v0, v1 | material, v2, n0, n1, n2}. The vertices are in registers, so the triangle's box (build input, same
+// min/max as the oracle's prim_bounds) and its share of the scene / centre bounds are produced here as well: the build has
+// no pass over the triangles before the Morton codes. Flat normal when none is given: cross(v1 - v0, v2 - v0), unnormalised.
+__global__ void __launch_bounds__(256)
+k_ingest_tris(int n, const float* __restrict__ v, const float* __restrict__ nrm, const int* __restrict__ mat, int mat_default,
+              float4* __restrict__ out_v, float4* __restrict__ out_n, float4* __restrict__ box, int* __restrict__ tri_bounds) {
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    float lo[3] = {__int_as_float(0x7f800000), __int_as_float(0x7f800000), __int_as_float(0x7f800000)};
+    float hi[3] = {__int_as_float(0xff800000), __int_as_float(0xff800000), __int_as_float(0xff800000)};
+    if (t < n) {
+        float a[9];
 #pragma unroll
-    for (int k = 0; k < 6; ++k) {
-        float a = lo[k % 3], b = hi[k % 3];
-        if (k >= 3) { a = q < n ? (lo[k - 3] + hi[k - 3]) * 0.5f : a; b = q < n ? a : b; }      // centre, as k_morton computes it
+        for (int k = 0; k < 9; ++k) a[k] = v[9 * (size_t)t + k];
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            a = fminf(a, __shfl_xor_sync(0xffffffffu, a, o));
-            b = fmaxf(b, __shfl_xor_sync(0xffffffffu, b, o));
+        for (int k = 0; k < 3; ++k)
+            out_v[6 * (size_t)t + k] = make_float4(a[3 * k], a[3 * k + 1], a[3 * k + 2], k == 1 ? __int_as_float(mat ? mat[t] : mat_default) : 0.f);
+        if (nrm) {
+#pragma unroll
+            for (int k = 0; k < 3; ++k)
+                out_n[6 * (size_t)t + k] = make_float4(nrm[9 * (size_t)t + 3 * k], nrm[9 * (size_t)t + 3 * k + 1], nrm[9 * (size_t)t + 3 * k + 2], 0.f);
+        } else {
+            float e1x = a[3] - a[0], e1y = a[4] - a[1], e1z = a[5] - a[2], e2x = a[6] - a[0], e2y = a[7] - a[1], e2z = a[8] - a[2];
+            float nx = e1y * e2z - e2y * e1z, ny = e1z * e2x - e2z * e1x, nz = e1x * e2y - e2x * e1y;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) out_n[6 * (size_t)t + k] = make_float4(nx, ny, nz, 0.f);
         }
-        if (lane == 0) { s_lo[k][w] = a; s_hi[k][w] = b; }
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { lo[k] = fminf(fminf(a[k], a[3 + k]), a[6 + k]); hi[k] = fmaxf(fmaxf(a[k], a[3 + k]), a[6 + k]); }
+        box[2 * (size_t)t] = make_float4(lo[0], lo[1], lo[2], 0.f);
+        box[2 * (size_t)t + 1] = make_float4(hi[0], hi[1], hi[2], 0.f);
     }
-    __syncthreads();
-    if (threadIdx.x < 6) {
-        int k = threadIdx.x;
-        float a = s_lo[k][0], b = s_hi[k][0];
-        for (int i = 1; i < (int)(blockDim.x >> 5); ++i) { a = fminf(a, s_lo[k][i]); b = fmaxf(b, s_hi[k][i]); }
-        const int at = k < 3 ? k : 6 + (k - 3);
-        if (a <= b) { atomicMin(&bounds[at], f2ord(a)); atomicMax(&bounds[at + 3], f2ord(b)); }
-    }
+    reduce_bounds(lo, hi, t < n, tri_bounds);
+}
+
+// raw_* = the packed arrays already on the device; allocates the records and the primitive boxes (all primitives)
+int lbvh_ingest_tris(Ctx* c, int n_spheres, int n_quads, int n_tris, bool have_normals, bool have_mat, int mat_default) {
+    int rc;
+    const size_t nn = (size_t)n_spheres + n_quads + n_tris, nt = (size_t)n_tris;
+    if ((rc = dev_reserve(c, c->tri_in_v, nt * 96)) || (rc = dev_reserve(c, c->aabb_min, nn * 32)) || (rc = dev_reserve(c, c->tri_bounds, 12 * sizeof(int))))
+        return rc;
+    k_init_bounds<<<1, 32, 0, c->stream>>>((int*)c->tri_bounds.p);
+    if (n_tris > 0)
+        k_ingest_tris<<<(unsigned)((nt + 255) / 256), 256, 0, c->stream>>>(n_tris, (const float*)c->raw_v.p, have_normals ? (const float*)c->raw_n.p : nullptr,
+            have_mat ? (const int*)c->raw_m.p : nullptr, mat_default, (float4*)c->tri_in_v.p, (float4*)c->tri_in_v.p + 3,
+            (float4*)c->aabb_min.p + 2 * ((size_t)n_spheres + n_quads), (int*)c->tri_bounds.p);
+    return PRT_OK;
 }
 
 __device__ __forceinline__ uint32_t expand10(uint32_t v) {
@@ -413,20 +474,34 @@ __global__ void k_gather_tris(int n, int ns, int nq, int tri_prim_base, const ui
 // round fits one tile, CTA 0 finishes alone with __syncthreads(). Everything another CTA wrote is read with ld.cg.
 constexpr int PL_THREADS = 256, PL_ITEMS = 4, PL_TILE = PL_THREADS * PL_ITEMS, PL_RMAX = 8;
 constexpr int PL_SPAN = PL_TILE + 4 * PL_RMAX;
+constexpr int PL_SMALL_ROUND = 160 << 10;   // rounds with at most this many clusters use 256-cluster tiles (one per thread)
 constexpr int PL_MAX_ROUNDS = 192;          // a round may merge a single pair (nested boxes): give up, Karras takes over
 constexpr int PL_MAX_HEIGHT = 84;           // 3 * height + 1 <= 256 stack entries (wavefront.cu STACK_TOTAL)
 // ctl words
-enum { PC_COUNT = 0, PC_NEXT = 2, PC_TICKET = 4, PC_HEIGHT = 6, PC_ROUNDS = 7, PC_FAIL = 8, PC_WORDS = 16 };
+enum { PC_COUNT = 0, PC_NEXT = 2, PC_TICKET = 4, PC_HEIGHT = 6, PC_ROUNDS = 7, PC_FAIL = 8, PC_BAR_COUNT = 9, PC_BAR_GEN = 10, PC_WORDS = 16,
+       PC_TRACE = 16, PC_ALL = PC_TRACE + 2 * (PL_MAX_ROUNDS + 1) };   // per round: cluster count, %globaltimer (ns, low word) at its start
 
-__device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long long* p) {
-    unsigned long long v; asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory"); return v;
+// Tile status words of the chained scan carry their own payload (flag and counts in ONE 64-bit word), so relaxed
+// device-scope accesses suffice: nothing else is read on the strength of having seen a flag.
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* p) {
+    unsigned long long v; asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory"); return v;
 }
-__device__ __forceinline__ void st_release_u64(unsigned long long* p, unsigned long long v) {
-    asm volatile("st.release.gpu.global.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
+__device__ __forceinline__ void st_relaxed_u64(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
 }
 
+// half-area of the union of two boxes; the exact expression is part of the bit-exact contract with the oracle
+__device__ __forceinline__ float union_area(float4 a0, float4 a1, float4 b0, float4 b1) {
+    const float dx = fmaxf(a1.x, b1.x) - fminf(a0.x, b0.x);
+    const float dy = fmaxf(a1.y, b1.y) - fminf(a0.y, b0.y);
+    const float dz = fmaxf(a1.z, b1.z) - fminf(a0.z, b0.z);
+    return (dx * dy + dy * dz) + dz * dx;
+}
+
+// RT = search radius known at compile time (4, the default: the neighbour loop is unrolled) or 0 = the run-time value R.
+template <int RT>
 __global__ void __launch_bounds__(PL_THREADS)
-k_ploc(int n, int R, int ns, int nq, const uint32_t* __restrict__ sorted_prim, const float4* leaf_box,
+k_ploc(int n, int R_, int ns, int nq, const uint32_t* __restrict__ sorted_prim, const float4* leaf_box,
        int* code_a, int* code_b, float4* box_a, float4* box_b, unsigned long long* status, int* ctl,
        BvhNode* __restrict__ nodes, int* __restrict__ children, int* __restrict__ parent) {
     cg::grid_group grid = cg::this_grid();
@@ -435,16 +510,25 @@ k_ploc(int n, int R, int ns, int nq, const uint32_t* __restrict__ sorted_prim, c
     __shared__ uint32_t s_warp[PL_THREADS / 32];
     __shared__ int s_tile;
     __shared__ uint32_t s_excl[2];
+    const int R = RT ? RT : R_;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const float INF = __int_as_float(0x7f800000);
     for (int round = 0;; ++round) {
         const int par = round & 1;
         const int c = __ldcg(&ctl[PC_COUNT + par]), next = __ldcg(&ctl[PC_NEXT + par]);
+        if (blockIdx.x == 0 && tid == 0) {                   // round trace (prt_debug_ploc_trace): one store pair per round
+            unsigned long long ns_; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(ns_));
+            ctl[PC_TRACE + 2 * round] = c; ctl[PC_TRACE + 2 * round + 1] = (int)(uint32_t)ns_;
+        }
         if (c <= 1) break;
         if (round >= PL_MAX_ROUNDS) { if (blockIdx.x == 0 && tid == 0) ctl[PC_FAIL] = 1; break; }
         const bool single = c <= PL_TILE;                    // the rest of the build fits one tile: CTA 0 finishes alone
         if (single && blockIdx.x != 0) break;
-        const int ntiles = (c + PL_TILE - 1) / PL_TILE;
+        // clusters per thread: 4 while there is work for every CTA, 1 for the thin middle rounds (a round is then as long as
+        // ONE tile's critical path - load, search, scan, look-back, write -, so short tiles on many CTAs beat long ones on few)
+        const int ipt = (single || c > PL_SMALL_ROUND) ? PL_ITEMS : 1;
+        const int tile = PL_THREADS * ipt;
+        const int ntiles = (c + tile - 1) / tile;
         // round r reads what round r-1 wrote (round 0: the sorted leaf boxes, codes implicit) and writes the other buffer
         const float4* bin = round == 0 ? leaf_box : (par ? box_b : box_a);
         const int* cin = par ? code_b : code_a;
@@ -457,8 +541,8 @@ k_ploc(int n, int R, int ns, int nq, const uint32_t* __restrict__ sorted_prim, c
             __syncthreads();
             const int t = s_tile;
             if (t >= ntiles) break;
-            const int t0 = t * PL_TILE, lo = t0 - 2 * R;     // global position of shared slot 0
-            for (int k = tid; k < PL_TILE + 4 * R; k += PL_THREADS) {
+            const int t0 = t * tile, lo = t0 - 2 * R;        // global position of shared slot 0
+            for (int k = tid; k < tile + 4 * R; k += PL_THREADS) {
                 const int g = lo + k;
                 if (g >= 0 && g < c) {
                     s_min[k] = __ldcg(&bin[2 * (size_t)g]); s_max[k] = __ldcg(&bin[2 * (size_t)g + 1]);
@@ -467,32 +551,38 @@ k_ploc(int n, int R, int ns, int nq, const uint32_t* __restrict__ sorted_prim, c
             }
             __syncthreads();
             // nearest neighbour of every cluster of the tile and of R more on either side (their choice decides "mutual")
-            for (int k = R + tid; k < PL_TILE + 3 * R; k += PL_THREADS) {
+            for (int k = R + tid; k < tile + 3 * R; k += PL_THREADS) {
                 const int g = lo + k;
                 int bj = -1;
                 if (g >= 0 && g < c) {
                     const float4 a0 = s_min[k], a1 = s_max[k];
                     float best = INF;
-                    const int j0 = max(0, g - R), j1 = min(c - 1, g + R);
-                    for (int j = j0; j <= j1; ++j) {
-                        if (j == g) continue;
-                        const float4 b0 = s_min[j - lo], b1 = s_max[j - lo];
-                        const float dx = fmaxf(a1.x, b1.x) - fminf(a0.x, b0.x);
-                        const float dy = fmaxf(a1.y, b1.y) - fminf(a0.y, b0.y);
-                        const float dz = fmaxf(a1.z, b1.z) - fminf(a0.z, b0.z);
-                        const float ar = (dx * dy + dy * dz) + dz * dx;
-                        if (ar < best || (ar == best && j == (g ^ 1))) { best = ar; bj = j; }   // ties: the partner g^1, else the lowest position
+                    if (RT) {                                // ascending j, like the run-time loop: ties go to the lowest position
+#pragma unroll
+                        for (int dr = -RT; dr <= RT; ++dr) {
+                            if (dr == 0) continue;
+                            const int j = g + dr;
+                            const float ar = (j >= 0 && j < c) ? union_area(a0, a1, s_min[k + dr], s_max[k + dr]) : INF;
+                            if ((ar < best || (ar == best && j == (g ^ 1))) && j >= 0 && j < c) { best = ar; bj = j; }
+                        }
+                    } else {
+                        const int j0 = max(0, g - R), j1 = min(c - 1, g + R);
+                        for (int j = j0; j <= j1; ++j) {
+                            if (j == g) continue;
+                            const float ar = union_area(a0, a1, s_min[j - lo], s_max[j - lo]);
+                            if (ar < best || (ar == best && j == (g ^ 1))) { best = ar; bj = j; }   // ties: the partner g^1, else the lowest position
+                        }
                     }
                 }
                 s_nn[k] = bj;
             }
             __syncthreads();
-            // 4 consecutive clusters per thread: kept (not absorbed by a lower position) / merging (lower one of a mutual pair)
+            // `ipt` consecutive clusters per thread: kept (not absorbed by a lower position) / merging (lower one of a mutual pair)
             uint32_t flags = 0, cnt = 0;                     // cnt: kept in the low half, merges in the high half
 #pragma unroll
             for (int m = 0; m < PL_ITEMS; ++m) {
-                const int k = 2 * R + tid * PL_ITEMS + m, g = lo + k;
-                if (g < c) {
+                const int k = 2 * R + tid * ipt + m, g = lo + k;
+                if (m < ipt && g < c) {
                     const int j = s_nn[k];
                     const bool mutual = s_nn[j - lo] == g;
                     const bool keep = !mutual || g < j, merge = mutual && g < j;
@@ -509,26 +599,46 @@ k_ploc(int n, int R, int ns, int nq, const uint32_t* __restrict__ sorted_prim, c
 #pragma unroll
             for (int k = 0; k < PL_THREADS / 32; ++k) { const uint32_t v = s_warp[k]; wbase += k < wid ? v : 0u; total += v; }
             uint32_t run = wbase + inc - cnt;                // exclusive prefix inside the tile
-            // chained scan across tiles (tickets are taken in order, so every predecessor is resident and will publish)
-            if (tid == 0) {
+            // Chained scan across tiles (tickets are taken in order, so every predecessor is resident and will publish): warp 0
+            // publishes this tile's aggregate, then looks back 128 tiles per step - four independent loads per lane in flight -
+            // until it meets an inclusive prefix. (With ~600 tiles in flight everybody waits on everybody, so the walk IS the
+            // tile's critical path: one thread, one tile per step took the whole build; 32 per step still cost 13 us per tile.)
+            if (wid == 0) {
                 const unsigned long long agg = ((unsigned long long)(total >> 16) << 28) | (unsigned long long)(total & 0xffffu);
+                const unsigned long long PAY = (1ull << 56) - 1ull;
                 unsigned long long excl = 0;
                 if (t > 0) {
-                    st_release_u64(&status[t], tag | (1ull << 56) | agg);
-                    for (int p = t - 1;; --p) {
-                        unsigned long long v;
-                        do { v = ld_acquire_u64(&status[p]); } while ((v >> 58) != (tag >> 58) || ((v >> 56) & 3ull) == 0ull);
-                        excl += v & ((1ull << 56) - 1ull);
-                        if (((v >> 56) & 3ull) == 2ull) break;
+                    if (lane == 0) st_relaxed_u64(&status[t], tag | (1ull << 56) | agg);
+                    bool done = false;
+                    for (int base = t - 1; !done; base -= 128) {
+                        unsigned long long v[4];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) { const int p = base - 32 * u - lane; v[u] = p >= 0 ? ld_relaxed_u64(&status[p]) : 0ull; }
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            if (done) break;
+                            const int p = base - 32 * u - lane;
+                            if (p >= 0) while ((v[u] >> 58) != (tag >> 58) || ((v[u] >> 56) & 3ull) == 0ull) v[u] = ld_relaxed_u64(&status[p]);
+                            const bool stop = p < 0 || ((v[u] >> 56) & 3ull) == 2ull;   // an inclusive prefix, or nothing before tile 0
+                            const uint32_t ball = __ballot_sync(0xffffffffu, stop);
+                            const int first = ball ? __ffs(ball) - 1 : 32;
+                            unsigned long long part = (p >= 0 && lane <= first) ? (v[u] & PAY) : 0ull;
+#pragma unroll
+                            for (int o = 16; o > 0; o >>= 1) part += __shfl_down_sync(0xffffffffu, part, o);
+                            excl += __shfl_sync(0xffffffffu, part, 0);
+                            done = ball != 0u;
+                        }
                     }
                 }
-                st_release_u64(&status[t], tag | (2ull << 56) | (excl + agg));
-                s_excl[0] = (uint32_t)(excl & ((1ull << 28) - 1ull)); s_excl[1] = (uint32_t)(excl >> 28);
-                if (t == ntiles - 1) {                       // the last tile knows the totals: parameters of the next round
-                    const unsigned long long all = excl + agg;
-                    const int c_next = (int)(all & ((1ull << 28) - 1ull)), merges = (int)(all >> 28);
-                    ctl[PC_COUNT + (par ^ 1)] = c_next; ctl[PC_NEXT + (par ^ 1)] = next - merges;
-                    ctl[PC_TICKET + (par ^ 1)] = 0; ctl[PC_ROUNDS] = round + 1;
+                if (lane == 0) {
+                    st_relaxed_u64(&status[t], tag | (2ull << 56) | (excl + agg));
+                    s_excl[0] = (uint32_t)(excl & ((1ull << 28) - 1ull)); s_excl[1] = (uint32_t)(excl >> 28);
+                    if (t == ntiles - 1) {                   // the last tile knows the totals: parameters of the next round
+                        const unsigned long long all = excl + agg;
+                        const int c_next = (int)(all & ((1ull << 28) - 1ull)), merges = (int)(all >> 28);
+                        ctl[PC_COUNT + (par ^ 1)] = c_next; ctl[PC_NEXT + (par ^ 1)] = next - merges;
+                        ctl[PC_TICKET + (par ^ 1)] = 0; ctl[PC_ROUNDS] = round + 1;
+                    }
                 }
             }
             __syncthreads();
@@ -537,7 +647,7 @@ k_ploc(int n, int R, int ns, int nq, const uint32_t* __restrict__ sorted_prim, c
             for (int m = 0; m < PL_ITEMS; ++m) {
                 const uint32_t f = (flags >> (2 * m)) & 3u;
                 if (!(f & 1u)) continue;
-                const int k = 2 * R + tid * PL_ITEMS + m;
+                const int k = 2 * R + tid * ipt + m;
                 const size_t pos = (size_t)E + (run & 0xffffu);
                 if (f & 2u) {
                     const int id = next - 1 - (int)(M + (run >> 16));
@@ -567,6 +677,7 @@ k_ploc(int n, int R, int ns, int nq, const uint32_t* __restrict__ sorted_prim, c
             }
             if (single) break;
         }
+        // (a hand-rolled counter/generation barrier was slower than cg's: 18 vs 10 us per thin round with 1184 CTAs of 128 threads)
         if (single) { __threadfence(); __syncthreads(); } else grid.sync();
     }
 }
@@ -699,15 +810,16 @@ int lbvh_build(Ctx* c) {
     if (want_wide && (rc = dev_reserve(c, c->wnodes, nn * sizeof(WideNode)))) return rc;
     const bool want_ploc = n > 2 && c->bvh_builder != 0;
     if (want_ploc && ((rc = dev_reserve(c, c->ploc_code, nn * 8)) || (rc = dev_reserve(c, c->ploc_box, nn * 32)) ||
-                      (rc = dev_reserve(c, c->ploc_status, ((nn + PL_TILE - 1) / PL_TILE) * 8)) ||
-                      (rc = dev_reserve(c, c->ploc_ctl, PC_WORDS * 4)))) return rc;
+                      (rc = dev_reserve(c, c->ploc_status, std::max<size_t>((nn + PL_TILE - 1) / PL_TILE, PL_SMALL_ROUND / PL_THREADS + 1) * 8)) ||
+                      (rc = dev_reserve(c, c->ploc_ctl, PC_ALL * 4)))) return rc;
     // every allocation is done: the timed region below is kernels only (cudaMalloc synchronises and is not build work)
     PRT_CUDA(c, cudaEventRecord(c->ev0, st));
     k_init_bounds<<<1, 32, 0, st>>>((int*)c->scene_bounds.p);
 
     const int T = 256, G = (n + T - 1) / T;
-    k_prim_bounds<<<G, T, 0, st>>>((const SphereRec*)c->spheres.p, ns, (const QuadRec*)c->quads.p, nq,
-                                   (const float4*)c->tri_in_v.p, nt, (float4*)c->aabb_min.p,
+    // boxes of the spheres and quads; the triangles' boxes and bounds come from the ingest pass of prt_set_scene
+    k_prim_bounds<<<std::max(1, (ns + nq + T - 1) / T), T, 0, st>>>((const SphereRec*)c->spheres.p, ns, (const QuadRec*)c->quads.p, nq,
+                                   (const float4*)c->tri_in_v.p, 0, nt ? (const int*)c->tri_bounds.p : nullptr, (float4*)c->aabb_min.p,
                                    (float4*)c->aabb_min.p + 1, (int*)c->scene_bounds.p);
     k_morton<<<G, T, 0, st>>>((const float4*)c->aabb_min.p, (const float4*)c->aabb_min.p + 1, n,
                               (const int*)c->scene_bounds.p + (c->morton_centroid ? 6 : 0), (uint32_t*)c->keys[0].p,
@@ -742,20 +854,23 @@ int lbvh_build(Ctx* c) {
             const int ctl0[PC_WORDS] = {n, 0, n - 1, 0};
             PRT_CUDA(c, cudaMemcpyAsync(ctl, ctl0, sizeof ctl0, cudaMemcpyHostToDevice, st));
             const int ntiles = (n + PL_TILE - 1) / PL_TILE;
-            PRT_CUDA(c, cudaMemsetAsync(c->ploc_status.p, 0, (size_t)ntiles * 8, st));
+            PRT_CUDA(c, cudaMemsetAsync(c->ploc_status.p, 0, c->ploc_status.bytes, st));
             int per_sm = 0;
-            PRT_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ploc, PL_THREADS, 0));
+            int R = std::min(PL_RMAX, std::max(1, c->ploc_radius));
+            const void* kern = R == 4 ? (const void*)k_ploc<4> : (const void*)k_ploc<0>;
+            PRT_CUDA(c, R == 4 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ploc<4>, PL_THREADS, 0)
+                               : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ploc<0>, PL_THREADS, 0));
             const int grid = std::max(1, std::min(ntiles, c->num_sms * std::max(1, per_sm)));
-            int R = std::min(PL_RMAX, std::max(1, c->ploc_radius)), n_ = n, ns_ = ns, nq_ = nq;
+            int n_ = n, ns_ = ns, nq_ = nq;
             const uint32_t* sp_ = sprim; const float4* lb_ = (const float4*)c->leaf_box.p;
             int *ca = (int*)c->ploc_code.p, *cb = ca + n;
             float4 *ba = (float4*)c->ploc_box.p, *bb = (float4*)c->node_min.p;
             unsigned long long* stt = (unsigned long long*)c->ploc_status.p;
             BvhNode* nodes_ = (BvhNode*)c->nodes.p; int* ch_ = (int*)c->children.p;
             void* args[] = {&n_, &R, &ns_, &nq_, &sp_, &lb_, &ca, &cb, &ba, &bb, &stt, &ctl, &nodes_, &ch_, &parent};
-            PRT_CUDA(c, cudaLaunchCooperativeKernel((const void*)k_ploc, dim3(grid), dim3(PL_THREADS), args, 0, st));
-            int res[PC_WORDS];
-            PRT_CUDA(c, cudaMemcpyAsync(res, ctl, sizeof res, cudaMemcpyDeviceToHost, st));
+            PRT_CUDA(c, cudaLaunchCooperativeKernel(kern, dim3(grid), dim3(PL_THREADS), args, 0, st));
+            int* res = c->ploc_trace;
+            PRT_CUDA(c, cudaMemcpyAsync(res, ctl, PC_ALL * 4, cudaMemcpyDeviceToHost, st));
             PRT_CUDA(c, cudaStreamSynchronize(st));
             c->ploc_rounds = res[PC_ROUNDS];
             ploc_done = !res[PC_FAIL] && res[PC_HEIGHT] <= PL_MAX_HEIGHT;

@@ -34,7 +34,8 @@ struct Ctx {
 
     // ---- LBVH ----
     DevBuf aabb_min, leaf_box;                  // {min, max} float4 pairs (32 B per box): per q in input order / per leaf slot in sorted order
-    DevBuf scene_bounds;                        // 6 ordered-int floats
+    DevBuf scene_bounds;                        // 12 ordered-int floats: scene bounds, bounds of the box centres
+    DevBuf tri_bounds;                          // the triangles' share of both, reduced when the scene is ingested
     DevBuf keys[2], vals[2];                    // radix sort ping-pong
     DevBuf block_hist;                          // digit-major per-block histograms
     DevBuf ray_keys[2][2], ray_vals[2][2], ray_hist[2];   // ray re-sorting, per buffer set: key/index ping-pong + histograms
@@ -52,6 +53,7 @@ struct Ctx {
     int bvh_builder = 1;                        // hierarchy over the sorted leaves: 1 PLOC (falls back to Karras when it fails), 0 Karras (plain LBVH)
     int ploc_radius = 4;                        // neighbours searched on either side (1..8); 4 measured best (oracle counters: dragon, 809 spheres)
     int builder_used = 0, bvh_height = 0, ploc_rounds = 0;
+    int ploc_trace[16 + 2 * 193] = {0};         // control words of the last PLOC build + (cluster count, ns timestamp) per round
     DevBuf tri_v, tri_n;                        // leaf-slot order (3 float4 per slot)
     DevBuf morton;                              // per q (kept for prt_debug_lbvh)
     int sorted_slot = 0;                        // which of keys/vals holds the sorted result
@@ -121,6 +123,7 @@ SceneView scene_view(const Ctx* c);
 
 // lbvh.cu
 int lbvh_build(Ctx* c);
+int lbvh_ingest_tris(Ctx* c, int n_spheres, int n_quads, int n_tris, bool have_normals, bool have_mat, int mat_default);
 int sort_ray_queue(Ctx* c, cudaStream_t st, int set, int64_t capacity, const uint32_t* n_dev, const float4* so, const float4* sd,
                    const float4* sb, float4* to, float4* td, float4* tb);
 // wavefront.cu

@@ -20,3 +20,8 @@ for i in range(4):
     c.build_bvh()
     st = c.stats()
     print("%s %s: build_ms %.3f builder %d height %d rounds %d" % (what, " ".join(sys.argv[2:]), st.build_ms, st.bvh_builder, st.bvh_height, st.ploc_rounds), flush=True)
+cnt, us = c.ploc_trace()
+if len(us):
+    print("PLOC rounds (clusters at start : microseconds):")
+    print("  " + "  ".join("%d:%.1f" % (int(a), b) for a, b in zip(cnt[:-1], us)))
+    print("  rounds with > 1 tile: %.1f us, single-CTA rounds: %.1f us" % (us[cnt[:-1] > 1024].sum(), us[cnt[:-1] <= 1024].sum()))

@@ -265,6 +265,13 @@ int  prt_debug_lbvh(prt_ctx* ctx, uint32_t* morton, uint32_t* sorted_prim,
  * the two-child nodes; every internal node has a record (greedy collapse by surface area, 2..4 slots). Returns
  * PRT_ERR_INVALID if not built. */
 int  prt_debug_wide(prt_ctx* ctx, uint32_t* words);
+/* The repo's own memcheck (compute-sanitizer is closed on the GPU pool): libprt_b200_checked.so is the same library compiled
+ * with -DPRT_CHECKED=1 - every data-derived index in device code (traversal stack pointers, queue slots, node and leaf
+ * codes, PLOC positions and node ids, sort scatter positions) is tested before the access, violations set PRT_CHK_* bits
+ * (prt_device.cuh) and skip the access. Returns the bits raised since the last call, OR-ed with 1<<30 (= "this is the
+ * checked library"); the regular library returns 0. */
+int  prt_debug_check_flags(prt_ctx* ctx);
+
 /* Round trace of the last PLOC build: counts[r] = clusters at the start of round r, ns[r] = device %globaltimer (low 32 bits,
  * nanoseconds) at that moment; returns the number of entries written (rounds + 1, <= max_rounds) or < 0. Profiling aid. */
 int  prt_debug_ploc_trace(prt_ctx* ctx, int32_t* counts, uint32_t* ns, int max_rounds);

@@ -25,10 +25,13 @@ def nvcc_path():
     raise RuntimeError("nvcc not found")
 
 
-def source_hash():
+OUT_CHECKED = os.path.join(HERE, "libprt_b200_checked.so")
+
+
+def source_hash(checked=False):
     """sha256 over the compiler flags and every source / header the library is built from."""
     import hashlib
-    h = hashlib.sha256(" ".join(NVCC_FLAGS).encode())
+    h = hashlib.sha256((" ".join(NVCC_FLAGS) + (" -DPRT_CHECKED=1" if checked else "")).encode())
     for d in SOURCES + HEADERS:
         with open(os.path.join(CSRC, d), "rb") as f:
             h.update(d.encode()); h.update(f.read())
@@ -38,28 +41,32 @@ def source_hash():
 STAMP = OUT + ".srchash"
 
 
-def needs_build():
-    """True when libprt_b200.so is missing or was built from other sources / flags than the ones in the tree (content hash,
-    not mtimes: the tree is copied to the GPU box)."""
-    if not os.path.exists(OUT) or not os.path.exists(STAMP):
+def needs_build(checked=False):
+    """True when the library is missing or was built from other sources / flags than the ones in the tree (content hash,
+    not mtimes: the tree is copied to the GPU box). checked=True: libprt_b200_checked.so (-DPRT_CHECKED=1, the bounds-checked
+    build the tests run the small configurations through - compute-sanitizer is closed on the GPU pool)."""
+    out = OUT_CHECKED if checked else OUT
+    if not os.path.exists(out) or not os.path.exists(out + ".srchash"):
         return True
-    with open(STAMP) as f:
-        return f.read().strip() != source_hash()
+    with open(out + ".srchash") as f:
+        return f.read().strip() != source_hash(checked)
 
 
-def build(force=False, verbose=False):
-    if not force and not needs_build():
-        return OUT
-    cmd = [nvcc_path()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", OUT] + SOURCES
+def build(force=False, verbose=False, checked=False):
+    out = OUT_CHECKED if checked else OUT
+    if not force and not needs_build(checked):
+        return out
+    cmd = [nvcc_path()] + NVCC_FLAGS + (["-DPRT_CHECKED=1"] if checked else []) + (["-Xptxas", "-v"] if verbose else []) + ["-o", out] + SOURCES
     r = subprocess.run(cmd, cwd=CSRC, capture_output=True, text=True)
     if verbose:
         print(r.stdout, r.stderr)
     if r.returncode != 0:
         raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
-    with open(STAMP, "w") as f:
-        f.write(source_hash())
-    return OUT
+    with open(out + ".srchash", "w") as f:
+        f.write(source_hash(checked))
+    return out
 
 
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build(force="--force" in sys.argv, checked=True))

@@ -48,14 +48,15 @@ EXPORTS = [
     "prt_create", "prt_create_multi", "prt_destroy", "prt_last_error", "prt_version", "prt_set_scene", "prt_build_bvh",
     "prt_set_camera", "prt_render", "prt_render_fresh", "prt_render_region", "prt_clear_accum", "prt_scale_accum", "prt_accum_device_ptr",
     "prt_set_accum_buffer", "prt_read_accum", "prt_accum_spp", "prt_set_accum_spp", "prt_resolve_display", "prt_trace_batch",
-    "prt_debug_lbvh", "prt_debug_wide", "prt_debug_scatter", "prt_debug_ploc_trace", "prt_host_alloc", "prt_host_free", "prt_num_prims", "prt_enable_counters", "prt_get_stats", "prt_set_option",
+    "prt_debug_lbvh", "prt_debug_wide", "prt_debug_scatter", "prt_debug_ploc_trace", "prt_debug_check_flags", "prt_host_alloc", "prt_host_free", "prt_num_prims", "prt_enable_counters", "prt_get_stats", "prt_set_option",
 ]
 
 _lib = None
 
 
 def lib_path():
-    return os.path.join(HERE, "libprt_b200.so")
+    """libprt_b200.so, or - PRT_CHECKED=1 in the environment - the bounds-checked build of the same sources."""
+    return os.path.join(HERE, "libprt_b200_checked.so" if os.environ.get("PRT_CHECKED") == "1" else "libprt_b200.so")
 
 
 def load_library():
@@ -65,9 +66,10 @@ def load_library():
         return _lib
     p = lib_path()
     from . import build as _build
-    if _build.needs_build():                       # missing, or built from other sources than the tree holds: never run a stale .so
+    checked = os.environ.get("PRT_CHECKED") == "1"
+    if _build.needs_build(checked=checked):        # missing, or built from other sources than the tree holds: never run a stale .so
         try:
-            _build.build()
+            _build.build(checked=checked)
         except Exception as e:  # noqa: BLE001
             raise PrtError(f"{p} is missing or older than its sources and could not be rebuilt ({e}); run "
                            "`python -m parallelraytracing_b200.build` (needs nvcc). There is no CPU fallback.")
@@ -97,6 +99,7 @@ def load_library():
     lib.prt_debug_wide.argtypes = [vp, vp]
     lib.prt_debug_scatter.argtypes = [vp, vp, vp, vp, vp, vp, u64, i32, vp]
     lib.prt_debug_ploc_trace.argtypes = [vp, vp, vp, i32]
+    lib.prt_debug_check_flags.argtypes = [vp]
     lib.prt_host_alloc.argtypes = [C.c_size_t]; lib.prt_host_alloc.restype = vp
     lib.prt_host_free.argtypes = [vp]; lib.prt_host_free.restype = None
     lib.prt_num_prims.argtypes = [vp]
@@ -269,6 +272,10 @@ class Context:
         self._check(self.lib.prt_debug_scatter(self.h, _ptr(mats), _ptr(i_), _ptr(n_), _ptr(f_), _ptr(k_), seed, len(mats), _ptr(out)),
                     "prt_debug_scatter")
         return out
+
+    def check_flags(self):
+        """Checked library only (PRT_CHECKED=1): PRT_CHK_* bits raised since the last call | 1<<30; 0 from the regular library."""
+        return self.lib.prt_debug_check_flags(self.h)
 
     def ploc_trace(self):
         """(clusters at the start of each PLOC round, microseconds each round took) of the last build."""

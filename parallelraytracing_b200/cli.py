@@ -63,7 +63,9 @@ def main(argv=None):
     ap.add_argument("--raw", default=None, help="also save the float accumulation buffer (sum of samples) as .npy")
     ap.add_argument("--partition", default="samples", choices=["samples", "tiles"],
                     help="multi-GPU split of a frame: sample ranges, or bands of rows (SURVEY 8e)")
-    ap.add_argument("--opt", action="append", default=[], help="prt_set_option key=value")
+    ap.add_argument("--opt", action="append", default=[], help="prt_set_option key=value (applied before Init, so build-time options count)")
+    ap.add_argument("--devices", default=None, help="comma-separated CUDA ordinals: ONE process drives them all (prt_create_multi); "
+                                                   "alternative to one process per GPU under torchrun")
     args = ap.parse_args(argv)
 
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
@@ -76,14 +78,25 @@ def main(argv=None):
     cam = S.Camera(pos=tuple(float(x) for x in cam.pos), front=cam.front, width=args.width, height=args.height)
 
     film = Film(args.width, args.height)
-    r = B200Renderer(device=local, max_depth=args.depth, samples_per_call=args.spp_per_frame, seed=args.seed)
+    devices = [int(d) for d in args.devices.split(",")] if args.devices else None
+    r = B200Renderer(device=devices if devices and len(devices) > 1 else (devices[0] if devices else local),
+                     max_depth=args.depth, samples_per_call=args.spp_per_frame, seed=args.seed)
     t0 = time.perf_counter()
+    # options BEFORE Init: build-time ones (bvh_builder, ploc_radius, bvh_wide, wide_min_prims, morton_centroid) take effect in
+    # prt_build_bvh, which Init runs - applied afterwards they silently measured the default tree (advisor finding, round 1)
+    from .capi import Context, PrtError
+    try:
+        r.ctx = Context(r.m_Device)
+        for kv in args.opt:
+            k, v = kv.split("=")
+            r.ctx.set_option(k, int(v))
+        if devices and len(devices) > 1 and args.partition == "tiles":
+            r.ctx.set_option("multi_partition", 1)
+    except PrtError as e:
+        raise SystemExit("B200Renderer: %s (there is no CPU path)" % e)
     r.Init(film, sd, cam)
     if not r.ok:
         raise SystemExit("B200Renderer.Init failed: no CUDA device or libprt_b200.so (there is no CPU path)")
-    for kv in args.opt:
-        k, v = kv.split("=")
-        r.ctx.set_option(k, int(v))
     init_ms = 1e3 * (time.perf_counter() - t0)
     film.Clear()
 
@@ -131,7 +144,8 @@ def main(argv=None):
         print(json.dumps({
             "scene": sd.name, "prims": sd.n_prims, "width": args.width, "height": args.height, "frames": args.frames,
             "spp_per_frame": args.spp_per_frame * world, "spp_total": int(weight), "depth": args.depth, "seed": args.seed,
-            "n_gpus": world, "init_ms": init_ms, "bvh_build_ms": st.build_ms,
+            "n_gpus": world * st.n_devices, "init_ms": init_ms, "bvh_build_ms": st.build_ms,
+            "bvh_builder": "ploc" if st.bvh_builder == 1 else "karras", "options": args.opt,
             "render_ms_avg": float(np.mean(render_ms)), "film_update_ms_avg": float(np.mean(film_ms)), "present_ms": upload_ms,
             "rays_rank0": int(rays), "mrays_per_s_rank0_wall": rays / max(1e-9, sum(render_ms)) / 1e3,
             "mean_radiance": float(accum.mean() / max(1, weight)), "out": args.out}))

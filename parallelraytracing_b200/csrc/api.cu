@@ -626,6 +626,22 @@ int prt_debug_scatter(prt_ctx* ctx, const prt_material* mats, const float* in_di
     return wavefront_debug_scatter(&ctx->c, mats, in_dirs, normals, fronts, keys, seed, n, out);
 }
 
+int prt_debug_check_flags(prt_ctx* ctx) {
+    if (!ctx) return PRT_ERR_INVALID;
+#if PRT_CHECKED
+    int flags = 0;
+    for (prt_ctx* d : all_devices(ctx)) {
+        cudaSetDevice(d->c.device);
+        cudaDeviceSynchronize();
+        flags |= (int)(wavefront_check_flags() | lbvh_check_flags());
+    }
+    cudaSetDevice(ctx->c.device);
+    return flags | 0x40000000;                 // bit 30: this IS the checked library
+#else
+    return 0;
+#endif
+}
+
 void* prt_host_alloc(size_t bytes) {
     void* p = nullptr;
     if (cudaHostAlloc(&p, bytes ? bytes : 16, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); return nullptr; }
@@ -743,6 +759,7 @@ int prt_set_option(prt_ctx* ctx, const char* key, int64_t value) {
     else if (!strcmp(key, "rr_start")) c->rr_start = value < 0 ? -1 : (int)value;                 // -1 = off (reference estimator)
     else if (!strcmp(key, "firefly_clamp_milli")) c->firefly_clamp = value <= 0 ? 0.f : (float)value * 1e-3f;   // 0 = off
     else if (!strcmp(key, "stage_timing")) c->stage_timing = value ? 1 : 0;
+    else if (!strcmp(key, "check_stack_limit")) { cudaSetDevice(c->device); wavefront_set_stack_limit((int)value); }   // checked library only (no-op otherwise)
     else return set_err(c, PRT_ERR_INVALID, std::string("unknown option: ") + key);
     return PRT_OK;
 }

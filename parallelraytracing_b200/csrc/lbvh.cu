@@ -284,6 +284,7 @@ k_rs_scatter(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ 
         int i = base + r * 32 + lane;
         if (i < n) {
             uint32_t pos = cnt[w][(key[r] >> shift) & 255u] + rank[r];
+            if (!PRT_CHECK(pos < (uint32_t)n, PRT_CHK_SORT)) continue;
             keys_out[pos] = key[r]; vals_out[pos] = val[r];
         }
     }
@@ -402,6 +403,7 @@ __global__ void k_refit(int n, const uint32_t* __restrict__ sorted_prim, const f
     int node = leaf_parent[pos];
     bool first = true;
     while (node >= 0) {
+        if (!PRT_CHECK(node < n - 1, PRT_CHK_REFIT)) return;
         // topology (written by k_karras, read-only here) is fetched BEFORE the fence/atomic so that its latency overlaps
         // theirs: per level the dependent chain is atomic -> child boxes, not atomic -> children -> boxes -> parent
         const int2 ch = __ldg(reinterpret_cast<const int2*>(children) + node);
@@ -649,9 +651,11 @@ k_ploc(int n, int R_, int ns, int nq, const uint32_t* __restrict__ sorted_prim, 
                 if (!(f & 1u)) continue;
                 const int k = 2 * R + tid * ipt + m;
                 const size_t pos = (size_t)E + (run & 0xffffu);
+                if (!PRT_CHECK(pos < (size_t)c && k < PL_SPAN, PRT_CHK_PLOC)) continue;
                 if (f & 2u) {
                     const int id = next - 1 - (int)(M + (run >> 16));
                     const int kj = s_nn[k] - lo;
+                    if (!PRT_CHECK(id >= 0 && id < n - 1 && kj >= 0 && kj < PL_SPAN, PRT_CHK_PLOC)) continue;
                     const float4 a0 = s_min[k], a1 = s_max[k], b0 = s_min[kj], b1 = s_max[kj];
                     const int ci = s_code[k], cj = s_code[kj];
                     const int h = max(__float_as_int(a0.w), __float_as_int(b0.w)) + 1;
@@ -742,6 +746,7 @@ __global__ void k_emit_wide(int n_internal, const int* __restrict__ parent, cons
             if (c < ns && code[c] >= 0) { const float ar = box_area(lo[c], hi[c]); if (ar > best) { best = ar; s = c; } }   // ties: lowest slot
         if (s >= 0) {
             const int cs = s == 0 ? code[0] : s == 1 ? code[1] : code[2];
+            if (!PRT_CHECK(cs < n_internal, PRT_CHK_REFIT)) break;
             const BvhNode ch = nodes[cs];
             if (s == 0) open_slot<0>(lo, hi, code, ns, ch);
             else if (s == 1) open_slot<1>(lo, hi, code, ns, ch);
@@ -779,6 +784,17 @@ __global__ void k_emit_wide(int n_internal, const int* __restrict__ parent, cons
 #pragma unroll
     for (int c = 0; c < 4; ++c) w.code[c] = c < ns ? code[c] : code[0];
     wide[i] = w;
+}
+
+unsigned lbvh_check_flags() {
+#if PRT_CHECKED
+    unsigned v = 0, z = 0;
+    cudaMemcpyFromSymbol(&v, g_prt_check_flags, sizeof v);
+    cudaMemcpyToSymbol(g_prt_check_flags, &z, sizeof z);
+    return v;
+#else
+    return 0u;
+#endif
 }
 
 // ------------------------------------------------------------------ host driver

@@ -20,6 +20,24 @@
 
 #define PRT_DEV __device__ __forceinline__
 
+// Checked build (-DPRT_CHECKED=1, libprt_b200_checked.so): every index that device code derives from data - traversal stack
+// pointers, queue slots, node / leaf codes, PLOC output positions and node ids, radix-sort scatter positions - is tested
+// before the access; a violation sets a bit in a device-global word (one per translation unit, read by prt_debug_check_flags)
+// and the access is skipped. compute-sanitizer is closed on this GPU pool, so this is the repo's own memcheck: the tests run
+// the small configurations of every kernel family through the checked library and require the word to stay zero.
+#define PRT_CHK_STACK   1u   /* traversal stack pointer beyond STACK_TOTAL                   */
+#define PRT_CHK_QUEUE   2u   /* ray / hit queue slot beyond the wave's capacity             */
+#define PRT_CHK_NODE    4u   /* node index or leaf code outside the BVH / primitive arrays  */
+#define PRT_CHK_PLOC    8u   /* PLOC: output position, node id or shared-memory slot        */
+#define PRT_CHK_SORT   16u   /* radix sort: scatter position beyond n                        */
+#define PRT_CHK_REFIT  32u   /* refit / wide emission: node index beyond n - 1               */
+#if PRT_CHECKED
+static __device__ unsigned int g_prt_check_flags = 0u;
+#define PRT_CHECK(cond, bit) ((cond) ? true : (atomicOr(&g_prt_check_flags, (bit)), false))
+#else
+#define PRT_CHECK(cond, bit) (true)
+#endif
+
 namespace prt {
 
 // ------------------------------------------------------------------ vectors
@@ -147,6 +165,7 @@ struct SceneView {
     uint32_t         one_bits; // 0x3f800000, read from the constant bank so that PRMT keeps its selector as the immediate
     float*           direct;   // != nullptr: a 1-spp single-wave "fresh" render writes each path's contribution straight to accum[3*slot..] (no contribution plane, no resolve)
     int              brute;    // tiny sphere/quad scene: test every primitive in list order, no BVH (see traverse())
+    uint32_t         capacity; // slots of the wave's queues / contribution plane (checked builds test every slot against it)
 };
 
 // ------------------------------------------------------------------ primitive tests
@@ -273,6 +292,7 @@ PRT_DEV float isect_box(const RayBox& r, float4 mn, float4 mx, float tmax) {
 // d = ray direction, dn = normalize(d) (the sphere test's local direction).
 PRT_DEV void test_leaf(const SceneView& sc, uint32_t code, V3 o, V3 d, V3 dn, const RayShear& rs, Best& best) {
     uint32_t type = PRT_LEAF_TYPE(code), idx = PRT_LEAF_INDEX(code);
+    if (!PRT_CHECK(type == 2u ? idx < (uint32_t)sc.n_prims : type == 0u ? idx < (uint32_t)sc.n_spheres : (type == 1u && idx < (uint32_t)sc.n_quads), PRT_CHK_NODE)) return;
     if (type == 2u) {
         float4 a = __ldg(&sc.tri_v[3 * idx + 0]);
         float4 b = __ldg(&sc.tri_v[3 * idx + 1]);

@@ -130,6 +130,9 @@ int sort_ray_queue(Ctx* c, cudaStream_t st, int set, int64_t capacity, const uin
 int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_begin, int64_t pixel_begin, int64_t pixel_count, bool fresh = false,
                      bool defer_finish = false);
 int wavefront_finish(Ctx* c);
+unsigned wavefront_check_flags();            // checked builds (-DPRT_CHECKED=1): violated-index bits since the last call, 0 otherwise
+unsigned lbvh_check_flags();
+void wavefront_set_stack_limit(int limit);
 int wavefront_trace_batch(Ctx* c, const prt_ray* rays, int n, prt_hit* out, int use_bvh);
 int film_resolve_display(Ctx* c, float exposure, float gamma, uint8_t* host_rgba);
 int wavefront_debug_scatter(Ctx* c, const prt_material* mats, const float* in_dirs, const float* normals, const int32_t* fronts,

@@ -27,6 +27,12 @@ constexpr int STACK_SMEM = 24;    // entries per thread held in shared memory
 // (advisor finding, round 1: 85 entries measured on an adversarial 1 M-triangle scene with the old 64). 256 in total.
 constexpr int STACK_TOTAL = 256;
 constexpr int STACK_LOCAL = STACK_TOTAL - STACK_SMEM;
+#if PRT_CHECKED
+static __device__ int g_prt_stack_limit = STACK_TOTAL;   // option check_stack_limit: lets a test prove that the stack check fires
+#define PRT_STACK_LIMIT g_prt_stack_limit
+#else
+#define PRT_STACK_LIMIT STACK_TOTAL
+#endif
 
 // queue entry: O = {o.xyz, bits(slot<<5 | bounce)}, D = {d.xyz, bits(path_key)}, B = {beta.rgb, 0}
 __device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
@@ -99,6 +105,7 @@ __device__ __forceinline__ Best traverse(const SceneView& sc, V3 o, V3 d, int* _
     int cur = sc.root_code;
     for (;;) {
         if (cur >= 0) {
+            if (!PRT_CHECK(cur < sc.n_prims - 1, PRT_CHK_NODE)) break;
             const BvhNode* nd = sc.nodes + cur;
             float4 lmin, lmax, rmin, rmax;
             ldg8(&nd->lmin, lmin, lmax); ldg8(&nd->rmin, rmin, rmax);
@@ -109,7 +116,7 @@ __device__ __forceinline__ Best traverse(const SceneView& sc, V3 o, V3 d, int* _
             if (tl >= 0.0f && tr >= 0.0f) {
                 int nearc = cl, farc = cr;
                 if (tr < tl) { nearc = cr; farc = cl; }
-                if (sp < SS) sstack[sp * WF_THREADS] = farc; else lstack[sp - SS] = farc;
+                if (sp < SS) sstack[sp * WF_THREADS] = farc; else if (PRT_CHECK(sp < PRT_STACK_LIMIT, PRT_CHK_STACK)) lstack[sp - SS] = farc;
                 ++sp;
                 cur = nearc;
                 continue;
@@ -224,7 +231,7 @@ k_extend_pt(SceneView sc, const float4* __restrict__ qo, const float4* __restric
                         cur = any ? nearc : below;
                         sp += push ? 1 : (any ? 0 : -1);
                     } else {                                             // deep stack (rare): spill entries live in local memory
-                        if (push) { lstack[sp - STACK_SMEM] = farc; ++sp; }
+                        if (push) { if (PRT_CHECK(sp < PRT_STACK_LIMIT, PRT_CHK_STACK)) lstack[sp - STACK_SMEM] = farc; ++sp; }
                         if (any) cur = nearc;
                         else { --sp; cur = sp < STACK_SMEM ? st[sp * WF_THREADS] : lstack[sp - STACK_SMEM]; }
                     }
@@ -301,6 +308,7 @@ k_extend_wide(SceneView sc, const float4* __restrict__ qo, const float4* __restr
             const bool nx = inv.x < 0.0f, ny = inv.y < 0.0f, nz = inv.z < 0.0f;
             for (;;) {
                 while (cur >= 0) {
+                    if (!PRT_CHECK(cur < sc.n_prims - 1, PRT_CHK_NODE)) { cur = PRT_DONE; break; }
                     const WideNode* nd = sc.wnodes + cur;
                     float4 a0, a1, b0, b1;
                     ldg8(nd, a0, a1); ldg8(reinterpret_cast<const char*>(nd) + 32, b0, b1);
@@ -351,7 +359,7 @@ k_extend_wide(SceneView sc, const float4* __restrict__ qo, const float4* __restr
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
                             if (key[k] != 0xffffffffu && k != near) {
-                                if (sp < STACK_SMEM) st[sp * WF_THREADS] = cc[k]; else lstack[sp - STACK_SMEM] = cc[k];
+                                if (sp < STACK_SMEM) st[sp * WF_THREADS] = cc[k]; else if (PRT_CHECK(sp < PRT_STACK_LIMIT, PRT_CHK_STACK)) lstack[sp - STACK_SMEM] = cc[k];
                                 ++sp;
                             }
                         if (any) cur = nearc;
@@ -399,6 +407,7 @@ __device__ __forceinline__ Best traverse_wide(const SceneView& sc, V3 o, V3 d, i
     st[0] = PRT_DONE;
     while (cur != PRT_DONE) {
         if (cur >= 0) {
+            if (!PRT_CHECK(cur < sc.n_prims - 1, PRT_CHK_NODE)) break;
             const WideNode* nd = sc.wnodes + cur;
             float4 a0, a1, b0, b1;
             ldg8(nd, a0, a1); ldg8(reinterpret_cast<const char*>(nd) + 32, b0, b1);
@@ -434,7 +443,7 @@ __device__ __forceinline__ Best traverse_wide(const SceneView& sc, V3 o, V3 d, i
 #pragma unroll
             for (int k = 0; k < 4; ++k)
                 if (key[k] != 0xffffffffu && key[k] > kmin) {                         // every hit child but the nearest
-                    if (sp < SS) st[sp * WF_THREADS] = cc[k]; else lstack[sp - SS] = cc[k];
+                    if (sp < SS) st[sp * WF_THREADS] = cc[k]; else if (PRT_CHECK(sp < PRT_STACK_LIMIT, PRT_CHK_STACK)) lstack[sp - SS] = cc[k];
                     ++sp;
                 }
             if (kmin != 0xffffffffu) { cur = nearc; continue; }
@@ -483,6 +492,7 @@ __device__ __forceinline__ V3 clamp_radiance(const SceneView& sc, V3 L) {
 // A path's contribution, written once when the path ends: into the wave's contribution plane (k_resolve sums it into the
 // accumulator in sample order), or - prt_render_fresh with one sample and one wave - straight into the accumulator.
 __device__ __forceinline__ void put_contrib(const SceneView& sc, float4* __restrict__ contrib, uint32_t slot, V3 L) {
+    if (!PRT_CHECK(slot < sc.capacity, PRT_CHK_QUEUE)) return;
     if (sc.direct) { float* a = sc.direct + 3 * (size_t)slot; a[0] = L.x; a[1] = L.y; a[2] = L.z; }
     else st_stream(&contrib[slot], make_float4(L.x, L.y, L.z, 0.f));
 }
@@ -517,7 +527,7 @@ __device__ __forceinline__ bool shade_segment(const SceneView& sc, V3 o, V3 d, u
 }
 
 // Queue compaction: ballot/popc, ONE atomic per warp; every lane of the warp must call this.
-__device__ __forceinline__ void push_compacted(bool cont, uint32_t lane, uint32_t* __restrict__ next_count,
+__device__ __forceinline__ void push_compacted(uint32_t sc_capacity, bool cont, uint32_t lane, uint32_t* __restrict__ next_count,
                                                float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb,
                                                V3 np, V3 ndir, V3 beta, uint32_t slot_bounce, uint32_t key) {
     uint32_t mask = __ballot_sync(0xffffffffu, cont);
@@ -528,6 +538,7 @@ __device__ __forceinline__ void push_compacted(bool cont, uint32_t lane, uint32_
         b0 = __shfl_sync(0xffffffffu, b0, leader);
         if (cont) {
             uint32_t j = b0 + __popc(mask & ((1u << lane) - 1u));
+            if (!PRT_CHECK(j < sc_capacity, PRT_CHK_QUEUE)) return;
             st_stream(&no[j], make_float4(np.x, np.y, np.z, __uint_as_float(slot_bounce)));
             st_stream(&nd[j], make_float4(ndir.x, ndir.y, ndir.z, __uint_as_float(key)));
             st_stream(&nb[j], make_float4(beta.x, beta.y, beta.z, 0.f));
@@ -579,13 +590,13 @@ __device__ __forceinline__ void sq_shade(const SceneView& sc, const float* __res
         if (!cont) put_contrib(sc, contrib, sb >> 5, L);
     }
     if (DEFER) { out->cont = cont; out->np = np; out->ndir = ndir; out->beta = beta; out->sb = sb + 1u; out->key = key; }
-    else push_compacted(cont, lane, next_count, no, nd, nb, np, ndir, beta, sb + 1u, key);
+    else push_compacted(sc.capacity, cont, lane, next_count, no, nd, nb, np, ndir, beta, sb + 1u, key);
 }
 
 // Block-wide compaction: ONE atomic on the queue counter per block and round instead of one per warp. All 256 threads
 // call it the same number of times. (ncu on the staged k_shade: 57 % of the stall samples sat on the per-warp
 // atomicAdd - ~0.6 M same-address atomics per launch at ~2 ns each were the kernel's whole duration.)
-__device__ __forceinline__ void push_block(const ShadeOut& o, uint32_t lane, uint32_t* __restrict__ next_count,
+__device__ __forceinline__ void push_block(uint32_t sc_capacity, const ShadeOut& o, uint32_t lane, uint32_t* __restrict__ next_count,
                                            float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb) {
     __shared__ uint32_t wcnt[WF_WARPS];
     __shared__ uint32_t block_base;
@@ -600,6 +611,7 @@ __device__ __forceinline__ void push_block(const ShadeOut& o, uint32_t lane, uin
     __syncthreads();
     if (o.cont) {
         const uint32_t j = block_base + pre + (uint32_t)__popc(mask & ((1u << lane) - 1u));
+        if (!PRT_CHECK(j < sc_capacity, PRT_CHK_QUEUE)) return;
         st_stream(&no[j], make_float4(o.np.x, o.np.y, o.np.z, __uint_as_float(o.sb)));
         st_stream(&nd[j], make_float4(o.ndir.x, o.ndir.y, o.ndir.z, __uint_as_float(o.key)));
         st_stream(&nb[j], make_float4(o.beta.x, o.beta.y, o.beta.z, 0.f));
@@ -650,11 +662,11 @@ k_shade(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ 
         out.cont = false;
         qn = sq_batch<true>(sc, q, qn, lane, live, xyz(o4), xyz(d4), xyz(b4), __float_as_uint(d4.w), __float_as_uint(o4.w),
                             h.x, __float_as_uint(h.y), h.z, h.w, bounce, max_depth, contrib, &qcount[bounce + 1], no, nd, nb, &out);
-        push_block(out, lane, &qcount[bounce + 1], no, nd, nb);
+        push_block(sc.capacity, out, lane, &qcount[bounce + 1], no, nd, nb);
     }
     out.cont = false;
     if (qn > 0) sq_shade<true>(sc, q, 0, qn, lane, bounce, max_depth, contrib, &qcount[bounce + 1], no, nd, nb, &out);
-    push_block(out, lane, &qcount[bounce + 1], no, nd, nb);
+    push_block(sc.capacity, out, lane, &qcount[bounce + 1], no, nd, nb);
 }
 
 // ------------------------------------------------------------------ fused stages
@@ -882,6 +894,7 @@ SceneView scene_view(const Ctx* c) {
     v.one_bits = 0x3f800000u;
     v.rr_start = c->rr_start; v.clamp = c->firefly_clamp > 0.f ? c->firefly_clamp : INFINITY;
     v.brute = 0;                                          // only wavefront_render's fused path turns it on
+    v.capacity = 0xffffffffu;
     v.direct = nullptr;
     return v;
 }
@@ -939,6 +952,7 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
     cudaStream_t sts[2] = {c->stream, nsets > 1 ? c->stream2 : c->stream};
 
     SceneView sc = scene_view(c);
+    sc.capacity = (uint32_t)(npix_wave * S_wave);                     // slots of one wave's queues and contribution plane
     CamView cam = cam_view(c->cam);
     // fresh = "clear, then render": with ONE sample in ONE wave every pixel of the range gets exactly one contribution, so the
     // paths write it straight into the accumulator (no memset, no contribution plane, no resolve); otherwise clear first
@@ -1227,6 +1241,26 @@ int wavefront_debug_scatter(Ctx* c, const prt_material* mats, const float* in_di
     for (DevBuf* b : {&dm, &di, &dn, &df, &dk, &dout}) dev_free(*b);
     if (e != cudaSuccess) return set_err(c, PRT_ERR_CUDA, std::string("debug_scatter: ") + cudaGetErrorString(e));
     return PRT_OK;
+}
+
+void wavefront_set_stack_limit(int limit) {
+#if PRT_CHECKED
+    limit = limit < STACK_SMEM ? STACK_SMEM : (limit > STACK_TOTAL ? STACK_TOTAL : limit);
+    cudaMemcpyToSymbol(g_prt_stack_limit, &limit, sizeof limit);
+#else
+    (void)limit;
+#endif
+}
+
+unsigned wavefront_check_flags() {
+#if PRT_CHECKED
+    unsigned v = 0, z = 0;
+    cudaMemcpyFromSymbol(&v, g_prt_check_flags, sizeof v);
+    cudaMemcpyToSymbol(g_prt_check_flags, &z, sizeof z);
+    return v;
+#else
+    return 0u;
+#endif
 }
 
 __global__ void k_scale(float* a, size_t n, float s) {

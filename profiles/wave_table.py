@@ -25,7 +25,13 @@ def main(path, extra):
     ix = {h: i for i, h in enumerate(H)}
     print("%-22s" % "kernel" + "".join("%11s" % c[1] for c in COLS))
     tot_ns, tot_b, tot_l2 = 0.0, 0.0, 0.0
+    w_issue = w_lanes = w_t = 0.0                                        # time-weighted means over the captured launches
     for r in rows[2:]:
+        if "smsp__issue_active.avg.pct_of_peak_sustained_active" in ix:
+            d = float(r[ix["gpu__time_duration.sum"]].replace(",", "")) * TO_NS.get(U[ix["gpu__time_duration.sum"]], 1.0)
+            w_t += d
+            w_issue += d * float(r[ix["smsp__issue_active.avg.pct_of_peak_sustained_active"]].replace(",", ""))
+            w_lanes += d * float(r[ix["smsp__thread_inst_executed_per_inst_executed.ratio"]].replace(",", ""))
         if "lts__t_sectors.sum" in ix:                                   # L2-level traffic: every sector the L2 served, 32 B each
             tot_l2 += float(r[ix["lts__t_sectors.sum"]].replace(",", "")) * 32.0
         line = "%-22s" % r[ix["Kernel Name"]].split("(")[0].replace("void ", "").replace("prt::", "")[:22]
@@ -44,11 +50,12 @@ def main(path, extra):
     print("total: %.3f ms (ncu: cold cache, serialised launches), %.1f MB DRAM traffic, %.1f MB L2-level traffic (lts__t_sectors.sum x 32 B)"
           % (tot_ns * 1e-6, tot_b * 1e-6, tot_l2 * 1e-6))
     if extra[:1] == ["--traffic-json"]:
-        wl, waves = extra[1], int(extra[2])
+        wl, waves = extra[1], float(extra[2])
         p = os.path.join(os.path.dirname(os.path.abspath(__file__)), "traffic.json")
         j = json.load(open(p)) if os.path.exists(p) else {}
         j[wl] = {"dram_bytes_per_step": tot_b * waves, "dram_bytes_per_wave": tot_b, "l2_bytes_per_step": tot_l2 * waves,
-                 "source": "profiles/wave_table.py %s: dram__bytes_read.sum+dram__bytes_write.sum over the captured launches of one wave x %d waves per step"
+                 "issue_slot_pct": (w_issue / w_t) if w_t else None, "lanes_per_inst": (w_lanes / w_t) if w_t else None,
+                 "source": "profiles/wave_table.py %s: dram__bytes_read.sum+dram__bytes_write.sum over the captured launches of one wave x %g waves per step; issue-slot %% and lanes/instruction are time-weighted means of the same launches"
                            % (os.path.basename(path), waves)}
         json.dump(j, open(p, "w"), indent=1)
 

@@ -65,6 +65,19 @@ def test_cli_end_to_end(tmp_path):
     rr.close()
 
 
+@pytest.mark.gpu
+def test_cli_build_time_options_take_effect():
+    """--opt is applied BEFORE Init builds the BVH (advisor finding, round 1: build-time options were silently ignored)."""
+    out = {}
+    for opt in ("bvh_builder=1", "bvh_builder=0"):
+        r = subprocess.run([sys.executable, "-m", "parallelraytracing_b200.cli", "--scene", "random_balls_small", "--width", "64",
+                            "--height", "48", "--frames", "2", "--depth", "6", "--opt", opt], cwd=ROOT, capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        out[opt] = json.loads(r.stdout.strip().splitlines()[-1])
+    assert out["bvh_builder=1"]["bvh_builder"] == "ploc" and out["bvh_builder=0"]["bvh_builder"] == "karras"
+    assert out["bvh_builder=1"]["mean_radiance"] == out["bvh_builder=0"]["mean_radiance"]      # the tree never changes the image
+
+
 def test_add_meshes_host_mirror():
     """scene.add_meshes = the host mirror of B200Renderer::AddMesh (SURVEY 8f-2): triangles after the scene's own
     primitives, one new material per mesh, flat unit normals when the mesh has none, offsets applied in fp32."""

@@ -56,6 +56,8 @@ _lib = None
 
 def lib_path():
     """libprt_b200.so, or - PRT_CHECKED=1 in the environment - the bounds-checked build of the same sources."""
+    if os.environ.get("PRT_LIB"):                # an experimental build of the same sources (profiling A/B runs only)
+        return os.environ["PRT_LIB"]
     return os.path.join(HERE, "libprt_b200_checked.so" if os.environ.get("PRT_CHECKED") == "1" else "libprt_b200.so")
 
 
@@ -67,7 +69,7 @@ def load_library():
     p = lib_path()
     from . import build as _build
     checked = os.environ.get("PRT_CHECKED") == "1"
-    if _build.needs_build(checked=checked):        # missing, or built from other sources than the tree holds: never run a stale .so
+    if not os.environ.get("PRT_LIB") and _build.needs_build(checked=checked):        # missing, or built from other sources than the tree holds: never run a stale .so
         try:
             _build.build(checked=checked)
         except Exception as e:  # noqa: BLE001

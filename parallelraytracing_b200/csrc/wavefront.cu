@@ -116,7 +116,7 @@ __device__ __forceinline__ Best traverse(const SceneView& sc, V3 o, V3 d, int* _
             if (tl >= 0.0f && tr >= 0.0f) {
                 int nearc = cl, farc = cr;
                 if (tr < tl) { nearc = cr; farc = cl; }
-                if (sp < SS) sstack[sp * WF_THREADS] = farc; else if (PRT_CHECK(sp < PRT_STACK_LIMIT, PRT_CHK_STACK)) lstack[sp - SS] = farc;
+                if (sp < SS) sstack[sp * WF_THREADS] = farc; else if (PRT_CHECK(sp < PRT_STACK_LIMIT, PRT_CHK_STACK)) lstack[sp - SS] = farc; else --sp;   // checked build: drop the entry, keep the walk consistent
                 ++sp;
                 cur = nearc;
                 continue;
@@ -231,7 +231,7 @@ k_extend_pt(SceneView sc, const float4* __restrict__ qo, const float4* __restric
                         cur = any ? nearc : below;
                         sp += push ? 1 : (any ? 0 : -1);
                     } else {                                             // deep stack (rare): spill entries live in local memory
-                        if (push) { if (PRT_CHECK(sp < PRT_STACK_LIMIT, PRT_CHK_STACK)) lstack[sp - STACK_SMEM] = farc; ++sp; }
+                        if (push && PRT_CHECK(sp < PRT_STACK_LIMIT, PRT_CHK_STACK)) { lstack[sp - STACK_SMEM] = farc; ++sp; }
                         if (any) cur = nearc;
                         else { --sp; cur = sp < STACK_SMEM ? st[sp * WF_THREADS] : lstack[sp - STACK_SMEM]; }
                     }
@@ -268,8 +268,14 @@ k_extend_pt(SceneView sc, const float4* __restrict__ qo, const float4* __restric
 // A is widened by 2^-22 |A| (its two roundings), the quantised box has a 2^-6-step margin (rounding of
 // A - Bp is <= 2^-9 step) and the far side gets the same 1+2^-21 factor as the two-child test. The closest hit
 // does not depend on any of this (order-free (t, prim_id) rule), only the node count does.
+// Resident CTAs per SM the register allocation must allow. Measured (one 16/32-spp wave, Mrays/s): 4 CTAs (63 registers)
+// soup 10 M 1156, dragon 960 K 6656, soup 1 M 1643; 5 CTAs (48 registers, 52 B of spills) 1184 / 6593 / 1525 - more warps
+// only help the scene that misses L2; 6 CTAs (40) 1150 / 6338; 8 CTAs (32) 595 / 5148; 3 CTAs (80 registers) 1020 / 6213.
+#ifndef PRT_EXT_MIN_BLOCKS
+#define PRT_EXT_MIN_BLOCKS 4
+#endif
 template <bool COUNT>
-__global__ void __launch_bounds__(WF_THREADS)
+__global__ void __launch_bounds__(WF_THREADS, PRT_EXT_MIN_BLOCKS)
 k_extend_wide(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ qd, float4* __restrict__ hits,
               const uint32_t* __restrict__ qcount, uint32_t* __restrict__ work, int bounce, int refill,
               unsigned long long* __restrict__ stats) {
@@ -359,7 +365,7 @@ k_extend_wide(SceneView sc, const float4* __restrict__ qo, const float4* __restr
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
                             if (key[k] != 0xffffffffu && k != near) {
-                                if (sp < STACK_SMEM) st[sp * WF_THREADS] = cc[k]; else if (PRT_CHECK(sp < PRT_STACK_LIMIT, PRT_CHK_STACK)) lstack[sp - STACK_SMEM] = cc[k];
+                                if (sp < STACK_SMEM) st[sp * WF_THREADS] = cc[k]; else if (PRT_CHECK(sp < PRT_STACK_LIMIT, PRT_CHK_STACK)) lstack[sp - STACK_SMEM] = cc[k]; else --sp;
                                 ++sp;
                             }
                         if (any) cur = nearc;
@@ -443,7 +449,7 @@ __device__ __forceinline__ Best traverse_wide(const SceneView& sc, V3 o, V3 d, i
 #pragma unroll
             for (int k = 0; k < 4; ++k)
                 if (key[k] != 0xffffffffu && key[k] > kmin) {                         // every hit child but the nearest
-                    if (sp < SS) st[sp * WF_THREADS] = cc[k]; else if (PRT_CHECK(sp < PRT_STACK_LIMIT, PRT_CHK_STACK)) lstack[sp - SS] = cc[k];
+                    if (sp < SS) st[sp * WF_THREADS] = cc[k]; else if (PRT_CHECK(sp < PRT_STACK_LIMIT, PRT_CHK_STACK)) lstack[sp - SS] = cc[k]; else --sp;
                     ++sp;
                 }
             if (kmin != 0xffffffffu) { cur = nearc; continue; }

@@ -619,8 +619,9 @@ def test_reference_cuda_backends_agree(tmp_path):
     """The reference's OWN CUDA backends (cuda_wavefront, cuda_megakernel: compiled unmodified for sm_100 into oracle/_ref by
     `make -C oracle refgpu`) and B200Renderer, behind the same Renderer interface on this GPU. They use cuRAND, so parity
     is statistical: the mean image of 400 spp at 160x90, depth 20, must agree to 1 % (Monte-Carlo error of the mean ~0.2 %).
-    The reference Cornell is left out: its coplanar wall quads (scene.cpp:342-349) make the two reference backends
-    disagree with EACH OTHER by 2 %."""
+    Reference Cornell (coplanar wall quads, scene.cpp:342-349: the two reference backends disagree with EACH OTHER by 2 % over
+    the whole image) is compared over the pixels that are NOT distance ties for the camera ray, the mask coming from the
+    reference's own second-hit distance."""
     import json
     import os
     import subprocess
@@ -628,7 +629,23 @@ def test_reference_cuda_backends_agree(tmp_path):
     if not os.path.exists(exe):
         pytest.skip("oracle/_ref/ref_gpu_driver not built (needs /root/reference at build time)")
     W, H, frames = 160, 90, 400
-    for preset in (int(S.ScenePreset.MATERIAL_TEST), int(S.ScenePreset.DEFAULT), int(S.ScenePreset.RANDOM_BALLS_SMALL)):
+    import oracle_lib
+    ref_cpu = oracle_lib.load_ref()
+    presets = [int(S.ScenePreset.MATERIAL_TEST), int(S.ScenePreset.DEFAULT), int(S.ScenePreset.RANDOM_BALLS_SMALL)]
+    if ref_cpu is not None:
+        presets.append(int(S.ScenePreset.CORNELL))
+    for preset in presets:
+        # Reference CORNELL: pixels whose camera ray sees two of the coplanar wall quads at the same distance (the reference's
+        # own second-hit distance, oracle/_ref) are tie pixels - every backend resolves them its own way - and are masked out
+        keep = np.ones((H, W), bool)
+        if preset == int(S.ScenePreset.CORNELL):
+            cam = S.Camera(width=W, height=H)
+            prim = util.primary_rays(cam, ref_cpu.camera_dirs(cam))
+            hits, second = ref_cpu.preset(preset).trace_batch(prim)
+            with np.errstate(invalid="ignore"):
+                tie = (hits["prim_id"] >= 0) & (np.abs(second - hits["t"]) <= 1e-4 * np.maximum(1.0, hits["t"]))
+            keep = ~tie.reshape(H, W)
+            assert 0.0 < (~keep).mean() < 0.5
         imgs = {}
         for backend in ("wavefront", "megakernel", "b200"):
             out = str(tmp_path / ("%s%d.bin" % (backend, preset)))
@@ -640,7 +657,13 @@ def test_reference_cuda_backends_agree(tmp_path):
             raw = np.fromfile(out, np.float32)
             imgs[backend] = raw[:W * H * 3].reshape(H, W, 3) / frames
         for ref in ("wavefront", "megakernel"):
-            m_ref, m_own = float(imgs[ref].mean()), float(imgs["b200"].mean())
+            m_ref, m_own = float(imgs[ref][keep].mean()), float(imgs["b200"][keep].mean())
+            print("preset %d vs %s: mean %.5f / %.5f (%.2f %%), %.1f %% of pixels masked" % (preset, ref, m_ref, m_own, 100 * (m_own / m_ref - 1), 100 * (~keep).mean()))
+            if preset == int(S.ScenePreset.CORNELL):
+                # measured: -0.85 % vs the reference wavefront, -1.40 % vs its megakernel, which differ by 0.55 % from each other
+                # on the same pixels: SECONDARY rays still meet the coplanar walls (bounded here at 2 %, not hidden)
+                assert abs(m_own - m_ref) <= 0.02 * m_ref, (preset, ref, m_ref, m_own)
+                continue            # block means straddle the masked tie regions
             assert abs(m_own - m_ref) <= 0.01 * m_ref, (preset, ref, m_ref, m_own)
             # coarse structure: 8x8 block means within 10 % + 0.02 absolute on >= 97 % of the blocks
             blk = lambda a: a[:88, :160].reshape(11, 8, 20, 8, 3).mean(axis=(1, 3))

@@ -206,6 +206,12 @@ int  prt_render_fresh(prt_ctx* ctx, int spp, int max_depth, uint64_t seed, int s
  * weight reported by prt_accum_spp unless the range is the whole frame. */
 int  prt_render_region(prt_ctx* ctx, int spp, int max_depth, uint64_t seed, int sample_begin, int pixel_begin, int pixel_count);
 
+/* Make the context's render stream wait (on the device, the host does not block) for a CUDA event of the caller's -
+ * cuda_event is a cudaEvent_t - before anything enqueued afterwards runs. The Renderer shim records such an event behind
+ * Film::AddSampleBufferGPU (which reads the sample buffer on the legacy default stream and returns without waiting,
+ * film.cu:90-99), so that the next ProgressiveRender cannot overwrite the buffer early - without a host synchronisation. */
+int  prt_wait_event(prt_ctx* ctx, void* cuda_event);
+
 /* Zero the accumulation buffer (Film::Clear, film.cu:25-35). */
 int  prt_clear_accum(prt_ctx* ctx);
 
@@ -283,7 +289,7 @@ int  prt_get_stats(prt_ctx* ctx, prt_stats* out);
 
 /* Tuning knobs (all optional): "wave_paths" (paths in flight per wave), "ctas_per_sm", "fused", "fused_max_prims",
  * "brute_max_prims", "persistent", "pt_refill", "pt_refill_wide", "bvh_wide", "wide_min_prims", "bvh_builder", "ploc_radius", "overlap",
- * "stage_timing", "rr_start", "firefly_clamp_milli", "multi_partition", "multi_reduce" (multi-device contexts), and for small waves (one sample per call, the reference's
+ * "stage_timing", "use_graph", "rr_start", "firefly_clamp_milli", "multi_partition", "multi_reduce" (multi-device contexts), and for small waves (one sample per call, the reference's
  * ProgressiveRender granularity) "tail_bounce" (0 = one launch per bounce always), "tail_adaptive", "tail_rays", "tail_rays_staged",
  * "tail_max_paths": bounces from the tail start on run inside one kernel; "sort_rays", "sort_key_bits",
  * "sort_min_rays": re-sort the ray queue of every bounce by origin cell and direction octant (staged pipeline, off). None of them changes the image except

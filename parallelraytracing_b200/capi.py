@@ -46,7 +46,7 @@ class PrtError(RuntimeError):
 
 EXPORTS = [
     "prt_create", "prt_create_multi", "prt_destroy", "prt_last_error", "prt_version", "prt_set_scene", "prt_build_bvh",
-    "prt_set_camera", "prt_render", "prt_render_fresh", "prt_render_region", "prt_clear_accum", "prt_scale_accum", "prt_accum_device_ptr",
+    "prt_set_camera", "prt_render", "prt_render_fresh", "prt_render_region", "prt_wait_event", "prt_clear_accum", "prt_scale_accum", "prt_accum_device_ptr",
     "prt_set_accum_buffer", "prt_read_accum", "prt_accum_spp", "prt_set_accum_spp", "prt_resolve_display", "prt_trace_batch",
     "prt_debug_lbvh", "prt_debug_wide", "prt_debug_scatter", "prt_debug_ploc_trace", "prt_debug_check_flags", "prt_host_alloc", "prt_host_free", "prt_num_prims", "prt_enable_counters", "prt_get_stats", "prt_set_option",
 ]
@@ -88,6 +88,7 @@ def load_library():
     lib.prt_render.argtypes = [vp, i32, i32, u64, i32]
     lib.prt_render_fresh.argtypes = [vp, i32, i32, u64, i32]
     lib.prt_render_region.argtypes = [vp, i32, i32, u64, i32, i32, i32]
+    lib.prt_wait_event.argtypes = [vp, vp]
     lib.prt_clear_accum.argtypes = [vp]
     lib.prt_scale_accum.argtypes = [vp, f32]
     lib.prt_accum_device_ptr.argtypes = [vp]; lib.prt_accum_device_ptr.restype = vp

@@ -376,8 +376,10 @@ void prt_destroy(prt_ctx* ctx) {
                       &c->q2_o[0], &c->q2_o[1], &c->q2_d[0], &c->q2_d[1], &c->q2_b[0], &c->q2_b[1], &c->hits2, &c->contrib2,
                       &c->qcount2, &c->qcount, &c->stats_dev, &c->ray_keys[0][0], &c->ray_keys[0][1], &c->ray_keys[1][0],
                       &c->ray_keys[1][1], &c->ray_vals[0][0], &c->ray_vals[0][1], &c->ray_vals[1][0], &c->ray_vals[1][1],
-                      &c->ray_hist[0], &c->ray_hist[1], &c->ploc_code, &c->ploc_box, &c->ploc_status, &c->ploc_ctl, &c->raw_v, &c->raw_n, &c->raw_m, &c->tri_bounds};
+                      &c->ray_hist[0], &c->ray_hist[1], &c->ploc_code, &c->ploc_box, &c->ploc_status, &c->ploc_ctl, &c->raw_v, &c->raw_n, &c->raw_m, &c->tri_bounds, &c->dyn_dev};
     for (DevBuf* b : bufs) dev_free(*b);
+    wavefront_drop_graphs(c);
+    if (c->dyn_host) cudaFreeHost(c->dyn_host);
     if (c->stats_host) cudaFreeHost(c->stats_host);
     for (int k = 0; k < 2; ++k) { if (c->stage[k]) cudaFreeHost(c->stage[k]); if (c->stage_ev[k]) cudaEventDestroy(c->stage_ev[k]); }
     for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
@@ -402,6 +404,7 @@ int prt_set_scene(prt_ctx* ctx, const prt_sphere* spheres, int n_spheres, const 
         return set_err(c, PRT_ERR_UNSUPPORTED, "prt_set_scene: more than 2^28 primitives");
     PRT_CUDA(c, cudaSetDevice(c->device));
     c->scene_set = false; c->bvh_built = false; c->hint_rays[0] = 0;
+    wavefront_drop_graphs(c);
     int rc;
     // spheres
     std::vector<SphereRec> hs((size_t)n_spheres);
@@ -467,6 +470,7 @@ int prt_build_bvh(prt_ctx* ctx) {
     Ctx* c = &ctx->c;
     if (!c->scene_set) return set_err(c, PRT_ERR_INVALID, "prt_build_bvh: call prt_set_scene first");
     PRT_CUDA(c, cudaSetDevice(c->device));
+    wavefront_drop_graphs(c);
     int rc = lbvh_build(c);
     for (prt_ctx* p : ctx->peers) {                        // every device builds its own BVH (deterministic: identical bits, no broadcast)
         if (rc != PRT_OK) break;
@@ -492,6 +496,7 @@ int prt_set_camera(prt_ctx* ctx, const prt_camera* cam) {
         if (rp != PRT_OK) return set_err(c, rp, p->c.err);
     }
     PRT_CUDA(c, cudaSetDevice(c->device));
+    wavefront_drop_graphs(c);
     c->cam = *cam;
     c->cam_set = true;
     if (resized) {
@@ -552,6 +557,14 @@ int prt_render_region(prt_ctx* ctx, int spp, int max_depth, uint64_t seed, int s
     return rc;
 }
 
+int prt_wait_event(prt_ctx* ctx, void* cuda_event) {
+    if (!ctx || !cuda_event) return set_err(ctx ? &ctx->c : nullptr, PRT_ERR_INVALID, "prt_wait_event: NULL argument");
+    Ctx* c = &ctx->c;
+    PRT_CUDA(c, cudaSetDevice(c->device));
+    PRT_CUDA(c, cudaStreamWaitEvent(c->stream, (cudaEvent_t)cuda_event, 0));
+    return PRT_OK;
+}
+
 int prt_clear_accum(prt_ctx* ctx) {
     if (!ctx) return set_err(nullptr, PRT_ERR_INVALID, "prt_clear_accum: ctx is NULL");
     Ctx* c = &ctx->c;
@@ -577,6 +590,7 @@ int prt_set_accum_buffer(prt_ctx* ctx, float* device_rgb) {
     if (!ctx) return set_err(nullptr, PRT_ERR_INVALID, "prt_set_accum_buffer: ctx is NULL");
     Ctx* c = &ctx->c;
     if (!c->cam_set) return set_err(c, PRT_ERR_INVALID, "prt_set_accum_buffer: call prt_set_camera first");
+    cudaSetDevice(c->device); wavefront_drop_graphs(c);
     if (device_rgb) { c->accum = device_rgb; c->accum_external = true; }
     else { c->accum = (float*)c->accum_own.p; c->accum_external = false; }
     c->accum_spp = 0;
@@ -703,6 +717,7 @@ int prt_enable_counters(prt_ctx* ctx, int on) {
     if (!ctx) return set_err(nullptr, PRT_ERR_INVALID, "prt_enable_counters: ctx is NULL");
     ctx->c.counters_on = on ? 1 : 0;
     for (prt_ctx* p : ctx->peers) p->c.counters_on = on ? 1 : 0;
+    // (the graph key holds the counter switch: no invalidation needed)
     return PRT_OK;
 }
 
@@ -734,6 +749,8 @@ int prt_set_option(prt_ctx* ctx, const char* key, int64_t value) {
         int rp = prt_set_option(p, key, value);
         if (rp != PRT_OK) return set_err(c, rp, p->c.err);
     }
+    cudaSetDevice(c->device); wavefront_drop_graphs(c);               // any option may change what a call enqueues
+    if (!strcmp(key, "use_graph")) { c->use_graph = value ? 1 : 0; return PRT_OK; }
     if (!strcmp(key, "wave_paths")) { if (value < 0) return set_err(c, PRT_ERR_INVALID, "wave_paths < 0"); c->wave_paths_opt = value; }
     else if (!strcmp(key, "ctas_per_sm")) { if (value < 1 || value > 32) return set_err(c, PRT_ERR_INVALID, "ctas_per_sm out of range"); c->ctas_per_sm = (int)value; }
     else if (!strcmp(key, "tail_bounce")) c->tail_bounce = value < 0 ? 0 : value;

@@ -14,6 +14,16 @@ struct DevBuf {
     void* p = nullptr; size_t bytes = 0;
 };
 
+// One captured 1-spp call (wavefront_render): everything the enqueue depends on except the first sample index and the seed.
+struct GraphKey {
+    uint64_t gen; int64_t pixel_begin, pixels; int max_depth, tail_b, counters; void* accum;
+    bool operator==(const GraphKey& o) const {
+        return gen == o.gen && pixel_begin == o.pixel_begin && pixels == o.pixels && max_depth == o.max_depth && tail_b == o.tail_b &&
+               counters == o.counters && accum == o.accum;
+    }
+};
+struct GraphEntry { GraphKey key; cudaGraphExec_t exec; int launches; };
+
 struct Ctx {
     int device = 0;
     int num_sms = 148;
@@ -102,6 +112,11 @@ struct Ctx {
     int rr_start = -1;                          // estimator options, both OFF by default so that parity with the
     float firefly_clamp = 0.f;                  // reference's estimator stays checkable: Russian roulette / radiance clamp
     int stage_timing = 1;                       // CUDA-event pairs around the hot kernels
+    int use_graph = 1;                          // one-sample calls replay a captured CUDA graph (option "use_graph")
+    uint64_t graph_gen = 0;                     // bumped by everything that changes what a call enqueues (scene, BVH, camera, options, buffers)
+    std::vector<GraphEntry> graphs;
+    uint32_t* dyn_host = nullptr;               // pinned {first sample, seed_lo, seed_hi}: read by a memcpy node at replay time
+    DevBuf dyn_dev;
     std::vector<cudaEvent_t> ev_pool;
     std::vector<std::pair<size_t, int>> pend_spans;   // a render that is enqueued but not finished yet (wavefront_finish)
     int pend_launches = 0; uint64_t pend_paths = 0; bool pend_active = false;
@@ -130,6 +145,7 @@ int sort_ray_queue(Ctx* c, cudaStream_t st, int set, int64_t capacity, const uin
 int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_begin, int64_t pixel_begin, int64_t pixel_count, bool fresh = false,
                      bool defer_finish = false);
 int wavefront_finish(Ctx* c);
+void wavefront_drop_graphs(Ctx* c);     // forget every captured call (anything it depends on changed)
 unsigned wavefront_check_flags();            // checked builds (-DPRT_CHECKED=1): violated-index bits since the last call, 0 otherwise
 unsigned lbvh_check_flags();
 void wavefront_set_stack_limit(int limit);

@@ -52,7 +52,9 @@ __device__ __forceinline__ void st_stream(float4* p, float4 v) { __stcs(p, v); }
 // ------------------------------------------------------------------ raygen
 __global__ void __launch_bounds__(WF_THREADS)
 k_raygen(CamView cam, int pix0, int npix, FastDiv div_npix, int n_paths, uint32_t sample0, uint32_t seed_lo, uint32_t seed_hi,
-         float4* __restrict__ qo, float4* __restrict__ qd, float4* __restrict__ qb, uint32_t* __restrict__ qcount) {
+         float4* __restrict__ qo, float4* __restrict__ qd, float4* __restrict__ qb, uint32_t* __restrict__ qcount,
+         const uint32_t* __restrict__ dyn = nullptr) {
+    if (dyn) { sample0 = dyn[0]; seed_lo = dyn[1]; seed_hi = dyn[2]; }     // CUDA-graph replay: the per-call values live in memory
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i == 0) qcount[0] = (uint32_t)n_paths;
     if (i >= n_paths) return;
@@ -686,9 +688,10 @@ template <bool COUNT, bool BRUTE>
 __global__ void __launch_bounds__(WF_THREADS)
 k_primary(SceneView sc, CamView cam, int pix0, int npix, FastDiv div_npix, int n_paths, uint32_t sample0, uint32_t seed_lo, uint32_t seed_hi,
           float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb, float4* __restrict__ contrib,
-          uint32_t* __restrict__ qcount, int max_depth, unsigned long long* __restrict__ stats) {
+          uint32_t* __restrict__ qcount, int max_depth, unsigned long long* __restrict__ stats, const uint32_t* __restrict__ dyn = nullptr) {
     __shared__ int sstack[BRUTE ? 1 : FUSED_STACK * WF_THREADS];
     __shared__ float sq[WF_WARPS * SQ_FLOATS];
+    if (dyn) { sample0 = dyn[0]; seed_lo = dyn[1]; seed_hi = dyn[2]; }     // CUDA-graph replay: the per-call values live in memory
     float* q = sq + (threadIdx.x >> 5) * SQ_FLOATS;
     const uint32_t count = (uint32_t)n_paths;
     const uint32_t lane = threadIdx.x & 31u;
@@ -971,7 +974,7 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
     const int grid_p = c->num_sms * c->ctas_per_sm;
     const uint32_t seed_lo = (uint32_t)seed, seed_hi = (uint32_t)(seed >> 32);
     const bool fused = c->fused < 0 ? (c->n_prims <= c->fused_max_prims) : (c->fused != 0);
-    const bool timing = c->stage_timing != 0;
+    const bool timing_opt = c->stage_timing != 0;
     const bool wide = sc.wnodes != nullptr && c->n_prims > 1;          // staged extend walks the 4-wide quantised nodes
     auto k_ext = wide ? (c->counters_on ? k_extend_wide<true> : k_extend_wide<false>)
                       : (c->counters_on ? k_extend_pt<true> : k_extend_pt<false>);
@@ -992,8 +995,55 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
         return ev_used++;
     };
 
+    // ---- the reference's call pattern: ONE sample per call (main.cpp:513). Such a call is 3-20 short launches + two memsets +
+    // the counter read-back; issued one by one they cost 26 us of host time against 155 us of device time (Cornell 1080p).
+    // The whole enqueue is captured ONCE into a CUDA graph per (scene, camera, depth, tail start) and replayed with one
+    // cudaGraphLaunch; what changes per call (first sample index, seed) reaches k_primary / k_raygen through three words that
+    // a memcpy node of the graph copies from pinned host memory at replay time.
+    if (!c->stats_host) PRT_CUDA(c, cudaHostAlloc((void**)&c->stats_host, (PRT_MAX_DEPTH + 4) * 8, cudaHostAllocDefault));
+    const bool use_graph = direct && c->use_graph && !c->sort_rays;
+    const uint32_t* dyn = nullptr;
+    bool capturing = false;
+    GraphKey gkey{};
+    if (use_graph) {
+        if (!c->dyn_host) PRT_CUDA(c, cudaHostAlloc((void**)&c->dyn_host, 16, cudaHostAllocDefault));
+        if ((rc = dev_reserve(c, c->dyn_dev, 16))) return rc;
+        c->dyn_host[0] = (uint32_t)sample_begin; c->dyn_host[1] = seed_lo; c->dyn_host[2] = seed_hi;
+        int tb = (c->tail_bounce > 0 && P <= c->tail_max_paths) ? c->tail_bounce : max_depth;        // same rule as in the wave loop
+        if (tb < max_depth && c->tail_adaptive) {
+            const unsigned long long h0 = c->hint_rays[0];
+            tb = max_depth;
+            for (int b = 1; b < max_depth; ++b) {
+                const double expect = h0 ? (double)P * (double)c->hint_rays[b] / (double)h0 : (double)P;
+                if (expect <= (double)(fused ? c->tail_rays : c->tail_rays_staged)) { tb = b; break; }
+            }
+        }
+        gkey = GraphKey{c->graph_gen, pixel_begin, P, max_depth, tb, c->counters_on, (void*)c->accum};
+        for (GraphEntry& g : c->graphs)
+            if (g.key == gkey) {                                      // replay
+                PRT_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+                PRT_CUDA(c, cudaGraphLaunch(g.exec, c->stream));
+                PRT_CUDA(c, cudaEventRecord(c->ev1, c->stream));
+                spans.clear();
+                c->pend_launches = g.launches; c->pend_paths = (uint64_t)P; c->pend_active = true;
+                c->accum_spp = spp;
+                if (defer_finish) return PRT_OK;
+                return wavefront_finish(c);
+            }
+        PRT_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+        PRT_CUDA(c, cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+        capturing = true;
+        dyn = (const uint32_t*)c->dyn_dev.p;
+    }
+    struct CaptureGuard {                                             // an error return below must not leave the stream capturing
+        Ctx* c; bool* on;
+        ~CaptureGuard() { if (*on) { cudaGraph_t g = nullptr; cudaStreamEndCapture(c->stream, &g); if (g) cudaGraphDestroy(g); } }
+    } guard{c, &capturing};
+    if (capturing) PRT_CUDA(c, cudaMemcpyAsync(c->dyn_dev.p, c->dyn_host, 12, cudaMemcpyHostToDevice, c->stream));
+    const bool timing = timing_opt && !capturing && !(direct && n_waves == 1);   // event pairs per kernel: measurable at one sample per call
+
     PRT_CUDA(c, cudaMemsetAsync(dstats, 0, (PRT_MAX_DEPTH + 4) * 8, c->stream));
-    PRT_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    if (!capturing) PRT_CUDA(c, cudaEventRecord(c->ev0, c->stream));
     if (nsets > 1) PRT_CUDA(c, cudaStreamWaitEvent(c->stream2, c->ev0, 0));
     int launches = 0;
     uint64_t paths = 0;
@@ -1031,7 +1081,7 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
                     auto kp = c->counters_on ? (brute ? k_primary<true, true> : k_primary<true, false>)
                                              : (brute ? k_primary<false, true> : k_primary<false, false>);
                     kp<<<grid, WF_THREADS, 0, st>>>(sc, cam, (int)p0, npix, div_npix, n_paths, (uint32_t)(sample_begin + s0), seed_lo,
-                                                    seed_hi, qo[1], qd[1], qb[1], contrib, qcount, max_depth, dstats);
+                                                    seed_hi, qo[1], qd[1], qb[1], contrib, qcount, max_depth, dstats, dyn);
                 }
                 if (timing) stamp(st);
                 ++launches;
@@ -1050,7 +1100,7 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
                 }
             } else {
                 k_raygen<<<(n_paths + WF_THREADS - 1) / WF_THREADS, WF_THREADS, 0, st>>>(
-                    cam, (int)p0, npix, div_npix, n_paths, (uint32_t)(sample_begin + s0), seed_lo, seed_hi, qo[0], qd[0], qb[0], qcount);
+                    cam, (int)p0, npix, div_npix, n_paths, (uint32_t)(sample_begin + s0), seed_lo, seed_hi, qo[0], qd[0], qb[0], qcount, dyn);
                 ++launches;
                 for (int b = 0; b < std::min(max_depth, tail_b); ++b) {
                     if (timing) spans.push_back({stamp(st), b == 0 ? 2 : 0});
@@ -1101,10 +1151,22 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
         PRT_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_join, 0));
     }
     cudaStream_t st = c->stream;
-    PRT_CUDA(c, cudaEventRecord(c->ev1, st));
+    if (!capturing) PRT_CUDA(c, cudaEventRecord(c->ev1, st));
     // counters come back through pinned memory behind the last kernel: one host wake-up per call, not two
-    if (!c->stats_host) PRT_CUDA(c, cudaHostAlloc((void**)&c->stats_host, (PRT_MAX_DEPTH + 4) * 8, cudaHostAllocDefault));
     PRT_CUDA(c, cudaMemcpyAsync(c->stats_host, dstats, (PRT_MAX_DEPTH + 4) * 8, cudaMemcpyDeviceToHost, st));
+    if (capturing) {
+        cudaGraph_t g = nullptr;
+        capturing = false;
+        PRT_CUDA(c, cudaStreamEndCapture(st, &g));
+        cudaGraphExec_t exec = nullptr;
+        cudaError_t e = cudaGraphInstantiate(&exec, g, 0);
+        cudaGraphDestroy(g);
+        if (e != cudaSuccess) return set_err(c, PRT_ERR_CUDA, std::string("cudaGraphInstantiate: ") + cudaGetErrorString(e));
+        if (c->graphs.size() >= 4) { cudaGraphExecDestroy(c->graphs.front().exec); c->graphs.erase(c->graphs.begin()); }   // tail starts flip between neighbours
+        c->graphs.push_back(GraphEntry{gkey, exec, launches});
+        PRT_CUDA(c, cudaGraphLaunch(exec, st));
+        PRT_CUDA(c, cudaEventRecord(c->ev1, st));
+    }
     c->pend_launches = launches; c->pend_paths = paths; c->pend_active = true;
     c->accum_spp = (fresh ? 0 : c->accum_spp) + spp;
     if (defer_finish) return PRT_OK;         // multi-device: the caller enqueues the reduce behind this, then finishes every device
@@ -1143,6 +1205,12 @@ int wavefront_finish(Ctx* c) {
     s.extend_ms = ms[0] + ms[2]; s.shade_ms = ms[1]; s.primary_ms = ms[2]; s.primary_launches = n_primary;
     s.n_prims = c->n_prims; s.n_nodes = c->n_prims > 1 ? c->n_prims - 1 : 0;
     return PRT_OK;
+}
+
+void wavefront_drop_graphs(Ctx* c) {
+    for (GraphEntry& g : c->graphs) cudaGraphExecDestroy(g.exec);
+    c->graphs.clear();
+    ++c->graph_gen;
 }
 
 int wavefront_trace_batch(Ctx* c, const prt_ray* rays, int n, prt_hit* out, int use_bvh) {

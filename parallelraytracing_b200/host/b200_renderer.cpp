@@ -6,7 +6,7 @@
 #include <cstdio>
 #include <cuda_runtime_api.h>
 
-B200Renderer::~B200Renderer() { prt_destroy(m_Ctx); }
+B200Renderer::~B200Renderer() { prt_destroy(m_Ctx); if (m_FilmDone) cudaEventDestroy((cudaEvent_t)m_FilmDone); }
 
 void B200Renderer::Init(Film& film, const Scene& scene, const Camera& camera)
 {
@@ -53,8 +53,9 @@ void B200Renderer::ProgressiveRender()
     if (m_Film->GetWidth() != (uint32_t)m_Camera->GetWidth() || m_Film->GetHeight() != (uint32_t)m_Camera->GetHeight()) return;
     const int k = m_SamplesPerCall;
     // Film::AddSampleBufferGPU of the previous frame ran on the legacy default stream and returned without waiting
-    // (film.cu:90-99); the context's streams are non-blocking, so the sample buffer must not be rewritten before it is read
-    cudaStreamSynchronize(cudaStreamLegacy);
+    // (film.cu:90-99); the context's streams are non-blocking, so the sample buffer must not be rewritten before it is read:
+    // the render stream waits ON THE DEVICE for the event recorded behind that kernel (no host synchronisation)
+    if (m_FilmDone) prt_wait_event(m_Ctx, m_FilmDone);
     if (prt_render_fresh(m_Ctx, k, m_Depth, m_Seed, m_NextSample) != PRT_OK) {          // clear + render; 1 spp writes the buffer directly
         std::fprintf(stderr, "[B200Renderer] %s\n", prt_last_error(m_Ctx));
         return;
@@ -62,4 +63,6 @@ void B200Renderer::ProgressiveRender()
     m_NextSample += k;
     if (k > 1) prt_scale_accum(m_Ctx, 1.0f / (float)k);    // Film adds rgb*weight: hand it the mean with weight k
     m_Film->AddSampleBufferGPU(prt_accum_device_ptr(m_Ctx), (float)k);   // film.cu:90-99
+    if (!m_FilmDone) cudaEventCreateWithFlags((cudaEvent_t*)&m_FilmDone, cudaEventDisableTiming);
+    if (m_FilmDone) cudaEventRecord((cudaEvent_t)m_FilmDone, cudaStreamLegacy);
 }

@@ -41,6 +41,7 @@ private:
     const Camera* m_Camera = nullptr;
     prt_ctx* m_Ctx = nullptr;
     bool m_Ok = false;
+    void* m_FilmDone = nullptr;    // cudaEvent_t recorded behind Film::AddSampleBufferGPU on the legacy stream
     int m_Device = 0;
     std::vector<int> m_Devices;    // empty: one device (m_Device)
     int m_Depth = 20;              // m_Depth of the reference backends

@@ -498,6 +498,25 @@ def result_json(args, R):
     return out
 
 
+def fast_math_parity(name, spp=8):
+    """Per-pixel metrics of fast_math=1 against the bit-exact mode on the workload's own frame (same seed, `spp` samples)."""
+    from parallelraytracing_b200.capi import Context
+    sd, cam, w = make_workload(name)
+    imgs = []
+    with Context(int(os.environ.get("LOCAL_RANK", "0"))) as c:
+        c.set_scene(sd); c.build_bvh(); c.set_camera(cam)
+        for fast in (0, 1):
+            c.set_option("fast_math", fast)
+            c.clear_accum(); c.render(spp, w["depth"], seed=4242)
+            imgs.append(c.read_accum().astype(np.float64) / spp)
+    d = np.abs(imgs[0] - imgs[1])
+    rel = d / np.maximum(np.abs(imgs[0]), 1e-3)
+    flip = rel.max(-1) > 1e-2
+    return {"spp": spp, "rmse": float(np.sqrt((d ** 2).mean())), "rmse_nonflip": float(np.sqrt((d[~flip] ** 2).mean())),
+            "max_rel_nonflip": float(rel[~flip].max()), "flip_pixels": int(flip.sum()), "pixels": int(flip.size),
+            "tolerance": "north star: per-pixel RMSE <= 1e-3, max relative error <= 1e-2 (flips = pixels where a path took another discrete decision)"}
+
+
 def emit(line, fd):
     os.write(fd, (line + "\n").encode())
 
@@ -569,6 +588,14 @@ def main():
             dist.barrier(group=gloo)
         if rank == 0:
             out["workloads"] = extra
+    if default_run and world == 1 and not args.no_extra:
+        # tolerance-mode float math (option fast_math, default off): the same workload, and its parity against the bit-exact mode
+        import copy
+        a2 = copy.copy(args); a2.opt = list(args.opt) + ["fast_math=1"]
+        fm = measure(a2, args.workload, max(1, min(args.steps, args.extra_steps)), 3)
+        out["fast_math"] = {"value": fm["value"], "unit": "Mrays/s", "ms_per_step": fm["ms_per_step"], "e2e": fm["e2e"]["value"],
+                            "speedup_vs_exact": fm["value"] / out["value"], "parity_vs_exact": fast_math_parity(args.workload),
+                            "what": "SFU approximations for divide / sqrt / rsqrt on the shading side only; hit ids unchanged; default OFF"}
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
             arm = CpuArm(args.workload)

@@ -751,6 +751,7 @@ int prt_set_option(prt_ctx* ctx, const char* key, int64_t value) {
     }
     cudaSetDevice(c->device); wavefront_drop_graphs(c);               // any option may change what a call enqueues
     if (!strcmp(key, "use_graph")) { c->use_graph = value ? 1 : 0; return PRT_OK; }
+    if (!strcmp(key, "fast_math")) { c->fast_math = value ? 1 : 0; return PRT_OK; }
     if (!strcmp(key, "wave_paths")) { if (value < 0) return set_err(c, PRT_ERR_INVALID, "wave_paths < 0"); c->wave_paths_opt = value; }
     else if (!strcmp(key, "ctas_per_sm")) { if (value < 1 || value > 32) return set_err(c, PRT_ERR_INVALID, "ctas_per_sm out of range"); c->ctas_per_sm = (int)value; }
     else if (!strcmp(key, "tail_bounce")) c->tail_bounce = value < 0 ? 0 : value;

@@ -58,6 +58,20 @@ PRT_DEV V3 cross(V3 a, V3 b) {
 PRT_DEV V3 normalize(V3 v) { float s = 1.0f / sqrtf(dot(v, v)); return v * s; }
 PRT_DEV V3 xyz(float4 f) { return mk(f.x, f.y, f.z); }
 
+// ------------------------------------------------------------------ tolerance-mode float math (option fast_math)
+// The default (FAST = false) is the bit-exact contract above: IEEE divide and square root in the oracle's operation order.
+// FAST = true replaces them ON THE SHADING SIDE ONLY - camera ray, surface normal, the four materials, the rejection-sampled
+// unit vector - by the SFU approximations (MUFU.RCP / RSQ / SQRT, <= 2 ulp, one instruction instead of a 6-10 instruction
+// refinement sequence). Intersection and traversal stay exact, so closest-hit ids, t and every integer output are unchanged;
+// radiance moves within the tolerance the north star states (per-pixel RMSE <= 1e-3, max relative error <= 1e-2; measured and
+// asserted in tests/test_gpu_parity.py::test_fast_math_mode).
+PRT_DEV float fast_rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+PRT_DEV float fast_rsqrt(float x) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+PRT_DEV float fast_sqrt(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+template <bool FAST> PRT_DEV float div_t(float a, float b) { if (FAST) return a * fast_rcp(b); return a / b; }
+template <bool FAST> PRT_DEV float sqrt_t(float x) { if (FAST) return fast_sqrt(x); return sqrtf(x); }
+template <bool FAST> PRT_DEV V3 normalize_t(V3 v) { if (FAST) return v * fast_rsqrt(dot(v, v)); return normalize(v); }
+
 // ------------------------------------------------------------------ exact division by a launch constant
 // floor(n / d) for n < 2^31 as one 32x32->64 multiply and a shift (Granlund & Montgomery 1994,
 // m = ceil(2^(31+L) / d), L = ceil(log2 d)); replaces the ~25-instruction integer division.
@@ -106,6 +120,7 @@ PRT_DEV float rng_pm1(Rng& r) {
     return fmaf(__int2float_rn((int)rng_next31(r)), 9.31322574615478515625e-10f, -1.0f);
 }
 // RandomUnitVector: rejection in the cube (math.h:26-36)
+template <bool FAST = false>
 PRT_DEV V3 rng_unit_vector(Rng& r) {
     for (;;) {
         float x = rng_pm1(r);
@@ -114,6 +129,7 @@ PRT_DEV V3 rng_unit_vector(Rng& r) {
         V3 p = mk(x, y, z);
         float l2 = dot(p, p);
         if (1e-8f < l2 && l2 <= 1.0f) {
+            if (FAST) return p * fast_rsqrt(l2);
             float l = sqrtf(l2);
             return mk(p.x / l, p.y / l, p.z / l);
         }
@@ -318,6 +334,7 @@ PRT_DEV void test_leaf(const SceneView& sc, uint32_t code, V3 o, V3 d, V3 dn, co
 struct Surface { V3 p; V3 n; bool front; int mat; };
 
 // Rebuild SurfaceInteraction{Position, Normal, IsFrontFace, Material} for a hit record.
+template <bool FAST = false>
 PRT_DEV Surface make_surface(const SceneView& sc, V3 o, V3 d, float t, uint32_t code, float u, float v) {
     Surface s;
     uint32_t type = PRT_LEAF_TYPE(code), idx = PRT_LEAF_INDEX(code);
@@ -332,18 +349,18 @@ PRT_DEV Surface make_surface(const SceneView& sc, V3 o, V3 d, float t, uint32_t 
         s.p = (xyz(a) * b0 + xyz(b) * u) + xyz(c) * v;
         V3 n = (xyz(na) * b0 + xyz(nb) * u) + xyz(nc) * v;
         if (dot(n, d) > 0.0f) { n = neg(n); s.front = false; } else s.front = true;   // shape.h:294-302
-        s.n = normalize(n);                             // TransformNormal, primitive.cpp:39
+        s.n = normalize_t<FAST>(n);                     // TransformNormal, primitive.cpp:39
         s.mat = __float_as_int(b.w);
     } else if (type == 0u) {
         float4 a = __ldg(&sc.spheres[idx].a);
         float4 b = __ldg(&sc.spheres[idx].b);
         // local hit point l + dn*t, normal = normalize(local point) (shape.h:194-199), then
         // Position = Mat*p' = p' + c and TransformNormal normalises once more (primitive.cpp:38-39)
-        V3 pl = (o - xyz(a)) + normalize(d) * t;
-        V3 n = normalize(pl);
+        V3 pl = (o - xyz(a)) + normalize_t<FAST>(d) * t;
+        V3 n = normalize_t<FAST>(pl);
         s.front = u != 0.0f;
         if (!s.front) n = neg(n);
-        s.n = normalize(n);
+        s.n = normalize_t<FAST>(n);
         s.p = pl + xyz(a);
         s.mat = __float_as_int(b.y);
     } else {
@@ -362,31 +379,32 @@ PRT_DEV V3 reflect(V3 i, V3 n) { float k = dot(n, i); return i - (n * k) * 2.0f;
 // MaterialHandle::{Emit,Scatter} (material.h:139-161). Returns true when the path
 // continues with direction out_d (already passed through Ray::Normalize as
 // cpu/renderer.cpp:84 does) and throughput factor atten; emit = Le of the surface.
+template <bool FAST = false>
 PRT_DEV bool scatter(const MatRec& m, V3 d, const Surface& s, Rng& rng, V3& atten, V3& out_d, V3& emit) {
     int type = __float_as_int(m.b.x);
     emit = mk(0.f, 0.f, 0.f);
     V3 dir;
     if (type == 1) {                                    // Lambertian, material.h:16-31
-        V3 ruv = rng_unit_vector(rng);
+        V3 ruv = rng_unit_vector<FAST>(rng);
         dir = s.n + ruv;
         if (fabsf(dir.x) < 1e-8f && fabsf(dir.y) < 1e-8f && fabsf(dir.z) < 1e-8f) dir = s.n;
-        dir = normalize(dir);
+        dir = normalize_t<FAST>(dir);
         atten = mk(m.a.x, m.a.y, m.a.z);
     } else if (type == 2) {                             // Metal, material.h:48-57
-        V3 r = normalize(reflect(d, s.n));
-        V3 ruv = rng_unit_vector(rng);
+        V3 r = normalize_t<FAST>(reflect(d, s.n));
+        V3 ruv = rng_unit_vector<FAST>(rng);
         r = r + ruv * m.a.w;
-        dir = normalize(r);
+        dir = normalize_t<FAST>(r);
         atten = mk(m.a.x, m.a.y, m.a.z);
         if (!(dot(dir, s.n) > 0.0f)) return false;
     } else if (type == 3) {                             // Dielectric, material.h:76-95
         atten = mk(1.f, 1.f, 1.f);
         float ior = m.a.w;
-        float ri = s.front ? (1.0f / ior) : ior;
+        float ri = s.front ? div_t<FAST>(1.0f, ior) : ior;
         float cos_t = fminf(dot(neg(d), s.n), 1.0f);
-        float sin_t = sqrtf(1.0f - cos_t * cos_t);
+        float sin_t = sqrt_t<FAST>(1.0f - cos_t * cos_t);
         bool cannot = ri * sin_t > 1.0f;
-        float r0 = (1.0f - ri) / (1.0f + ri);
+        float r0 = div_t<FAST>(1.0f - ri, 1.0f + ri);
         r0 = r0 * r0;
         float x = 1.0f - cos_t;
         float x5 = ((x * x) * (x * x)) * x;             // pow(1-cos, 5)
@@ -398,25 +416,26 @@ PRT_DEV bool scatter(const MatRec& m, V3 d, const Surface& s, Rng& rng, V3& atte
         else {                                          // "Reflect" = refract, math.h:45-50
             float c2 = fminf(dot(neg(d), s.n), 1.0f);
             V3 perp = (d + s.n * c2) * ri;
-            float k = -sqrtf(fabsf(1.0f - dot(perp, perp)));
+            float k = -sqrt_t<FAST>(fabsf(1.0f - dot(perp, perp)));
             dir = perp + s.n * k;
         }
     } else {                                            // Emissive / invalid: path ends
         if (type == 4) emit = mk(m.a.x, m.a.y, m.a.z);
         return false;
     }
-    out_d = normalize(dir);                             // scatteredRay.Normalize(), cpu/renderer.cpp:84
+    out_d = normalize_t<FAST>(dir);                             // scatteredRay.Normalize(), cpu/renderer.cpp:84
     return true;
 }
 
 // Camera::GetCameraRay (camera.h:104-132)
 struct CamView { V3 pos, front, right, up; float tan_half, aspect, w, h; int W, H; FastDiv divW; };
+template <bool FAST = false>
 PRT_DEV V3 camera_dir(const CamView& c, float px, float py) {
-    float ndc_x = (px / c.w) * 2.0f - 1.0f;
-    float ndc_y = 1.0f - (py / c.h) * 2.0f;
-    V3 dc = normalize(mk(ndc_x * c.aspect * c.tan_half, ndc_y * c.tan_half, -1.0f));
+    float ndc_x = div_t<FAST>(px, c.w) * 2.0f - 1.0f;
+    float ndc_y = 1.0f - div_t<FAST>(py, c.h) * 2.0f;
+    V3 dc = normalize_t<FAST>(mk(ndc_x * c.aspect * c.tan_half, ndc_y * c.tan_half, -1.0f));
     V3 w = (c.right * dc.x + c.up * dc.y) + neg(c.front) * dc.z;
-    return normalize(w);
+    return normalize_t<FAST>(w);
 }
 
 }  // namespace prt

@@ -112,6 +112,7 @@ struct Ctx {
     int rr_start = -1;                          // estimator options, both OFF by default so that parity with the
     float firefly_clamp = 0.f;                  // reference's estimator stays checkable: Russian roulette / radiance clamp
     int stage_timing = 1;                       // CUDA-event pairs around the hot kernels
+    int fast_math = 0;                          // option: SFU approximations for divide / sqrt / rsqrt on the SHADING side (default: bit-exact IEEE)
     int use_graph = 1;                          // one-sample calls replay a captured CUDA graph (option "use_graph")
     uint64_t graph_gen = 0;                     // bumped by everything that changes what a call enqueues (scene, BVH, camera, options, buffers)
     std::vector<GraphEntry> graphs;

@@ -50,6 +50,7 @@ __device__ __forceinline__ float4 ld_stream(const float4* p) { return __ldcs(p);
 __device__ __forceinline__ void st_stream(float4* p, float4 v) { __stcs(p, v); }
 
 // ------------------------------------------------------------------ raygen
+template <bool FAST>
 __global__ void __launch_bounds__(WF_THREADS)
 k_raygen(CamView cam, int pix0, int npix, FastDiv div_npix, int n_paths, uint32_t sample0, uint32_t seed_lo, uint32_t seed_hi,
          float4* __restrict__ qo, float4* __restrict__ qd, float4* __restrict__ qb, uint32_t* __restrict__ qcount,
@@ -61,7 +62,7 @@ k_raygen(CamView cam, int pix0, int npix, FastDiv div_npix, int n_paths, uint32_
     int s_local = (int)fdiv((uint32_t)i, div_npix);
     int pixel = pix0 + (i - s_local * npix);
     int y = (int)fdiv((uint32_t)pixel, cam.divW), x = pixel - y * cam.W;
-    V3 d = camera_dir(cam, (float)x + 0.5f, (float)y + 0.5f);     // pixel centre, cpu/renderer.cpp:45
+    V3 d = camera_dir<FAST>(cam, (float)x + 0.5f, (float)y + 0.5f);     // pixel centre, cpu/renderer.cpp:45
     uint32_t key = path_key(seed_lo, seed_hi, (uint32_t)pixel, sample0 + (uint32_t)s_local);
     st_stream(&qo[i], make_float4(cam.pos.x, cam.pos.y, cam.pos.z, __uint_as_float((uint32_t)i << 5)));
     st_stream(&qd[i], make_float4(d.x, d.y, d.z, __uint_as_float(key)));
@@ -505,19 +506,20 @@ __device__ __forceinline__ void put_contrib(const SceneView& sc, float4* __restr
     else st_stream(&contrib[slot], make_float4(L.x, L.y, L.z, 0.f));
 }
 
+template <bool FAST = false>
 __device__ __forceinline__ bool shade_segment(const SceneView& sc, V3 o, V3 d, uint32_t key, int bounce, int max_depth,
                                               float t, uint32_t code, float hu, float hv, V3& beta, V3& np, V3& ndir, V3& L) {
     if (code == PRT_NO_HIT) {
         L = clamp_radiance(sc, beta * mk(sc.sky_r, sc.sky_g, sc.sky_b));   // cpu/renderer.cpp:99
         return false;
     }
-    Surface s = make_surface(sc, o, d, t, code, hu, hv);
+    Surface s = make_surface<FAST>(sc, o, d, t, code, hu, hv);
     MatRec m;
     if (s.mat >= 0 && s.mat < sc.n_mats) { m.a = __ldg(&sc.mats[s.mat].a); m.b = __ldg(&sc.mats[s.mat].b); }
     else { m.a = make_float4(0, 0, 0, 0); m.b = make_float4(0, 0, 0, 0); }
     Rng rng = rng_for_bounce(key, (uint32_t)bounce);
     V3 atten, emit;
-    bool sc_ok = scatter(m, d, s, rng, atten, ndir, emit);
+    bool sc_ok = scatter<FAST>(m, d, s, rng, atten, ndir, emit);
     L = clamp_radiance(sc, beta * emit);                                // L += emitted (renderer.cpp:74)
     if (sc_ok && bounce + 1 < max_depth) {
         beta = beta * atten;
@@ -526,7 +528,7 @@ __device__ __forceinline__ bool shade_segment(const SceneView& sc, V3 o, V3 d, u
         if (sc.rr_start >= 0 && bounce >= sc.rr_start) {
             const float p = fmaxf(fminf(fmaxf(fmaxf(beta.x, beta.y), beta.z), 1.0f), 0.05f);
             if (rng_uniform(rng) > p) return false;
-            beta = mk(beta.x / p, beta.y / p, beta.z / p);
+            beta = mk(div_t<FAST>(beta.x, p), div_t<FAST>(beta.y, p), div_t<FAST>(beta.z, p));
         }
         np = s.p;
         return true;
@@ -579,7 +581,7 @@ __device__ __forceinline__ void sq_put(float* __restrict__ q, int e, V3 o, V3 d,
 // A continuing path as it leaves shading; with DEFER the caller pushes it (block-wide, push_block) instead of the warp.
 struct ShadeOut { bool cont; V3 np, ndir, beta; uint32_t sb, key; };
 
-template <bool DEFER = false>
+template <bool DEFER = false, bool FAST = false>
 __device__ __forceinline__ void sq_shade(const SceneView& sc, const float* __restrict__ q, int first, int n, uint32_t lane,
                                          int bounce, int max_depth, float4* __restrict__ contrib, uint32_t* __restrict__ next_count,
                                          float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb, ShadeOut* out = nullptr) {
@@ -593,7 +595,7 @@ __device__ __forceinline__ void sq_shade(const SceneView& sc, const float* __res
         beta = mk(q[6 * SQ_CAP + e], q[7 * SQ_CAP + e], q[8 * SQ_CAP + e]);
         key = __float_as_uint(q[9 * SQ_CAP + e]); sb = __float_as_uint(q[10 * SQ_CAP + e]);
         V3 L;
-        cont = shade_segment(sc, o, d, key, bounce, max_depth, q[11 * SQ_CAP + e], __float_as_uint(q[12 * SQ_CAP + e]),
+        cont = shade_segment<FAST>(sc, o, d, key, bounce, max_depth, q[11 * SQ_CAP + e], __float_as_uint(q[12 * SQ_CAP + e]),
                              q[13 * SQ_CAP + e], q[14 * SQ_CAP + e], beta, np, ndir, L);
         if (!cont) put_contrib(sc, contrib, sb >> 5, L);
     }
@@ -628,7 +630,7 @@ __device__ __forceinline__ void push_block(uint32_t sc_capacity, const ShadeOut&
 
 // One batch of <= 32 segments whose closest hit is known: misses end here, hits go through the queue.
 // `live` = this lane holds a segment. Returns the new queue length. Whole warp calls.
-template <bool DEFER = false>
+template <bool DEFER = false, bool FAST = false>
 __device__ __forceinline__ int sq_batch(const SceneView& sc, float* __restrict__ q, int qn, uint32_t lane, bool live,
                                         V3 o, V3 d, V3 beta, uint32_t key, uint32_t slot_bounce, float t, uint32_t code, float u, float v,
                                         int bounce, int max_depth, float4* __restrict__ contrib, uint32_t* __restrict__ next_count,
@@ -644,13 +646,14 @@ __device__ __forceinline__ int sq_batch(const SceneView& sc, float* __restrict__
     __syncwarp();
     if (qn >= 32) {
         qn -= 32;
-        sq_shade<DEFER>(sc, q, qn, 32, lane, bounce, max_depth, contrib, next_count, no, nd, nb, out);
+        sq_shade<DEFER, FAST>(sc, q, qn, 32, lane, bounce, max_depth, contrib, next_count, no, nd, nb, out);
         __syncwarp();
     }
     return qn;
 }
 
 
+template <bool FAST>
 __global__ void __launch_bounds__(WF_THREADS)
 k_shade(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ qd, const float4* __restrict__ qb,
         const float4* __restrict__ hits, float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb,
@@ -668,12 +671,12 @@ k_shade(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ 
         const bool live = i < count;
         if (live) { o4 = ld_stream(&qo[i]); d4 = ld_stream(&qd[i]); b4 = ld_stream(&qb[i]); h = ld_stream(&hits[i]); }
         out.cont = false;
-        qn = sq_batch<true>(sc, q, qn, lane, live, xyz(o4), xyz(d4), xyz(b4), __float_as_uint(d4.w), __float_as_uint(o4.w),
+        qn = sq_batch<true, FAST>(sc, q, qn, lane, live, xyz(o4), xyz(d4), xyz(b4), __float_as_uint(d4.w), __float_as_uint(o4.w),
                             h.x, __float_as_uint(h.y), h.z, h.w, bounce, max_depth, contrib, &qcount[bounce + 1], no, nd, nb, &out);
         push_block(sc.capacity, out, lane, &qcount[bounce + 1], no, nd, nb);
     }
     out.cont = false;
-    if (qn > 0) sq_shade<true>(sc, q, 0, qn, lane, bounce, max_depth, contrib, &qcount[bounce + 1], no, nd, nb, &out);
+    if (qn > 0) sq_shade<true, FAST>(sc, q, 0, qn, lane, bounce, max_depth, contrib, &qcount[bounce + 1], no, nd, nb, &out);
     push_block(sc.capacity, out, lane, &qcount[bounce + 1], no, nd, nb);
 }
 
@@ -684,7 +687,7 @@ k_shade(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ 
 // Results are bit-identical to the staged kernels (same device functions, same order).
 constexpr int FUSED_STACK = 16;   // fused kernels walk trees of <= fused_max_prims primitives; leaves room for the shade queue
 
-template <bool COUNT, bool BRUTE>
+template <bool COUNT, bool BRUTE, bool FAST>
 __global__ void __launch_bounds__(WF_THREADS)
 k_primary(SceneView sc, CamView cam, int pix0, int npix, FastDiv div_npix, int n_paths, uint32_t sample0, uint32_t seed_lo, uint32_t seed_hi,
           float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb, float4* __restrict__ contrib,
@@ -708,14 +711,14 @@ k_primary(SceneView sc, CamView cam, int pix0, int npix, FastDiv div_npix, int n
             int s_local = (int)fdiv(i, div_npix);
             int pixel = pix0 + ((int)i - s_local * npix);
             int y = (int)fdiv((uint32_t)pixel, cam.divW), x = pixel - y * cam.W;
-            d = camera_dir(cam, (float)x + 0.5f, (float)y + 0.5f);
+            d = camera_dir<FAST>(cam, (float)x + 0.5f, (float)y + 0.5f);
             key = path_key(seed_lo, seed_hi, (uint32_t)pixel, sample0 + (uint32_t)s_local);
             b = traverse<COUNT, BRUTE, FUSED_STACK>(sc, cam.pos, d, BRUTE ? sstack : sstack + threadIdx.x, nn, npr);
         }
-        qn = sq_batch(sc, q, qn, lane, live, cam.pos, d, mk(1.f, 1.f, 1.f), key, i << 5, b.t, b.code, b.u, b.v,
+        qn = sq_batch<false, FAST>(sc, q, qn, lane, live, cam.pos, d, mk(1.f, 1.f, 1.f), key, i << 5, b.t, b.code, b.u, b.v,
                       0, max_depth, contrib, &qcount[1], no, nd, nb);
     }
-    if (qn > 0) sq_shade(sc, q, 0, qn, lane, 0, max_depth, contrib, &qcount[1], no, nd, nb);
+    if (qn > 0) sq_shade<false, FAST>(sc, q, 0, qn, lane, 0, max_depth, contrib, &qcount[1], no, nd, nb);
     if (COUNT) {
         for (int o = 16; o > 0; o >>= 1) { nn += __shfl_xor_sync(0xffffffffu, nn, o); npr += __shfl_xor_sync(0xffffffffu, npr, o); }
         if (lane == 0 && (nn | npr)) {
@@ -726,7 +729,7 @@ k_primary(SceneView sc, CamView cam, int pix0, int npix, FastDiv div_npix, int n
     if (blockIdx.x == 0 && threadIdx.x == 0) { atomicAdd(&stats[0], (unsigned long long)count); qcount[0] = count; }
 }
 
-template <bool COUNT, bool BRUTE>
+template <bool COUNT, bool BRUTE, bool FAST>
 __global__ void __launch_bounds__(WF_THREADS)
 k_bounce(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ qd, const float4* __restrict__ qb,
          float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb, float4* __restrict__ contrib,
@@ -748,10 +751,10 @@ k_bounce(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__
             o4 = ld_stream(&qo[i]); d4 = ld_stream(&qd[i]); b4 = ld_stream(&qb[i]);
             b = traverse<COUNT, BRUTE, FUSED_STACK>(sc, xyz(o4), xyz(d4), BRUTE ? sstack : sstack + threadIdx.x, nn, npr);
         }
-        qn = sq_batch(sc, q, qn, lane, live, xyz(o4), xyz(d4), xyz(b4), __float_as_uint(d4.w), __float_as_uint(o4.w),
+        qn = sq_batch<false, FAST>(sc, q, qn, lane, live, xyz(o4), xyz(d4), xyz(b4), __float_as_uint(d4.w), __float_as_uint(o4.w),
                       b.t, b.code, b.u, b.v, bounce, max_depth, contrib, &qcount[bounce + 1], no, nd, nb);
     }
-    if (qn > 0) sq_shade(sc, q, 0, qn, lane, bounce, max_depth, contrib, &qcount[bounce + 1], no, nd, nb);
+    if (qn > 0) sq_shade<false, FAST>(sc, q, 0, qn, lane, bounce, max_depth, contrib, &qcount[bounce + 1], no, nd, nb);
     if (COUNT) {
         for (int o = 16; o > 0; o >>= 1) { nn += __shfl_xor_sync(0xffffffffu, nn, o); npr += __shfl_xor_sync(0xffffffffu, npr, o); }
         if (lane == 0 && (nn | npr)) {
@@ -767,7 +770,7 @@ k_bounce(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__
 // queue, times 17 bounces at depth 20. k_tail takes the queue of bounce `bounce0` and follows every ray in it to the
 // end of its path inside the thread: no queue, no compaction, one launch. Same device functions, same RNG keys, one
 // contribution per path => the image and the per-bounce ray counts are bit-identical to the launch-per-bounce form.
-template <bool COUNT, bool BRUTE, bool WIDE = false>
+template <bool COUNT, bool BRUTE, bool WIDE, bool FAST>
 __global__ void __launch_bounds__(WF_THREADS)
 k_tail(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ qd, const float4* __restrict__ qb,
        float4* __restrict__ contrib, const uint32_t* __restrict__ qcount, int bounce0, int max_depth,
@@ -797,7 +800,7 @@ k_tail(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ q
                 const Best b = WIDE ? traverse_wide<COUNT, FUSED_STACK>(sc, o, d, sstack + threadIdx.x, nn, npr)
                                     : traverse<COUNT, BRUTE, FUSED_STACK>(sc, o, d, BRUTE ? sstack : sstack + threadIdx.x, nn, npr);
                 V3 np, ndir, L;
-                if (shade_segment(sc, o, d, key, bounce, max_depth, b.t, b.code, b.u, b.v, beta, np, ndir, L)) { o = np; d = ndir; }
+                if (shade_segment<FAST>(sc, o, d, key, bounce, max_depth, b.t, b.code, b.u, b.v, beta, np, ndir, L)) { o = np; d = ndir; }
                 else { put_contrib(sc, contrib, slot, L); alive = false; }
             }
         }
@@ -975,6 +978,7 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
     const uint32_t seed_lo = (uint32_t)seed, seed_hi = (uint32_t)(seed >> 32);
     const bool fused = c->fused < 0 ? (c->n_prims <= c->fused_max_prims) : (c->fused != 0);
     const bool timing_opt = c->stage_timing != 0;
+    const bool fastm = c->fast_math != 0;                              // tolerance-mode float math on the shading side (prt_device.cuh)
     const bool wide = sc.wnodes != nullptr && c->n_prims > 1;          // staged extend walks the 4-wide quantised nodes
     auto k_ext = wide ? (c->counters_on ? k_extend_wide<true> : k_extend_wide<false>)
                       : (c->counters_on ? k_extend_pt<true> : k_extend_pt<false>);
@@ -1078,8 +1082,10 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
             if (fused) {
                 if (timing) spans.push_back({stamp(st), 2});
                 {
-                    auto kp = c->counters_on ? (brute ? k_primary<true, true> : k_primary<true, false>)
-                                             : (brute ? k_primary<false, true> : k_primary<false, false>);
+                    auto kp = fastm ? (c->counters_on ? (brute ? k_primary<true, true, true> : k_primary<true, false, true>)
+                                                      : (brute ? k_primary<false, true, true> : k_primary<false, false, true>))
+                                    : (c->counters_on ? (brute ? k_primary<true, true, false> : k_primary<true, false, false>)
+                                                      : (brute ? k_primary<false, true, false> : k_primary<false, false, false>));
                     kp<<<grid, WF_THREADS, 0, st>>>(sc, cam, (int)p0, npix, div_npix, n_paths, (uint32_t)(sample_begin + s0), seed_lo,
                                                     seed_hi, qo[1], qd[1], qb[1], contrib, qcount, max_depth, dstats, dyn);
                 }
@@ -1089,8 +1095,10 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
                 for (int b = 1; b < std::min(max_depth, tail_b); ++b) {
                     if (timing) spans.push_back({stamp(st), 0});
                     {
-                        auto kb = c->counters_on ? (brute ? k_bounce<true, true> : k_bounce<true, false>)
-                                                 : (brute ? k_bounce<false, true> : k_bounce<false, false>);
+                        auto kb = fastm ? (c->counters_on ? (brute ? k_bounce<true, true, true> : k_bounce<true, false, true>)
+                                                          : (brute ? k_bounce<false, true, true> : k_bounce<false, false, true>))
+                                        : (c->counters_on ? (brute ? k_bounce<true, true, false> : k_bounce<true, false, false>)
+                                                          : (brute ? k_bounce<false, true, false> : k_bounce<false, false, false>));
                         kb<<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], qb[cur], qo[cur ^ 1], qd[cur ^ 1], qb[cur ^ 1],
                                                         contrib, qcount, b, max_depth, dstats);
                     }
@@ -1099,7 +1107,7 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
                     cur ^= 1;
                 }
             } else {
-                k_raygen<<<(n_paths + WF_THREADS - 1) / WF_THREADS, WF_THREADS, 0, st>>>(
+                (fastm ? k_raygen<true> : k_raygen<false>)<<<(n_paths + WF_THREADS - 1) / WF_THREADS, WF_THREADS, 0, st>>>(
                     cam, (int)p0, npix, div_npix, n_paths, (uint32_t)(sample_begin + s0), seed_lo, seed_hi, qo[0], qd[0], qb[0], qcount, dyn);
                 ++launches;
                 for (int b = 0; b < std::min(max_depth, tail_b); ++b) {
@@ -1110,7 +1118,7 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
                     } else if (c->counters_on) k_extend<true><<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], hits, qcount, b, dstats);
                     else k_extend<false><<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], hits, qcount, b, dstats);
                     if (timing) spans.push_back({stamp(st), 1});
-                    k_shade<<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], qb[cur], hits, qo[cur ^ 1], qd[cur ^ 1], qb[cur ^ 1],
+                    (fastm ? k_shade<true> : k_shade<false>)<<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], qb[cur], hits, qo[cur ^ 1], qd[cur ^ 1], qb[cur ^ 1],
                                                          contrib, qcount, b, max_depth);
                     if (timing) stamp(st);
                     launches += 2;
@@ -1131,8 +1139,10 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
             if (tail_b < max_depth) {
                 if (timing) spans.push_back({stamp(st), 0});
                 const bool tw = wide && !fused;                        // staged scenes with wide nodes: same walk as their extend kernel
-                auto kt = c->counters_on ? (brute && fused ? k_tail<true, true> : tw ? k_tail<true, false, true> : k_tail<true, false>)
-                                         : (brute && fused ? k_tail<false, true> : tw ? k_tail<false, false, true> : k_tail<false, false>);
+                auto kt = fastm ? (c->counters_on ? (brute && fused ? k_tail<true, true, false, true> : tw ? k_tail<true, false, true, true> : k_tail<true, false, false, true>)
+                                                  : (brute && fused ? k_tail<false, true, false, true> : tw ? k_tail<false, false, true, true> : k_tail<false, false, false, true>))
+                                : (c->counters_on ? (brute && fused ? k_tail<true, true, false, false> : tw ? k_tail<true, false, true, false> : k_tail<true, false, false, false>)
+                                                  : (brute && fused ? k_tail<false, true, false, false> : tw ? k_tail<false, false, true, false> : k_tail<false, false, false, false>));
                 kt<<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], qb[cur], contrib, qcount, tail_b, max_depth, dstats);
                 if (timing) stamp(st);
                 ++launches;

@@ -297,6 +297,34 @@ def test_c1_full_size(ctx, oracle):
         assert abs(st.rays_total - ref_rays) <= 0.01 * ref_rays
 
 
+@pytest.mark.parametrize("name,W,H,spp,depth", [("cornell", 128, 128, 16, 8), ("default", 96, 96, 8, 8), ("random_balls_large", 96, 54, 8, 8),
+                                                 ("closed_cornell", 96, 96, 8, 12), ("dragon3", 64, 64, 4, 8)])
+def test_fast_math_mode(ctx, gold, name, W, H, spp, depth):
+    """Option fast_math (default OFF): SFU approximations for divide / sqrt / rsqrt on the SHADING side only. Integer work is
+    untouched - hit records of a fixed batch stay bit-identical - and radiance stays within the north star's tolerance
+    against the bit-exact mode (= the oracle): per-pixel RMSE <= 1e-3, max relative error <= 1e-2 over non-flip pixels,
+    flips (a path took another discrete decision: Schlick draw, rejection loop, metal horizon) counted and bounded."""
+    sd = SCENES[name](gold)
+    cam = S.Camera(width=W, height=H) if name != "dragon3" else S.Camera(pos=(0.0, 1.0, 5.0), front=S._normalize(S._v3(0, -1, -5)), width=W, height=H)
+    ctx.set_scene(sd); ctx.build_bvh(); ctx.set_camera(cam)
+    rays = util.fixed_ray_batch(sd, 8192, seed=5, clamp_extent=60.0)
+    out = {}
+    for fast in (0, 1):
+        ctx.set_option("fast_math", fast)
+        ctx.clear_accum(); ctx.render(spp, depth, seed=11)
+        out[fast] = (ctx.read_accum(), list(ctx.stats().rays_per_bounce), ctx.trace_batch(rays))
+    ctx.set_option("fast_math", 0)
+    assert np.array_equal(out[0][2], out[1][2]), "closest-hit records must not depend on fast_math"
+    assert out[0][1][0] == out[1][1][0]                                      # same camera rays
+    m = util.image_metrics(out[0][0] / spp, out[1][0] / spp)
+    drift = abs(sum(out[1][1]) - sum(out[0][1])) / sum(out[0][1])
+    print("fast_math %s: %s, ray-count drift %.2e" % (name, m, drift))
+    assert m["rmse_nonflip"] <= 1e-3 and m["max_rel_nonflip"] <= 1e-2, m
+    assert m["flips"] <= 0.01 * m["n"] and drift <= 1e-3, (m, drift)
+    # (the estimator has no cosine or texture term: a path's radiance is a product of material constants, so most images come
+    # out bit-identical and a difference can only be a flipped discrete decision)
+
+
 def test_sample_ranges_compose(ctx, gold):
     """Multi-GPU sharding rule: samples [0,6) == [0,2) + [2,6), any wave size."""
     sd = S.closed_cornell(); cam = S.Camera(width=80, height=60)

@@ -69,6 +69,24 @@ k_raygen(CamView cam, int pix0, int npix, FastDiv div_npix, int n_paths, uint32_
     st_stream(&qb[i], make_float4(1.f, 1.f, 1.f, 0.f));
 }
 
+// Camera rays without a queue: in the staged pipeline the bounce-0 extend and shade kernels compute their ray from its path
+// index (same functions, same bits as k_raygen) instead of reading what k_raygen wrote - 48 B written + 80 B read per path
+// that never cross HBM (17 of the 50 GB a 64-spp step of the 960 K-triangle scene moved). PRIM: 0 = rays come from the queue,
+// 1 = camera rays (bit-exact math), 2 = camera rays (fast_math).
+struct PrimaryGen {
+    CamView cam; int pix0, npix, n_paths; FastDiv div_npix; uint32_t sample0, seed_lo, seed_hi; const uint32_t* dyn;
+};
+template <bool FAST>
+__device__ __forceinline__ void primary_ray(const PrimaryGen& g, uint32_t i, V3& d, uint32_t& key) {
+    uint32_t sample0 = g.sample0, lo = g.seed_lo, hi = g.seed_hi;
+    if (g.dyn) { sample0 = g.dyn[0]; lo = g.dyn[1]; hi = g.dyn[2]; }        // CUDA-graph replay: the per-call values live in memory
+    const int s_local = (int)fdiv(i, g.div_npix);
+    const int pixel = g.pix0 + ((int)i - s_local * g.npix);
+    const int y = (int)fdiv((uint32_t)pixel, g.cam.divW), x = pixel - y * g.cam.W;
+    d = camera_dir<FAST>(g.cam, (float)x + 0.5f, (float)y + 0.5f);           // pixel centre, cpu/renderer.cpp:45
+    key = path_key(lo, hi, (uint32_t)pixel, sample0 + (uint32_t)s_local);
+}
+
 // ------------------------------------------------------------------ extend
 // Closest hit by stack traversal of the two-child LBVH. One thread per ray; the traversal
 // stack lives in shared memory ([entry][thread], conflict-free), overflowing to local memory.
@@ -167,13 +185,13 @@ k_extend(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__
 // Order-independent result: (t, prim_id) tie rule makes the closest hit unique, so records are
 // bit-identical to k_extend / the CPU oracle; node and leaf counters are identical too.
 #define PRT_DONE ((int)0x80000000)
-template <bool COUNT>
+template <bool COUNT, int PRIM = 0>
 __global__ void __launch_bounds__(WF_THREADS)
 k_extend_pt(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ qd, float4* __restrict__ hits,
             const uint32_t* __restrict__ qcount, uint32_t* __restrict__ work, int bounce, int refill,
-            unsigned long long* __restrict__ stats) {
+            unsigned long long* __restrict__ stats, PrimaryGen pg) {
     __shared__ int sstack[STACK_SMEM * WF_THREADS];
-    const uint32_t count = qcount[bounce];
+    const uint32_t count = PRIM ? (uint32_t)pg.n_paths : qcount[bounce];
     const uint32_t lane = threadIdx.x & 31u;
     int* __restrict__ st = sstack + threadIdx.x;
     int lstack[STACK_LOCAL];
@@ -196,8 +214,8 @@ k_extend_pt(SceneView sc, const float4* __restrict__ qo, const float4* __restric
             if (!have) {
                 idx = base + __popc(idle & ((1u << lane) - 1u));
                 if (idx < count) {
-                    float4 o4 = ld_stream(&qo[idx]), d4 = ld_stream(&qd[idx]);
-                    o = xyz(o4); d = xyz(d4);
+                    if (PRIM) { uint32_t key_; o = pg.cam.pos; primary_ray<PRIM == 2>(pg, idx, d, key_); }
+                    else { float4 o4 = ld_stream(&qo[idx]), d4 = ld_stream(&qd[idx]); o = xyz(o4); d = xyz(d4); }
                     rb = make_raybox(o, d);
                     if (sc.n_tris > 0) rs = make_shear(d);
                     dn = sc.n_spheres > 0 ? normalize(d) : d;
@@ -277,13 +295,13 @@ k_extend_pt(SceneView sc, const float4* __restrict__ qo, const float4* __restric
 #ifndef PRT_EXT_MIN_BLOCKS
 #define PRT_EXT_MIN_BLOCKS 4
 #endif
-template <bool COUNT>
+template <bool COUNT, int PRIM = 0>
 __global__ void __launch_bounds__(WF_THREADS, PRT_EXT_MIN_BLOCKS)
 k_extend_wide(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ qd, float4* __restrict__ hits,
               const uint32_t* __restrict__ qcount, uint32_t* __restrict__ work, int bounce, int refill,
-              unsigned long long* __restrict__ stats) {
+              unsigned long long* __restrict__ stats, PrimaryGen pg) {
     __shared__ int sstack[STACK_SMEM * WF_THREADS];
-    const uint32_t count = qcount[bounce];
+    const uint32_t count = PRIM ? (uint32_t)pg.n_paths : qcount[bounce];
     const uint32_t lane = threadIdx.x & 31u;
     int* __restrict__ st = sstack + threadIdx.x;
     int lstack[STACK_LOCAL];
@@ -301,8 +319,8 @@ k_extend_wide(SceneView sc, const float4* __restrict__ qo, const float4* __restr
             if (!have) {
                 idx = base + __popc(idle & ((1u << lane) - 1u));
                 if (idx < count) {
-                    float4 o4 = ld_stream(&qo[idx]), d4 = ld_stream(&qd[idx]);
-                    o = xyz(o4); d = xyz(d4);
+                    if (PRIM) { uint32_t key_; o = pg.cam.pos; primary_ray<PRIM == 2>(pg, idx, d, key_); }
+                    else { float4 o4 = ld_stream(&qo[idx]), d4 = ld_stream(&qd[idx]); o = xyz(o4); d = xyz(d4); }
                     inv = mk(safe_inv(d.x), safe_inv(d.y), safe_inv(d.z));
                     if (sc.n_tris > 0) rs = make_shear(d);
                     dn = sc.n_spheres > 0 ? normalize(d) : d;
@@ -653,14 +671,14 @@ __device__ __forceinline__ int sq_batch(const SceneView& sc, float* __restrict__
 }
 
 
-template <bool FAST>
+template <bool FAST, bool PRIMARY = false>
 __global__ void __launch_bounds__(WF_THREADS)
 k_shade(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ qd, const float4* __restrict__ qb,
         const float4* __restrict__ hits, float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb,
-        float4* __restrict__ contrib, uint32_t* __restrict__ qcount, int bounce, int max_depth) {
+        float4* __restrict__ contrib, uint32_t* __restrict__ qcount, int bounce, int max_depth, PrimaryGen pg) {
     __shared__ float sq[WF_WARPS * SQ_FLOATS];
     float* q = sq + (threadIdx.x >> 5) * SQ_FLOATS;
-    const uint32_t count = qcount[bounce];
+    const uint32_t count = PRIMARY ? (uint32_t)pg.n_paths : qcount[bounce];
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t stride = gridDim.x * WF_THREADS;
     int qn = 0;
@@ -669,7 +687,14 @@ k_shade(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ 
         const uint32_t i = cbase + threadIdx.x;
         float4 o4 = make_float4(0, 0, 0, 0), d4 = o4, b4 = o4, h = o4;
         const bool live = i < count;
-        if (live) { o4 = ld_stream(&qo[i]); d4 = ld_stream(&qd[i]); b4 = ld_stream(&qb[i]); h = ld_stream(&hits[i]); }
+        if (live) {
+            if (PRIMARY) {                                                  // camera ray recomputed from the path index (see PrimaryGen)
+                V3 d; uint32_t key; primary_ray<FAST>(pg, i, d, key);
+                o4 = make_float4(pg.cam.pos.x, pg.cam.pos.y, pg.cam.pos.z, __uint_as_float(i << 5));
+                d4 = make_float4(d.x, d.y, d.z, __uint_as_float(key)); b4 = make_float4(1.f, 1.f, 1.f, 0.f);
+            } else { o4 = ld_stream(&qo[i]); d4 = ld_stream(&qd[i]); b4 = ld_stream(&qb[i]); }
+            h = ld_stream(&hits[i]);
+        }
         out.cont = false;
         qn = sq_batch<true, FAST>(sc, q, qn, lane, live, xyz(o4), xyz(d4), xyz(b4), __float_as_uint(d4.w), __float_as_uint(o4.w),
                             h.x, __float_as_uint(h.y), h.z, h.w, bounce, max_depth, contrib, &qcount[bounce + 1], no, nd, nb, &out);
@@ -980,8 +1005,13 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
     const bool timing_opt = c->stage_timing != 0;
     const bool fastm = c->fast_math != 0;                              // tolerance-mode float math on the shading side (prt_device.cuh)
     const bool wide = sc.wnodes != nullptr && c->n_prims > 1;          // staged extend walks the 4-wide quantised nodes
-    auto k_ext = wide ? (c->counters_on ? k_extend_wide<true> : k_extend_wide<false>)
-                      : (c->counters_on ? k_extend_pt<true> : k_extend_pt<false>);
+    auto k_ext = wide ? (c->counters_on ? k_extend_wide<true, 0> : k_extend_wide<false, 0>)
+                      : (c->counters_on ? k_extend_pt<true, 0> : k_extend_pt<false, 0>);
+    // bounce 0 of the staged pipeline: camera rays are computed in the kernels (no k_raygen, no queue traffic for them)
+    auto k_ext0 = fastm ? (wide ? (c->counters_on ? k_extend_wide<true, 2> : k_extend_wide<false, 2>)
+                                : (c->counters_on ? k_extend_pt<true, 2> : k_extend_pt<false, 2>))
+                        : (wide ? (c->counters_on ? k_extend_wide<true, 1> : k_extend_wide<false, 1>)
+                                : (c->counters_on ? k_extend_pt<true, 1> : k_extend_pt<false, 1>));
     int grid_pt = grid_p;
     {   // persistent extend: exactly the CTAs that are resident at once
         int per_sm = 0;
@@ -1107,19 +1137,25 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
                     cur ^= 1;
                 }
             } else {
-                (fastm ? k_raygen<true> : k_raygen<false>)<<<(n_paths + WF_THREADS - 1) / WF_THREADS, WF_THREADS, 0, st>>>(
-                    cam, (int)p0, npix, div_npix, n_paths, (uint32_t)(sample_begin + s0), seed_lo, seed_hi, qo[0], qd[0], qb[0], qcount, dyn);
-                ++launches;
+                const PrimaryGen pg{cam, (int)p0, npix, n_paths, div_npix, (uint32_t)(sample_begin + s0), seed_lo, seed_hi, dyn};
+                const bool gen0 = c->persistent != 0;                  // the persistent extend kernels generate camera rays themselves
+                if (!gen0) {
+                    (fastm ? k_raygen<true> : k_raygen<false>)<<<(n_paths + WF_THREADS - 1) / WF_THREADS, WF_THREADS, 0, st>>>(
+                        cam, (int)p0, npix, div_npix, n_paths, (uint32_t)(sample_begin + s0), seed_lo, seed_hi, qo[0], qd[0], qb[0], qcount, dyn);
+                    ++launches;
+                }
                 for (int b = 0; b < std::min(max_depth, tail_b); ++b) {
+                    const bool prim = gen0 && b == 0;
                     if (timing) spans.push_back({stamp(st), b == 0 ? 2 : 0});
                     if (c->persistent) {
                         uint32_t* work = qcount + (PRT_MAX_DEPTH + 2) + b;
-                        k_ext<<<grid_pt, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], hits, qcount, work, b, wide ? c->pt_refill_wide : c->pt_refill, dstats);
+                        (prim ? k_ext0 : k_ext)<<<grid_pt, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], hits, qcount, work, b, wide ? c->pt_refill_wide : c->pt_refill, dstats, pg);
                     } else if (c->counters_on) k_extend<true><<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], hits, qcount, b, dstats);
                     else k_extend<false><<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], hits, qcount, b, dstats);
                     if (timing) spans.push_back({stamp(st), 1});
-                    (fastm ? k_shade<true> : k_shade<false>)<<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], qb[cur], hits, qo[cur ^ 1], qd[cur ^ 1], qb[cur ^ 1],
-                                                         contrib, qcount, b, max_depth);
+                    auto ksh = prim ? (fastm ? k_shade<true, true> : k_shade<false, true>) : (fastm ? k_shade<true, false> : k_shade<false, false>);
+                    ksh<<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], qb[cur], hits, qo[cur ^ 1], qd[cur ^ 1], qb[cur ^ 1],
+                                                         contrib, qcount, b, max_depth, pg);
                     if (timing) stamp(st);
                     launches += 2;
                     cur ^= 1;
@@ -1247,16 +1283,16 @@ int wavefront_trace_batch(Ctx* c, const prt_ray* rays, int n, prt_hit* out, int 
         int per_sm = 4;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, WF_THREADS, 0);
         k<<<std::max(1, c->num_sms * std::max(1, per_sm)), WF_THREADS, 0, st>>>(sc, (const float4*)c->q_o[0].p, (const float4*)c->q_d[0].p,
-                                                                                (float4*)c->hits.p, qcount, work, 0, c->pt_refill_wide, dstats);
+                                                                                (float4*)c->hits.p, qcount, work, 0, c->pt_refill_wide, dstats, PrimaryGen{});
     } else if (use_bvh && c->persistent) {
         uint32_t* work = qcount + (PRT_MAX_DEPTH + 2);
         int per_sm = 4;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_extend_pt<false>, WF_THREADS, 0);
         const int gpt = std::max(1, c->num_sms * std::max(1, per_sm));
         if (c->counters_on)
-            k_extend_pt<true><<<gpt, WF_THREADS, 0, st>>>(sc, (const float4*)c->q_o[0].p, (const float4*)c->q_d[0].p, (float4*)c->hits.p, qcount, work, 0, c->pt_refill, dstats);
+            k_extend_pt<true><<<gpt, WF_THREADS, 0, st>>>(sc, (const float4*)c->q_o[0].p, (const float4*)c->q_d[0].p, (float4*)c->hits.p, qcount, work, 0, c->pt_refill, dstats, PrimaryGen{});
         else
-            k_extend_pt<false><<<gpt, WF_THREADS, 0, st>>>(sc, (const float4*)c->q_o[0].p, (const float4*)c->q_d[0].p, (float4*)c->hits.p, qcount, work, 0, c->pt_refill, dstats);
+            k_extend_pt<false><<<gpt, WF_THREADS, 0, st>>>(sc, (const float4*)c->q_o[0].p, (const float4*)c->q_d[0].p, (float4*)c->hits.p, qcount, work, 0, c->pt_refill, dstats, PrimaryGen{});
     } else if (use_bvh) {
         if (c->counters_on)
             k_extend<true><<<grid, WF_THREADS, 0, st>>>(sc, (const float4*)c->q_o[0].p, (const float4*)c->q_d[0].p, (float4*)c->hits.p, qcount, 0, dstats);

@@ -464,7 +464,7 @@ def test_small_wave_tail_kernel_staged_scenes(ctx, gold):
             st = ctx.stats()
             out.append((ctx.read_accum(), list(st.rays_per_bounce), st.kernel_launches, st.nodes_visited, st.prims_tested))
         ctx.set_option("tail_bounce", 2); ctx.set_option("tail_adaptive", 1)
-        assert [o[2] for o in out] == [26, 5, 9, 25]          # raygen + 2/bounce + resolve; raygen + 2*tail + k_tail + resolve
+        assert [o[2] for o in out] == [25, 4, 8, 24]          # 2/bounce + resolve; 2*tail + k_tail + resolve (no raygen launch: bounce 0 makes its own camera rays)
         for o in out[1:]:      # the tail walks the same kind of node as the extend kernel (two-child / 4-wide): counters equal too
             assert np.array_equal(o[0], out[0][0]) and o[1] == out[0][1] and o[3:] == out[0][3:], sd.name
     ctx.enable_counters(False)

@@ -757,6 +757,7 @@ int prt_set_option(prt_ctx* ctx, const char* key, int64_t value) {
     else if (!strcmp(key, "tail_bounce")) c->tail_bounce = value < 0 ? 0 : value;
     else if (!strcmp(key, "tail_max_paths")) c->tail_max_paths = value < 0 ? 0 : value;
     else if (!strcmp(key, "tail_adaptive")) c->tail_adaptive = value ? 1 : 0;
+    else if (!strcmp(key, "tail_pool")) c->tail_pool = value ? 1 : 0;
     else if (!strcmp(key, "tail_rays")) c->tail_rays = value < 0 ? 0 : value;
     else if (!strcmp(key, "morton_centroid")) c->morton_centroid = value ? 1 : 0;
     else if (!strcmp(key, "sort_rays")) c->sort_rays = value ? 1 : 0;

@@ -101,6 +101,7 @@ struct Ctx {
     int tail_adaptive = 1;             //   tail_adaptive the start is the first bounce whose queue is expected to hold <= tail_rays
     int tail_rays = 512 << 10;         //   rays (survival per bounce taken from the previous call on this scene; none yet: 1.0)
     int tail_rays_staged = 64 << 10;   //   same for the staged pipeline (its tail walks the two-child tree in-thread: hand over later)
+    int tail_pool = 1;                 // fused scenes: the tail runs as a block-local wavefront (k_tail_pool) instead of one ray per thread
     int tail_max_paths = 1 << 26;      // waves with more paths never use the tail
     unsigned long long hint_rays[PRT_MAX_DEPTH] = {0};   // rays per bounce of the last fused render of this scene; [0] = 0: none yet
     int fused = -1;                             // 1: k_primary/k_bounce, 0: raygen/extend/shade as separate stages, -1: by scene size

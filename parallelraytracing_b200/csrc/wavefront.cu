@@ -842,6 +842,134 @@ k_tail(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ q
         if (rays_at[k]) atomicAdd(&stats[k], (unsigned long long)rays_at[k]);
 }
 
+// The same tail as a BLOCK-LOCAL WAVEFRONT (fused scenes). k_tail keeps one ray per thread until its path ends: after two
+// bounces a third of the lanes are alive (ncu: 9.2 of 32 lanes per instruction, 47 of the 155 us of a one-sample Cornell call).
+// Here a block owns a contiguous chunk of the queue and a pool of <= 256 rays in shared memory; every round it (A) finds the
+// closest hit of every pooled ray, finishes the misses and packs the hits densely, (B) shades the dense hits at full width,
+// (C) packs the surviving paths into the other pool buffer and tops it up from its chunk. No global queue traffic, no launch
+// per bounce, warps stay full until the chunk runs dry. Same device functions and RNG keys: image, per-bounce ray counts
+// and traversal counters are bit-identical to the launch-per-bounce form.
+template <bool COUNT, bool BRUTE, bool FAST>
+__global__ void __launch_bounds__(WF_THREADS)
+k_tail_pool(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ qd, const float4* __restrict__ qb,
+            float4* __restrict__ contrib, const uint32_t* __restrict__ qcount, int bounce0, int max_depth,
+            unsigned long long* __restrict__ stats) {
+    __shared__ int sstack[BRUTE ? 1 : FUSED_STACK * WF_THREADS];
+    __shared__ float pool[2][11][WF_THREADS];                          // o.xyz d.xyz beta.rgb key slot_bounce, [word][entry]
+    __shared__ float hrec[4][WF_THREADS];                              // t, code, u, v of this round's hits, dense
+    __shared__ int hsrc[WF_THREADS];                                   // pool entry of each dense hit
+    __shared__ uint32_t rays_at[PRT_MAX_DEPTH];
+    __shared__ uint32_t s_warp[WF_WARPS];
+    const int tid = threadIdx.x;
+    const uint32_t lane = tid & 31u, wid = tid >> 5, lt = (1u << lane) - 1u;
+    for (int k = tid; k < PRT_MAX_DEPTH; k += WF_THREADS) rays_at[k] = 0u;
+    const uint32_t count = qcount[bounce0];
+    const uint32_t per = (count + gridDim.x - 1) / gridDim.x;
+    uint32_t cursor = min(count, blockIdx.x * per);
+    const uint32_t cend = min(count, cursor + per);
+    uint32_t nn = 0, npr = 0;
+    int cur = 0, pool_n = 0;
+    // block-wide exclusive position of a flag + total (two barriers)
+    auto pack = [&](bool flag, int& total) -> int {
+        const uint32_t m = __ballot_sync(0xffffffffu, flag);
+        __syncthreads();                                               // s_warp free again
+        if (lane == 0) s_warp[wid] = (uint32_t)__popc(m);
+        __syncthreads();
+        int base = 0; total = 0;
+#pragma unroll
+        for (int k = 0; k < WF_WARPS; ++k) { const int v = (int)s_warp[k]; base += k < (int)wid ? v : 0; total += v; }
+        return base + __popc(m & lt);
+    };
+    for (;;) {
+        // ---- (C') top the pool up from this block's chunk of the queue
+        const int take = min((int)(cend - cursor), WF_THREADS - pool_n);
+        if (tid < take) {
+            const float4 o4 = ld_stream(&qo[cursor + tid]), d4 = ld_stream(&qd[cursor + tid]), b4 = ld_stream(&qb[cursor + tid]);
+            const int e = pool_n + tid;
+            pool[cur][0][e] = o4.x; pool[cur][1][e] = o4.y; pool[cur][2][e] = o4.z;
+            pool[cur][3][e] = d4.x; pool[cur][4][e] = d4.y; pool[cur][5][e] = d4.z;
+            pool[cur][6][e] = b4.x; pool[cur][7][e] = b4.y; pool[cur][8][e] = b4.z;
+            pool[cur][9][e] = d4.w; pool[cur][10][e] = o4.w;
+        }
+        cursor += (uint32_t)take; pool_n += take;
+        __syncthreads();
+        if (pool_n == 0) break;
+        if (cursor == cend && pool_n <= 32) {
+            // the chunk is used up and what is left fits one warp: the remaining bounces are a latency chain, and a round
+            // of the pool costs five block barriers - warp 0 follows those few paths to their end in-thread (as k_tail does)
+            if (wid == 0 && (int)lane < pool_n) {
+                V3 o = mk(pool[cur][0][lane], pool[cur][1][lane], pool[cur][2][lane]);
+                V3 d = mk(pool[cur][3][lane], pool[cur][4][lane], pool[cur][5][lane]);
+                V3 beta = mk(pool[cur][6][lane], pool[cur][7][lane], pool[cur][8][lane]);
+                const uint32_t key = __float_as_uint(pool[cur][9][lane]), sb0 = __float_as_uint(pool[cur][10][lane]);
+                for (int bounce = (int)(sb0 & 31u); bounce < max_depth; ++bounce) {
+                    atomicAdd(&rays_at[bounce], 1u);
+                    const Best b = traverse<COUNT, BRUTE, FUSED_STACK>(sc, o, d, BRUTE ? sstack : sstack + tid, nn, npr);
+                    V3 np, ndir, L;
+                    if (shade_segment<FAST>(sc, o, d, key, bounce, max_depth, b.t, b.code, b.u, b.v, beta, np, ndir, L)) { o = np; d = ndir; }
+                    else { put_contrib(sc, contrib, sb0 >> 5, L); break; }
+                }
+            }
+            break;
+        }
+        // ---- (A) closest hit of every pooled ray; misses end here
+        bool hit = false;
+        Best b; best_init(b);
+        if (tid < pool_n) {
+            const V3 o = mk(pool[cur][0][tid], pool[cur][1][tid], pool[cur][2][tid]);
+            const V3 d = mk(pool[cur][3][tid], pool[cur][4][tid], pool[cur][5][tid]);
+            const uint32_t sb = __float_as_uint(pool[cur][10][tid]);
+            atomicAdd(&rays_at[sb & 31u], 1u);
+            b = traverse<COUNT, BRUTE, FUSED_STACK>(sc, o, d, BRUTE ? sstack : sstack + tid, nn, npr);
+            hit = b.code != PRT_NO_HIT;
+            if (!hit) {
+                const V3 beta = mk(pool[cur][6][tid], pool[cur][7][tid], pool[cur][8][tid]);
+                put_contrib(sc, contrib, sb >> 5, clamp_radiance(sc, beta * mk(sc.sky_r, sc.sky_g, sc.sky_b)));   // cpu/renderer.cpp:99
+            }
+        }
+        int n_hits;
+        const int hp = pack(hit, n_hits);
+        if (hit) { hrec[0][hp] = b.t; hrec[1][hp] = __uint_as_float(b.code); hrec[2][hp] = b.u; hrec[3][hp] = b.v; hsrc[hp] = tid; }
+        __syncthreads();
+        // ---- (B) shade the dense hits
+        bool cont = false;
+        V3 np = mk(0, 0, 0), ndir = np, beta = np; uint32_t key = 0, sb = 0;
+        if (tid < n_hits) {
+            const int e = hsrc[tid];
+            const V3 o = mk(pool[cur][0][e], pool[cur][1][e], pool[cur][2][e]);
+            const V3 d = mk(pool[cur][3][e], pool[cur][4][e], pool[cur][5][e]);
+            beta = mk(pool[cur][6][e], pool[cur][7][e], pool[cur][8][e]);
+            key = __float_as_uint(pool[cur][9][e]); sb = __float_as_uint(pool[cur][10][e]);
+            V3 L;
+            cont = shade_segment<FAST>(sc, o, d, key, (int)(sb & 31u), max_depth, hrec[0][tid], __float_as_uint(hrec[1][tid]), hrec[2][tid],
+                                       hrec[3][tid], beta, np, ndir, L);
+            if (!cont) put_contrib(sc, contrib, sb >> 5, L);
+        }
+        // ---- (C) survivors into the other pool buffer
+        int n_cont;
+        const int cp = pack(cont, n_cont);
+        if (cont) {
+            const int nx = cur ^ 1;
+            pool[nx][0][cp] = np.x; pool[nx][1][cp] = np.y; pool[nx][2][cp] = np.z;
+            pool[nx][3][cp] = ndir.x; pool[nx][4][cp] = ndir.y; pool[nx][5][cp] = ndir.z;
+            pool[nx][6][cp] = beta.x; pool[nx][7][cp] = beta.y; pool[nx][8][cp] = beta.z;
+            pool[nx][9][cp] = __uint_as_float(key); pool[nx][10][cp] = __uint_as_float(sb + 1u);
+        }
+        cur ^= 1; pool_n = n_cont;
+        __syncthreads();
+    }
+    if (COUNT) {
+        for (int o = 16; o > 0; o >>= 1) { nn += __shfl_xor_sync(0xffffffffu, nn, o); npr += __shfl_xor_sync(0xffffffffu, npr, o); }
+        if (lane == 0 && (nn | npr)) {
+            atomicAdd(&stats[PRT_MAX_DEPTH + 0], (unsigned long long)nn);
+            atomicAdd(&stats[PRT_MAX_DEPTH + 1], (unsigned long long)npr);
+        }
+    }
+    __syncthreads();
+    for (int k = tid; k < PRT_MAX_DEPTH; k += WF_THREADS)
+        if (rays_at[k]) atomicAdd(&stats[k], (unsigned long long)rays_at[k]);
+}
+
 // ------------------------------------------------------------------ resolve (accumulate)
 // accum[3p+c] += sum over the wave's samples, in sample order (Film::AddSample, film.cu:37-55)
 __global__ void __launch_bounds__(WF_THREADS)
@@ -1179,6 +1307,13 @@ int wavefront_render(Ctx* c, int spp, int max_depth, uint64_t seed, int sample_b
                                                   : (brute && fused ? k_tail<false, true, false, true> : tw ? k_tail<false, false, true, true> : k_tail<false, false, false, true>))
                                 : (c->counters_on ? (brute && fused ? k_tail<true, true, false, false> : tw ? k_tail<true, false, true, false> : k_tail<true, false, false, false>)
                                                   : (brute && fused ? k_tail<false, true, false, false> : tw ? k_tail<false, false, true, false> : k_tail<false, false, false, false>));
+                if (fused && c->tail_pool) {                          // block-local wavefront (scenes of the fused path)
+                    auto kp = fastm ? (c->counters_on ? (brute ? k_tail_pool<true, true, true> : k_tail_pool<true, false, true>)
+                                                      : (brute ? k_tail_pool<false, true, true> : k_tail_pool<false, false, true>))
+                                    : (c->counters_on ? (brute ? k_tail_pool<true, true, false> : k_tail_pool<true, false, false>)
+                                                      : (brute ? k_tail_pool<false, true, false> : k_tail_pool<false, false, false>));
+                    kp<<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], qb[cur], contrib, qcount, tail_b, max_depth, dstats);
+                } else
                 kt<<<grid, WF_THREADS, 0, st>>>(sc, qo[cur], qd[cur], qb[cur], contrib, qcount, tail_b, max_depth, dstats);
                 if (timing) stamp(st);
                 ++launches;

@@ -518,6 +518,7 @@ __global__ void k_gather_tris(int n, int ns, int nq, int tri_prim_base, const ui
 // round fits one tile, CTA 0 finishes alone with __syncthreads(). Everything another CTA wrote is read with ld.cg.
 constexpr int PL_THREADS = 256, PL_ITEMS = 4, PL_TILE = PL_THREADS * PL_ITEMS, PL_RMAX = 8;
 constexpr int PL_SPAN = PL_TILE + 4 * PL_RMAX;
+constexpr int PL_LOAD_TRIPS = (PL_SPAN + PL_THREADS - 1) / PL_THREADS;
 constexpr int PL_SMALL_ROUND = 160 << 10;   // rounds with at most this many clusters use 256-cluster tiles (one per thread)
 constexpr int PL_MAX_ROUNDS = 192;          // a round may merge a single pair (nested boxes): give up, Karras takes over
 constexpr int PL_MAX_HEIGHT = 84;           // 3 * height + 1 <= 256 stack entries (wavefront.cu STACK_TOTAL)
@@ -586,12 +587,28 @@ k_ploc(int n, int R_, int ns, int nq, const uint32_t* __restrict__ sorted_prim, 
             const int t = s_tile;
             if (t >= ntiles) break;
             const int t0 = t * tile, lo = t0 - 2 * R;        // global position of shared slot 0
-            for (int k = tid; k < tile + 4 * R; k += PL_THREADS) {
-                const int g = lo + k;
-                if (g >= 0 && g < c) {
-                    s_min[k] = __ldcg(&bin[2 * (size_t)g]); s_max[k] = __ldcg(&bin[2 * (size_t)g + 1]);
-                    s_code[k] = round == 0 ? ~g : __ldcg(&cin[g]);
+            // The tile's boxes go global -> shared with cp.async (L2 only: other CTAs wrote them last round), all in flight at
+            // once; as a load/store loop each of its five trips waited for its own DRAM round trip before the next began.
+            {
+                int codes[PL_LOAD_TRIPS];
+#pragma unroll
+                for (int it = 0; it < PL_LOAD_TRIPS; ++it) {
+                    const int k = tid + it * PL_THREADS, g = lo + k;
+                    codes[it] = 0;
+                    if (k < tile + 4 * R && g >= 0 && g < c) {
+                        const unsigned dmin = (unsigned)__cvta_generic_to_shared(&s_min[k]), dmax = (unsigned)__cvta_generic_to_shared(&s_max[k]);
+                        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dmin), "l"(bin + 2 * (size_t)g) : "memory");
+                        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dmax), "l"(bin + 2 * (size_t)g + 1) : "memory");
+                        codes[it] = round == 0 ? ~g : __ldcg(&cin[g]);
+                    }
                 }
+#pragma unroll
+                for (int it = 0; it < PL_LOAD_TRIPS; ++it) {
+                    const int k = tid + it * PL_THREADS;
+                    if (k < tile + 4 * R) s_code[k] = codes[it];
+                }
+                asm volatile("cp.async.commit_group;" ::: "memory");
+                asm volatile("cp.async.wait_group 0;" ::: "memory");
             }
             __syncthreads();
             // nearest neighbour of every cluster of the tile and of R more on either side (their choice decides "mutual")

@@ -424,7 +424,8 @@ def result_json(args, R):
     cont = rays_step - paths_step                      # segments that continued into another bounce
     fused = R["shd_ms"] == 0.0
     # ALGORITHMIC bytes: B_ray = B_queue + B_shade + 64*n_node + 48*n_leaf.
-    #   staged: extend 32 in + 16 hit out; shade 32+16+16 in, 48 out per continuing ray, 16 out per finished path
+    #   staged: extend 32 in (bounce >= 1 only) + 16 hit out; shade 48 in (bounce >= 1 only) + 16 hit in, 48 out per continuing ray,
+    #           16 out per finished path
     #   fused : no hit queue and no queue traffic for camera rays: 48 in per bounce>=1 ray, 48 out per continuing
     #           ray, 16 out per finished path
     b_shade = 64 if sd.n_tris > (len(sd.spheres) + len(sd.quads)) else 16
@@ -433,7 +434,8 @@ def result_json(args, R):
         queue_bytes = cont * 48 + cont * 48 + paths_step * 16
         kname = "k_primary + k_bounce (fused raygen/extend/shade/compaction, warp-uniform list loop)"
     else:
-        queue_bytes = rays_step * (32 + 16) + rays_step * 64 + cont * 48 + paths_step * 16 + paths_step * 48
+        # camera rays (bounce 0) never touch a queue: the bounce-0 extend / shade kernels compute them from the path index
+        queue_bytes = cont * 32 + rays_step * 16 + cont * 48 + rays_step * 16 + cont * 48 + paths_step * 16
         wide = sd.n_prims >= 4096 and not any(o.startswith("bvh_wide=0") for o in args.opt)
         kname = ("k_extend_wide + k_shade (persistent traversal of the 4-wide quantised nodes, shade/compaction)" if wide else
                  "k_extend_pt + k_shade (persistent two-child BVH traversal, shade/compaction)")

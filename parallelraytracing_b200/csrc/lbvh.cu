@@ -492,12 +492,13 @@ __global__ void k_gather_tris(int n, int ns, int nq, int tri_prim_base, const ui
     if (q < ns + nq) { leaf_box[2 * (size_t)pos] = prim_box[2 * (size_t)q]; leaf_box[2 * (size_t)pos + 1] = prim_box[2 * (size_t)q + 1]; return; }
     int t = q - ns - nq;
     // one 96-byte input record per triangle (positions, material in v1.w, normals): one random gather instead of three
-    float4 a = in_v[6 * (size_t)t], b = in_v[6 * (size_t)t + 1], c = in_v[6 * (size_t)t + 2];
+    float4 a, b, c, n0, n1, n2;                                          // 3 x 256-bit loads of the 96-byte record
+    ldg8(&in_v[6 * (size_t)t], a, b); ldg8(&in_v[6 * (size_t)t + 2], c, n0); ldg8(&in_v[6 * (size_t)t + 4], n1, n2);
     leaf_box[2 * (size_t)pos] = make_float4(fminf(fminf(a.x, b.x), c.x), fminf(fminf(a.y, b.y), c.y), fminf(fminf(a.z, b.z), c.z), 0.f);
     leaf_box[2 * (size_t)pos + 1] = make_float4(fmaxf(fmaxf(a.x, b.x), c.x), fmaxf(fmaxf(a.y, b.y), c.y), fmaxf(fmaxf(a.z, b.z), c.z), 0.f);
     a.w = __int_as_float(tri_prim_base + t); c.w = 0.f;
     out_v[3 * pos] = a; out_v[3 * pos + 1] = b; out_v[3 * pos + 2] = c;
-    out_n[3 * pos] = in_n[6 * (size_t)t]; out_n[3 * pos + 1] = in_n[6 * (size_t)t + 1]; out_n[3 * pos + 2] = in_n[6 * (size_t)t + 2];
+    out_n[3 * pos] = n0; out_n[3 * pos + 1] = n1; out_n[3 * pos + 2] = n2;
 }
 
 // ------------------------------------------------------------------ PLOC: the tree-quality pass
@@ -724,17 +725,17 @@ k_ploc(int n, int R_, int ns, int nq, const uint32_t* __restrict__ sorted_prim, 
                     nd.lmax = make_float4(a1.x, a1.y, a1.z, __int_as_float(cj < 0 ? leaf_code(~cj, (uint32_t)qj, ns, nq) : cj));
                     nd.rmin = make_float4(b0.x, b0.y, b0.z, 0.f);
                     nd.rmax = make_float4(b1.x, b1.y, b1.z, 0.f);
-                    nodes[id] = nd;
+                    stg8(&nodes[id].lmin, nd.lmin, nd.lmax); stg8(&nodes[id].rmin, nd.rmin, nd.rmax);
                     *reinterpret_cast<int2*>(children + 2 * (size_t)id) = make_int2(ci, cj);
                     if (ci >= 0) parent[ci] = id;
                     if (cj >= 0) parent[cj] = id;
                     if (id == 0) { parent[0] = -1; ctl[PC_HEIGHT] = h; }
                     __stcg(&cout[pos], id);
-                    __stcg(&bout[2 * pos], make_float4(fminf(a0.x, b0.x), fminf(a0.y, b0.y), fminf(a0.z, b0.z), __int_as_float(h)));
-                    __stcg(&bout[2 * pos + 1], make_float4(fmaxf(a1.x, b1.x), fmaxf(a1.y, b1.y), fmaxf(a1.z, b1.z), 0.f));
+                    stg8(&bout[2 * pos], make_float4(fminf(a0.x, b0.x), fminf(a0.y, b0.y), fminf(a0.z, b0.z), __int_as_float(h)),
+                         make_float4(fmaxf(a1.x, b1.x), fmaxf(a1.y, b1.y), fmaxf(a1.z, b1.z), 0.f));
                     run += 0x10000u;
                 } else {
-                    __stcg(&cout[pos], s_code[k]); __stcg(&bout[2 * pos], s_min[k]); __stcg(&bout[2 * pos + 1], s_max[k]);
+                    __stcg(&cout[pos], s_code[k]); stg8(&bout[2 * pos], s_min[k], s_max[k]);
                 }
                 run += 1u;
             }
@@ -790,7 +791,8 @@ __global__ void k_emit_wide(int n_internal, const int* __restrict__ parent, cons
     (void)parent;
     float lo[4][3], hi[4][3]; int code[4]; int ns = 2;
     {
-        const BvhNode nd = nodes[i];
+        BvhNode nd;                                                      // 2 x 256-bit loads: every 32-byte sector is requested once
+        ldg8(&nodes[i].lmin, nd.lmin, nd.lmax); ldg8(&nodes[i].rmin, nd.rmin, nd.rmax);
         lo[0][0] = nd.lmin.x; lo[0][1] = nd.lmin.y; lo[0][2] = nd.lmin.z; hi[0][0] = nd.lmax.x; hi[0][1] = nd.lmax.y; hi[0][2] = nd.lmax.z;
         lo[1][0] = nd.rmin.x; lo[1][1] = nd.rmin.y; lo[1][2] = nd.rmin.z; hi[1][0] = nd.rmax.x; hi[1][1] = nd.rmax.y; hi[1][2] = nd.rmax.z;
         code[0] = __float_as_int(nd.lmin.w); code[1] = __float_as_int(nd.lmax.w);
@@ -806,7 +808,8 @@ __global__ void k_emit_wide(int n_internal, const int* __restrict__ parent, cons
         if (s >= 0) {
             const int cs = s == 0 ? code[0] : s == 1 ? code[1] : code[2];
             if (!PRT_CHECK(cs < n_internal, PRT_CHK_REFIT)) break;
-            const BvhNode ch = nodes[cs];
+            BvhNode ch;
+            ldg8(&nodes[cs].lmin, ch.lmin, ch.lmax); ldg8(&nodes[cs].rmin, ch.rmin, ch.rmax);
             if (s == 0) open_slot<0>(lo, hi, code, ns, ch);
             else if (s == 1) open_slot<1>(lo, hi, code, ns, ch);
             else open_slot<2>(lo, hi, code, ns, ch);
@@ -842,7 +845,10 @@ __global__ void k_emit_wide(int n_internal, const int* __restrict__ parent, cons
     w.sx = sc[0] * 32768.0f; w.sy = sc[1] * 32768.0f; w.sz = sc[2] * 32768.0f;
 #pragma unroll
     for (int c = 0; c < 4; ++c) w.code[c] = c < ns ? code[c] : code[0];
-    wide[i] = w;
+    stg8(&wide[i], make_float4(w.ox, w.oy, w.oz, w.sx),
+         make_float4(__int_as_float(w.code[0]), __int_as_float(w.code[1]), __int_as_float(w.code[2]), __int_as_float(w.code[3])));
+    stg8(reinterpret_cast<char*>(&wide[i]) + 32, make_float4(__uint_as_float(w.qlo[0]), __uint_as_float(w.qlo[1]), __uint_as_float(w.qlo[2]), __uint_as_float(w.qhi[0])),
+         make_float4(__uint_as_float(w.qhi[1]), __uint_as_float(w.qhi[2]), w.sy, w.sz));
 }
 
 unsigned lbvh_check_flags() {

@@ -136,6 +136,22 @@ PRT_DEV V3 rng_unit_vector(Rng& r) {
     }
 }
 
+// 256-bit read-only load (sm_100 LDG.E.256): a divergent node fetch costs one L1 wavefront per 128-byte
+// line per INSTRUCTION, so 2 x 32 B instead of 4 x 16 B halves the L1tex work of a 64-byte BVH node.
+PRT_DEV void ldg8(const void* p, float4& a, float4& b) {
+    unsigned r0, r1, r2, r3, r4, r5, r6, r7;
+    asm("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3), "=r"(r4), "=r"(r5), "=r"(r6), "=r"(r7) : "l"(p));
+    a = make_float4(__uint_as_float(r0), __uint_as_float(r1), __uint_as_float(r2), __uint_as_float(r3));
+    b = make_float4(__uint_as_float(r4), __uint_as_float(r5), __uint_as_float(r6), __uint_as_float(r7));
+}
+// 256-bit store (sm_100 STG.E.256); p must be 32-byte aligned
+PRT_DEV void stg8(void* p, float4 a, float4 b) {
+    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" :: "l"(p),
+                 "r"(__float_as_uint(a.x)), "r"(__float_as_uint(a.y)), "r"(__float_as_uint(a.z)), "r"(__float_as_uint(a.w)),
+                 "r"(__float_as_uint(b.x)), "r"(__float_as_uint(b.y)), "r"(__float_as_uint(b.z)), "r"(__float_as_uint(b.w)) : "memory");
+}
+
 // ------------------------------------------------------------------ scene records
 // Device layouts (16-byte planes, fetched with 128-bit loads).
 struct SphereRec { float4 a; float4 b; };          // a={c.xyz, r}  b={tmin, mat, prim_id, 0}

@@ -36,15 +36,6 @@ static __device__ int g_prt_stack_limit = STACK_TOTAL;   // option check_stack_l
 
 // queue entry: O = {o.xyz, bits(slot<<5 | bounce)}, D = {d.xyz, bits(path_key)}, B = {beta.rgb, 0}
 __device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
-// 256-bit read-only load (sm_100 LDG.E.256): a divergent node fetch costs one L1 wavefront per 128-byte
-// line per INSTRUCTION, so 2 x 32 B instead of 4 x 16 B halves the L1tex work of a 64-byte BVH node.
-__device__ __forceinline__ void ldg8(const void* p, float4& a, float4& b) {
-    unsigned r0, r1, r2, r3, r4, r5, r6, r7;
-    asm("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-        : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3), "=r"(r4), "=r"(r5), "=r"(r6), "=r"(r7) : "l"(p));
-    a = make_float4(__uint_as_float(r0), __uint_as_float(r1), __uint_as_float(r2), __uint_as_float(r3));
-    b = make_float4(__uint_as_float(r4), __uint_as_float(r5), __uint_as_float(r6), __uint_as_float(r7));
-}
 // streaming (read-once / write-once) queue traffic: bypass L1, do not pollute it for the BVH
 __device__ __forceinline__ float4 ld_stream(const float4* p) { return __ldcs(p); }
 __device__ __forceinline__ void st_stream(float4* p, float4 v) { __stcs(p, v); }

@@ -248,6 +248,22 @@ int  prt_resolve_display(prt_ctx* ctx, float exposure, float gamma, uint8_t* hos
  * quantised nodes the render path uses (same hits, fewer node visits). */
 int  prt_trace_batch(prt_ctx* ctx, const prt_ray* rays, int n, prt_hit* out, int use_bvh);
 
+/* prt_trace_batch for callers that cannot allocate (stream capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * NO COUNTERPART IN THE REFERENCE. Same kernels and the same hit records, bit
+ * for bit, as prt_trace_batch, but
+ *   - rays_dev / out_dev are DEVICE-accessible pointers of the caller's (device memory of the context's device, or pinned /
+ *     managed memory the GPU can address); the kernels read and write them directly, nothing is copied;
+ *   - the scratch (ray queue, hit plane, counters) is a static device array of the library, sized for at most
+ *     PRT_TRACE_STATIC_MAX_RAYS rays (3 MB + 1 KB, held by every GPU that loads the library until the process exits);
+ *     n above that returns PRT_ERR_INVALID with a message, n = 0 only resolves the array's address (the once-per-device set-up);
+ *   - no cudaMalloc / cudaFree / allocating routine is called, prt_stats is not updated;
+ *   - cuda_stream is the cudaStream_t to enqueue on (NULL = the context's render stream). The call waits for that stream
+ *     before it returns, unless the stream is being captured, in which case the chain is only recorded.
+ * Every call on one GPU shares the one array: calls that overlap on the GPU (two streams, two contexts, two graph launches
+ * in flight) race on it - serialise them. A multi-device context traces on its root device. */
+#define PRT_TRACE_STATIC_MAX_RAYS 65536
+int  prt_trace_batch_static(prt_ctx* ctx, const prt_ray* rays_dev, int n, prt_hit* out_dev, int use_bvh, void* cuda_stream);
+
 /* MaterialHandle::{Emit,Scatter} known answers (src/core/material.h:11-161, math.h:10-50) through the device function the
  * render path shades with. Record k: material mats[k], incoming unit direction in_dirs[3k..], hit normal facing the ray
  * normals[3k..], IsFrontFace fronts[k], RNG stream of (seed, pixel = keys[3k], sample = keys[3k+1], bounce = keys[3k+2]).

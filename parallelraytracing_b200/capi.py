@@ -47,7 +47,7 @@ class PrtError(RuntimeError):
 EXPORTS = [
     "prt_create", "prt_create_multi", "prt_destroy", "prt_last_error", "prt_version", "prt_set_scene", "prt_build_bvh",
     "prt_set_camera", "prt_render", "prt_render_fresh", "prt_render_region", "prt_wait_event", "prt_clear_accum", "prt_scale_accum", "prt_accum_device_ptr",
-    "prt_set_accum_buffer", "prt_read_accum", "prt_accum_spp", "prt_set_accum_spp", "prt_resolve_display", "prt_trace_batch",
+    "prt_set_accum_buffer", "prt_read_accum", "prt_accum_spp", "prt_set_accum_spp", "prt_resolve_display", "prt_trace_batch", "prt_trace_batch_static",
     "prt_debug_lbvh", "prt_debug_wide", "prt_debug_scatter", "prt_debug_ploc_trace", "prt_debug_check_flags", "prt_host_alloc", "prt_host_free", "prt_num_prims", "prt_enable_counters", "prt_get_stats", "prt_set_option",
 ]
 
@@ -98,6 +98,7 @@ def load_library():
     lib.prt_set_accum_spp.argtypes = [vp, i32]
     lib.prt_resolve_display.argtypes = [vp, f32, f32, vp]
     lib.prt_trace_batch.argtypes = [vp, vp, i32, vp, i32]
+    lib.prt_trace_batch_static.argtypes = [vp, vp, i32, vp, i32, vp]
     lib.prt_debug_lbvh.argtypes = [vp, vp, vp, vp, vp, vp, vp]
     lib.prt_debug_wide.argtypes = [vp, vp]
     lib.prt_debug_scatter.argtypes = [vp, vp, vp, vp, vp, vp, u64, i32, vp]
@@ -245,6 +246,11 @@ class Context:
         out = np.zeros(len(rays), dtype=hit_dt)
         self._check(self.lib.prt_trace_batch(self.h, _ptr(rays), len(rays), _ptr(out), int(use_bvh)), "prt_trace_batch")
         return out
+
+    def trace_batch_static(self, rays_dev, n, out_dev, use_bvh=2, stream=None):
+        """prt_trace_batch_static: device pointers (ints) of n prt_ray records in and n prt_hit records out; allocates nothing."""
+        self._check(self.lib.prt_trace_batch_static(self.h, C.c_void_p(rays_dev), int(n), C.c_void_p(out_dev), int(use_bvh),
+                                                    C.c_void_p(stream)), "prt_trace_batch_static")
 
     def num_prims(self):
         return self.lib.prt_num_prims(self.h)

@@ -15,6 +15,8 @@
 #include "prt_internal.h"
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
+#include <mutex>
 
 namespace prt {
 
@@ -1546,3 +1548,95 @@ int film_resolve_display(Ctx* c, float exposure, float gamma, uint8_t* host_rgba
 }
 
 }  // namespace prt
+
+// ------------------------------------------------------------------ closest-hit batch without any allocation
+// prt_trace_batch_static (prt.h): the kernel chain of wavefront_trace_batch (k_load_rays -> extend -> k_hit_records, the same
+// kernels, hence the same bits) with its scratch - the SoA ray queue, the hit plane and the queue / work counters - in a
+// file-scope device array instead of context buffers that grow through cudaMalloc. The array exists once per GPU that
+// loads the library (3 MB + 1 KB, held until the process exits), every call on that GPU shares it and it keeps the last
+// call's contents: the counters are cleared by every call, the planes are fully overwritten for [0, n) before they are read.
+namespace prt {
+constexpr int    NOALLOC_MAX_RAYS  = PRT_TRACE_STATIC_MAX_RAYS;
+constexpr size_t NOALLOC_CTR_BYTES = 1024;                                       // qcount + work (272 B) | counters (288 B at +512)
+constexpr size_t NOALLOC_BYTES     = NOALLOC_CTR_BYTES + (size_t)NOALLOC_MAX_RAYS * 3 * sizeof(float4);
+static_assert(2 * (PRT_MAX_DEPTH + 2) * 4 <= 512 && (PRT_MAX_DEPTH + 4) * 8 <= 512, "counter block of the static scratch");
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_BYTES];
+
+// In host code `g_noalloc_scratch` is only a handle of the symbol, not a device address: the address each device maps it at
+// comes from cudaGetSymbolAddress with that device current, once per device.
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static unsigned char* g_noalloc_ptr[NOALLOC_MAX_DEVICES];
+static std::mutex g_noalloc_mu;
+
+static int noalloc_scratch(Ctx* c, unsigned char** out) {
+    if (c->device < 0 || c->device >= NOALLOC_MAX_DEVICES) return set_err(c, PRT_ERR_INVALID, "prt_trace_batch_static: device ordinal out of range");
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[c->device]) {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);             // c->device is current (set by the caller)
+        if (e != cudaSuccess || !p) {
+            cudaGetLastError();
+            return set_err(c, PRT_ERR_CUDA, std::string("prt_trace_batch_static: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+        }
+        g_noalloc_ptr[c->device] = (unsigned char*)p;
+    }
+    *out = g_noalloc_ptr[c->device];
+    return PRT_OK;
+}
+
+static int trace_batch_static(Ctx* c, const prt_ray* d_rays, int n, prt_hit* d_out, int use_bvh, cudaStream_t st) {
+    unsigned char* base = nullptr;
+    int rc;
+    if ((rc = noalloc_scratch(c, &base))) return rc;
+    if (n == 0) return PRT_OK;                                                   // set-up only
+    uint32_t* qcount = (uint32_t*)base;
+    uint32_t* work = qcount + (PRT_MAX_DEPTH + 2);
+    unsigned long long* dstats = (unsigned long long*)(base + 512);
+    float4* qo = (float4*)(base + NOALLOC_CTR_BYTES);
+    float4* qd = qo + NOALLOC_MAX_RAYS;
+    float4* hits = qd + NOALLOC_MAX_RAYS;
+    SceneView sc = scene_view(c);
+    PRT_CUDA(c, cudaMemsetAsync(base, 0, NOALLOC_CTR_BYTES, st));                // counters must start at zero
+    const int G = (n + WF_THREADS - 1) / WF_THREADS;
+    k_load_rays<<<G, WF_THREADS, 0, st>>>(d_rays, n, qo, qd, qcount);
+    const int grid = std::min(G, c->num_sms * c->ctas_per_sm);
+    if (use_bvh == 2 && sc.wnodes != nullptr && c->n_prims > 1) {
+        int per_sm = 4;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_extend_wide<false>, WF_THREADS, 0);
+        k_extend_wide<false><<<std::max(1, c->num_sms * std::max(1, per_sm)), WF_THREADS, 0, st>>>(
+            sc, qo, qd, hits, qcount, work, 0, c->pt_refill_wide, dstats, PrimaryGen{});
+    } else if (use_bvh && c->persistent) {
+        int per_sm = 4;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_extend_pt<false>, WF_THREADS, 0);
+        k_extend_pt<false><<<std::max(1, c->num_sms * std::max(1, per_sm)), WF_THREADS, 0, st>>>(
+            sc, qo, qd, hits, qcount, work, 0, c->pt_refill, dstats, PrimaryGen{});
+    } else if (use_bvh) {
+        k_extend<false><<<grid, WF_THREADS, 0, st>>>(sc, qo, qd, hits, qcount, 0, dstats);
+    } else {
+        k_extend_brute<<<grid, WF_THREADS, 0, st>>>(sc, (const uint32_t*)c->vals[c->sorted_slot].p, qo, qd, hits, qcount, 0);
+    }
+    k_hit_records<<<G, WF_THREADS, 0, st>>>(sc, qo, qd, hits, n, d_out);
+    PRT_CUDA(c, cudaGetLastError());
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    PRT_CUDA(c, cudaStreamIsCapturing(st, &cap));
+    if (cap == cudaStreamCaptureStatusNone) PRT_CUDA(c, cudaStreamSynchronize(st));   // a capturing stream only records the chain
+    return PRT_OK;
+}
+}  // namespace prt
+
+extern "C" int prt_trace_batch_static(prt_ctx* ctx, const prt_ray* rays_dev, int n, prt_hit* out_dev, int use_bvh, void* cuda_stream) {
+    using namespace prt;
+    if (!ctx || (n > 0 && (!rays_dev || !out_dev))) return set_err(ctx ? &ctx->c : nullptr, PRT_ERR_INVALID, "prt_trace_batch_static: NULL argument");
+    Ctx* c = &ctx->c;
+    if (n < 0) return set_err(c, PRT_ERR_INVALID, "prt_trace_batch_static: negative ray count");
+    if (n > NOALLOC_MAX_RAYS) {
+        char buf[160];
+        snprintf(buf, sizeof buf, "prt_trace_batch_static: %d rays exceed the static scratch (PRT_TRACE_STATIC_MAX_RAYS = %d); split the batch or use prt_trace_batch",
+                 n, NOALLOC_MAX_RAYS);
+        return set_err(c, PRT_ERR_INVALID, buf);
+    }
+    if (use_bvh < 0 || use_bvh > 2) return set_err(c, PRT_ERR_INVALID, "prt_trace_batch_static: use_bvh must be 0, 1 or 2");
+    if (!c->scene_set || !c->bvh_built) return set_err(c, PRT_ERR_INVALID, "prt_trace_batch_static: scene/BVH not ready");
+    PRT_CUDA(c, cudaSetDevice(c->device));
+    return trace_batch_static(c, rays_dev, n, out_dev, use_bvh, cuda_stream ? (cudaStream_t)cuda_stream : c->stream);
+}

@@ -395,10 +395,12 @@ void build_lbvh(Scene& sc) {
 }
 
 inline float safe_inv(float d) { float a = fabsf(d) < 1e-20f ? copysignf(1e-20f, d) : d; return 1.0f / a; }
-inline float isect_box(V3 o, V3 inv, V3 mn, V3 mx, float tmax) {
-    float x0 = (mn.x - o.x) * inv.x, x1 = (mx.x - o.x) * inv.x;
-    float y0 = (mn.y - o.y) * inv.y, y1 = (mx.y - o.y) * inv.y;
-    float z0 = (mn.z - o.z) * inv.z, z1 = (mx.z - o.z) * inv.z;
+/* Slab test of the two-child walk (prt_device.cuh:isect_box). pad is 0 except on axes the ray is parallel to (ray_pad below);
+ * fmaf with a zero addend is the rounded product, so every other ray keeps the bits of (m - o) * inv. */
+inline float isect_box(V3 o, V3 inv, V3 pad, V3 mn, V3 mx, float tmax) {
+    float x0 = fmaf(mn.x - o.x, inv.x, -pad.x), x1 = fmaf(mx.x - o.x, inv.x, pad.x);
+    float y0 = fmaf(mn.y - o.y, inv.y, -pad.y), y1 = fmaf(mx.y - o.y, inv.y, pad.y);
+    float z0 = fmaf(mn.z - o.z, inv.z, -pad.z), z1 = fmaf(mx.z - o.z, inv.z, pad.z);
     float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.0f));
     float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), tmax));
     tf = tf * 1.00000047683715820312f;
@@ -407,6 +409,25 @@ inline float isect_box(V3 o, V3 inv, V3 mn, V3 mx, float tmax) {
 inline void child_box(const Scene& sc, int ch, V3& mn, V3& mx) {
     if (ch < 0) { uint32_t q = sc.sorted_prim[~ch]; mn = sc.amin[q]; mx = sc.amax[q]; }
     else { mn = sc.node_min[ch]; mx = sc.node_max[ch]; }
+}
+
+/* prt_device.cuh:make_raybox - a ray parallel to a slab (|d_k| < 1e-20, inv = +-1e20) that lies exactly in one of its planes
+ * would "leave at t = 0"; on such axes the slab products are loosened by P = twice the largest t a point of the scene box
+ * (the union of the root's two child boxes) can have on the ray's dominant axis */
+inline V3 ray_pad(const Scene& sc, V3 o, V3 d, V3 inv) {
+    V3 pad = mk(0.0f, 0.0f, 0.0f);
+    const float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
+    if ((ax < 1e-20f || ay < 1e-20f || az < 1e-20f) && sc.n_prims() > 1) {
+        V3 lmn, lmx, rmn, rmx;
+        child_box(sc, sc.children[0], lmn, lmx); child_box(sc, sc.children[1], rmn, rmx);
+        const float ex = fmaxf(fabsf(fminf(lmn.x, rmn.x) - o.x), fabsf(fmaxf(lmx.x, rmx.x) - o.x));
+        const float ey = fmaxf(fabsf(fminf(lmn.y, rmn.y) - o.y), fabsf(fmaxf(lmx.y, rmx.y) - o.y));
+        const float ez = fmaxf(fabsf(fminf(lmn.z, rmn.z) - o.z), fabsf(fmaxf(lmx.z, rmx.z) - o.z));
+        float P = (ax >= ay && ax >= az) ? ex * fabsf(inv.x) : (ay >= az ? ey * fabsf(inv.y) : ez * fabsf(inv.z));
+        P = fminf(P * 2.0f, 1e30f);
+        pad = mk(ax < 1e-20f ? copysignf(P, inv.x) : 0.0f, ay < 1e-20f ? copysignf(P, inv.y) : 0.0f, az < 1e-20f ? copysignf(P, inv.z) : 0.0f);
+    }
+    return pad;
 }
 
 /* deepest traversal stack any ray needed since the last reset, in entries of the DEVICE stack (its DONE sentinel included):
@@ -421,6 +442,7 @@ Hit closest_bvh(const Scene& sc, V3 o, V3 d, uint64_t* n_nodes, uint64_t* n_test
     int n = sc.n_prims();
     if (n == 0) return h;
     V3 inv = mk(safe_inv(d.x), safe_inv(d.y), safe_inv(d.z));
+    V3 pad = ray_pad(sc, o, d, inv);
     Shear rs = make_shear(d);
     V3 dn = normalize(d);
     int stack[512]; int sp = 0;
@@ -432,8 +454,8 @@ Hit closest_bvh(const Scene& sc, V3 o, V3 d, uint64_t* n_nodes, uint64_t* n_test
             int cl = sc.children[2 * cur], cr = sc.children[2 * cur + 1];
             V3 lmn, lmx, rmn, rmx;
             child_box(sc, cl, lmn, lmx); child_box(sc, cr, rmn, rmx);
-            float tl = isect_box(o, inv, lmn, lmx, h.t);
-            float tr = isect_box(o, inv, rmn, rmx, h.t);
+            float tl = isect_box(o, inv, pad, lmn, lmx, h.t);
+            float tr = isect_box(o, inv, pad, rmn, rmx, h.t);
             if (tl >= 0.0f && tr >= 0.0f) {
                 int nearc = cl, farc = cr;
                 if (tr < tl) { nearc = cr; farc = cl; }

@@ -299,21 +299,40 @@ PRT_DEV float isect_tri(V3 v0, V3 v1, V3 v2, V3 o, const RayShear& rs, float tmi
 }
 
 // ------------------------------------------------------------------ ray/box (robust slab)
-struct RayBox { V3 o; V3 inv; };
+struct RayBox { V3 o; V3 inv; V3 pad; };           // pad: 0, except on axes the ray is parallel to (see make_raybox)
 PRT_DEV float safe_inv(float d) {
     float a = fabsf(d) < 1e-20f ? copysignf(1e-20f, d) : d;
     return 1.0f / a;
 }
-PRT_DEV RayBox make_raybox(V3 o, V3 d) {
-    RayBox r; r.o = o; r.inv = mk(safe_inv(d.x), safe_inv(d.y), safe_inv(d.z)); return r;
+// A ray PARALLEL to a slab (direction component 0: inv = +-1e20) that lies exactly in one of the slab's planes gets the
+// product 0 there - "leaves at t = 0" - although it stays in the closed slab for every t: an axis-parallel ray through a vertex
+// that is the extreme of its box was culled, while the list loop (the reference's algorithm, primitive.cpp:21-59) reports
+// the hit (found by tests/test_fuzz_parity.py). On such an axis the two slab products are therefore loosened by P in t
+// (isect_box adds it inside the FMA that replaces the multiply: no instruction more), P = twice the largest t any point
+// of the scene box can have on the ray's dominant axis. In coordinates that is P * 1e-20: boxes the origin is strictly
+// outside of are culled as before. Every other ray has pad = 0 and the products keep their bits.
+PRT_DEV RayBox make_raybox(const SceneView& sc, V3 o, V3 d) {
+    RayBox r; r.o = o; r.inv = mk(safe_inv(d.x), safe_inv(d.y), safe_inv(d.z)); r.pad = mk(0.f, 0.f, 0.f);
+    const float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
+    if ((ax < 1e-20f || ay < 1e-20f || az < 1e-20f) && sc.n_prims > 1) {         // rare: exactly axis-parallel rays only
+        const float4 lmn = __ldg(&sc.nodes[0].lmin), lmx = __ldg(&sc.nodes[0].lmax);
+        const float4 rmn = __ldg(&sc.nodes[0].rmin), rmx = __ldg(&sc.nodes[0].rmax);
+        const float ex = fmaxf(fabsf(fminf(lmn.x, rmn.x) - o.x), fabsf(fmaxf(lmx.x, rmx.x) - o.x));
+        const float ey = fmaxf(fabsf(fminf(lmn.y, rmn.y) - o.y), fabsf(fmaxf(lmx.y, rmx.y) - o.y));
+        const float ez = fmaxf(fabsf(fminf(lmn.z, rmn.z) - o.z), fabsf(fmaxf(lmx.z, rmx.z) - o.z));
+        float P = (ax >= ay && ax >= az) ? ex * fabsf(r.inv.x) : (ay >= az ? ey * fabsf(r.inv.y) : ez * fabsf(r.inv.z));
+        P = fminf(P * 2.0f, 1e30f);
+        r.pad = mk(ax < 1e-20f ? copysignf(P, r.inv.x) : 0.f, ay < 1e-20f ? copysignf(P, r.inv.y) : 0.f, az < 1e-20f ? copysignf(P, r.inv.z) : 0.f);
+    }
+    return r;
 }
 // Returns entry distance (>=0) if the box [mn,mx] overlaps the ray within [0,tmax], else -1.
 // The far side is widened by 1+2^-21 (covers the <=3 ulp error of the three slab products),
 // so a primitive that the exact test would report is never culled by rounding.
 PRT_DEV float isect_box(const RayBox& r, float4 mn, float4 mx, float tmax) {
-    float x0 = (mn.x - r.o.x) * r.inv.x, x1 = (mx.x - r.o.x) * r.inv.x;
-    float y0 = (mn.y - r.o.y) * r.inv.y, y1 = (mx.y - r.o.y) * r.inv.y;
-    float z0 = (mn.z - r.o.z) * r.inv.z, z1 = (mx.z - r.o.z) * r.inv.z;
+    float x0 = fmaf(mn.x - r.o.x, r.inv.x, -r.pad.x), x1 = fmaf(mx.x - r.o.x, r.inv.x, r.pad.x);
+    float y0 = fmaf(mn.y - r.o.y, r.inv.y, -r.pad.y), y1 = fmaf(mx.y - r.o.y, r.inv.y, r.pad.y);
+    float z0 = fmaf(mn.z - r.o.z, r.inv.z, -r.pad.z), z1 = fmaf(mx.z - r.o.z, r.inv.z, r.pad.z);
     float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.0f));
     float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), tmax));
     tf = tf * 1.00000047683715820312f;

@@ -109,7 +109,7 @@ __device__ __forceinline__ Best traverse(const SceneView& sc, V3 o, V3 d, int* _
         if (COUNT) n_prims += (uint32_t)sc.n_prims;
         return best;
     }
-    RayBox rb = make_raybox(o, d);
+    RayBox rb = make_raybox(sc, o, d);
     RayShear rs; V3 dn = d;
     if (sc.n_tris > 0) rs = make_shear(d);            // per-ray triangle-test constants: only if there are triangles
     else { rs.kx = 0; rs.ky = 1; rs.kz = 2; rs.sx = rs.sy = rs.sz = 0.f; }
@@ -191,7 +191,7 @@ k_extend_pt(SceneView sc, const float4* __restrict__ qo, const float4* __restric
     uint32_t nn = 0, np = 0;
     bool have = false, exhausted = (sc.n_prims == 0);
     uint32_t idx = 0; V3 o = mk(0, 0, 0), d = o, dn = o; RayBox rb; RayShear rs; Best best; int cur = PRT_DONE, sp = 0;
-    rb.o = o; rb.inv = o; rs.kx = 0; rs.ky = 1; rs.kz = 2; rs.sx = rs.sy = rs.sz = 0.f; best_init(best);
+    rb.o = o; rb.inv = o; rb.pad = o; rs.kx = 0; rs.ky = 1; rs.kz = 2; rs.sx = rs.sy = rs.sz = 0.f; best_init(best);
     if (sc.n_prims == 0) {          // nothing to hit: every ray is a miss
         for (uint32_t i = blockIdx.x * WF_THREADS + threadIdx.x; i < count; i += gridDim.x * WF_THREADS)
             st_stream(&hits[i], make_float4(best.t, __uint_as_float(best.code), 0.f, 0.f));
@@ -209,7 +209,7 @@ k_extend_pt(SceneView sc, const float4* __restrict__ qo, const float4* __restric
                 if (idx < count) {
                     if (PRIM) { uint32_t key_; o = pg.cam.pos; primary_ray<PRIM == 2>(pg, idx, d, key_); }
                     else { float4 o4 = ld_stream(&qo[idx]), d4 = ld_stream(&qd[idx]); o = xyz(o4); d = xyz(d4); }
-                    rb = make_raybox(o, d);
+                    rb = make_raybox(sc, o, d);
                     if (sc.n_tris > 0) rs = make_shear(d);
                     dn = sc.n_spheres > 0 ? normalize(d) : d;
                     best_init(best);

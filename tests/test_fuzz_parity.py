@@ -1,0 +1,143 @@
+"""Seeded fuzz of the closest-hit path on small, nasty scenes: mixed spheres / quads / triangles with degenerate members
+(zero-area and needle triangles, exact duplicates, coplanar overlaps, boxes of zero thickness, 1e-4 .. 1e3 scale ratios) and
+rays that the slab / plane / watertight tests find awkward (exact-zero and negative-zero direction components, axis-parallel
+rays inside face planes, origins ON surfaces, rays through shared vertices and edges).
+  CPU (-m "not gpu"): the oracle's BVH walks (two-child, 4-wide) against its own brute-force list loop - the reference's
+       algorithm (primitive.cpp:21-59), which the pinned tests anchor - for both builders.
+  GPU (-m gpu): prt_trace_batch in all three modes against the oracle, byte for byte, counters included."""
+import numpy as np
+import pytest
+
+import util
+from parallelraytracing_b200 import scene as S
+from parallelraytracing_b200.capi import ray_dt
+
+SEEDS = list(range(16))
+
+
+def fuzz_scene(seed):
+    rng = np.random.default_rng(1000 + seed)
+    b = S.SceneBuilder("fuzz%d" % seed)
+    mats = [b.lambertian((0.7, 0.6, 0.5)), b.metal((0.8, 0.8, 0.8), 0.2), b.dielectric(1.5), b.emissive((3, 3, 3))]
+    ext = float(10.0 ** rng.uniform(-1, 2))                                    # scene size 0.1 .. 100
+    for _ in range(int(rng.integers(0, 12))):
+        r = ext * 10.0 ** rng.uniform(-3, -0.5)
+        b.add_sphere(r, mats[int(rng.integers(0, 4))], trans=tuple(rng.uniform(-ext, ext, 3)))
+    if seed % 3 == 0:                                                         # concentric and touching spheres
+        c = tuple(rng.uniform(-ext, ext, 3))
+        for k in range(3):
+            b.add_sphere(ext * 0.1 * (k + 1), mats[k], trans=c)
+    for _ in range(int(rng.integers(0, 8))):
+        b.add_quad(ext * rng.uniform(0.05, 1.0), ext * rng.uniform(0.05, 1.0), mats[int(rng.integers(0, 4))],
+                   euler=tuple(rng.choice([0.0, 90.0, 180.0, 37.0, -63.5], 3)), trans=tuple(rng.uniform(-ext, ext, 3)))
+    nt = int(rng.integers(1, 400))
+    c = rng.uniform(-ext, ext, (nt, 1, 3))
+    tv = c + rng.standard_normal((nt, 3, 3)) * ext * 10.0 ** rng.uniform(-3, -0.5, (nt, 1, 1))
+    k = max(nt // 8, 1)
+    tv[0:k, 2] = tv[0:k, 1]                                                   # zero area: two equal vertices
+    tv[k:2 * k, 2] = 0.5 * (tv[k:2 * k, 0] + tv[k:2 * k, 1])                  # zero area: collinear
+    m = min(k, max(nt - 3 * k, 0))
+    tv[2 * k:2 * k + m] = tv[3 * k:3 * k + m]                                 # exact duplicates: the lowest id wins
+    tv[4 * k:5 * k, :, 1] = np.float32(c[4 * k:5 * k, 0, 1:2])                # axis-aligned, flat boxes (y extent 0)
+    tv[5 * k:6 * k, 1] = tv[5 * k:6 * k, 0] + (tv[5 * k:6 * k, 1] - tv[5 * k:6 * k, 0]) * 1e-5   # needles
+    if seed % 2:                                                              # a fan sharing one vertex and its edges
+        apex = rng.uniform(-ext, ext, 3)
+        ring = apex + ext * 0.3 * np.stack([np.cos(np.arange(9) * 0.7), np.sin(np.arange(9) * 0.7), np.full(9, 0.4)], 1)
+        fan = np.stack([np.repeat(apex[None], 8, 0), ring[:-1], ring[1:]], 1)
+        tv = np.concatenate([tv, fan])
+    b.add_triangles(tv.astype(np.float32), None, rng.integers(0, 4, len(tv)).astype(np.int32))
+    if seed % 4 == 1:
+        b.add_quad(ext, ext, mats[0], trans=(0, -ext, 0))                      # a quad AFTER the triangle block of the list
+    return b.build(), ext, tv.astype(np.float32)
+
+
+def fuzz_rays(sd, ext, tv, seed, n=6000):
+    rng = np.random.default_rng(2000 + seed)
+    parts = [util.fixed_ray_batch(sd, n, seed=seed + 1), util.incoherent_rays(n, ext, seed=seed + 2)]
+    # rays with exact-zero / negative-zero components, some of them inside the planes of flat boxes
+    r = util.incoherent_rays(n, ext, seed=seed + 3)
+    axis = rng.integers(0, 3, n)
+    for a, f in enumerate(("dx", "dy", "dz")):
+        r[f][axis == a] = rng.choice(np.array([0.0, -0.0], np.float32), (axis == a).sum())
+    l = np.sqrt(r["dx"].astype(np.float64) ** 2 + r["dy"].astype(np.float64) ** 2 + r["dz"].astype(np.float64) ** 2)
+    for f in ("dx", "dy", "dz"):
+        r[f] = (r[f] / l).astype(np.float32)
+    parts.append(r)
+    ax = np.zeros(n, ray_dt)                                                  # axis-parallel rays aimed at vertices (two zero components)
+    v = tv.reshape(-1, 3)[rng.integers(0, len(tv) * 3, n)]
+    a = rng.integers(0, 3, n); sgn = rng.choice([-1.0, 1.0], n).astype(np.float32)
+    o = v.copy(); o[np.arange(n), a] -= sgn * ext * 3
+    ax["ox"], ax["oy"], ax["oz"] = o.T
+    for k, f in enumerate(("dx", "dy", "dz")):
+        ax[f] = np.where(a == k, sgn, np.float32(0.0))
+    parts.append(ax)
+    # rays through vertices and edge midpoints from random origins
+    tgt = np.where(rng.random((n, 1)) < 0.5, v, 0.5 * (v + tv.reshape(-1, 3)[rng.integers(0, len(tv) * 3, n)]))
+    o = rng.uniform(-2 * ext, 2 * ext, (n, 3)).astype(np.float32)
+    d = (tgt - o).astype(np.float64); d /= np.maximum(np.linalg.norm(d, axis=1, keepdims=True), 1e-30)
+    e = np.zeros(n, ray_dt)
+    e["ox"], e["oy"], e["oz"] = o.T
+    e["dx"], e["dy"], e["dz"] = d.astype(np.float32).T
+    parts.append(e)
+    return np.concatenate(parts)
+
+
+def same_records(a, b):
+    """Bit-equal hit records, except that any NaN equals any NaN (a needle triangle whose float32 cross product underflows has
+    a NaN normal on both sides; the GPU's canonical NaN is 0x7fffffff, x86's 0xffc00000)."""
+    for f in a.dtype.names:
+        x, y = a[f], b[f]
+        if x.dtype.kind == "f":
+            ok = (x.view(np.uint32) == y.view(np.uint32)) | (np.isnan(x) & np.isnan(y))
+        else:
+            ok = x == y
+        if not ok.all():
+            return False
+    return True
+
+
+def with_bounces(trace, rays, seed):
+    """The batch plus the rays that start ON the surfaces it hit (origins exactly on primitives: the tMin rules)."""
+    hits = trace(rays)
+    fin = np.isfinite(hits["nx"]) & np.isfinite(hits["ny"]) & np.isfinite(hits["nz"]) & np.isfinite(hits["px"])
+    return np.concatenate([rays, util.bounce_rays(hits[fin], seed=seed + 7)])
+
+
+@pytest.mark.parametrize("seed", SEEDS)
+def test_oracle_bvh_walks_equal_the_list_loop(oracle, seed):
+    sd, ext, tv = fuzz_scene(seed)
+    for builder in (1, 0):
+        osc = oracle.scene(sd); osc.set_builder(builder, 4)
+        rays = with_bounces(lambda r: osc.trace_batch(r, use_bvh=0), fuzz_rays(sd, ext, tv, seed, n=1500), seed)
+        brute = osc.trace_batch(rays, use_bvh=0)
+        assert (brute["prim_id"] >= 0).sum() > 50
+        for mode in (1, 2):
+            assert same_records(osc.trace_batch(rays, use_bvh=mode), brute), (seed, builder, mode)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed", SEEDS)
+def test_gpu_closest_hit_fuzz_vs_oracle(oracle, seed):
+    from parallelraytracing_b200.capi import Context
+    sd, ext, tv = fuzz_scene(seed)
+    ctx = Context(0)
+    try:
+        for builder in (1, 0):
+            ctx.set_option("bvh_builder", builder); ctx.set_option("bvh_wide", 1)      # 4-wide nodes also below wide_min_prims
+            ctx.set_scene(sd); ctx.build_bvh()
+            osc = oracle.scene(sd); osc.set_builder(builder, 4)
+            g, o = ctx.debug_lbvh(), osc.get_lbvh()
+            for key in ("morton", "sorted_prim", "node_children", "node_bounds"):
+                assert g[key].tobytes() == o[key].tobytes(), (seed, builder, key)
+            rays = with_bounces(lambda r: ctx.trace_batch(r, use_bvh=0), fuzz_rays(sd, ext, tv, seed), seed)
+            ctx.enable_counters(True)
+            for mode in (0, 1, 2):
+                cnt = np.zeros(2, np.uint64)
+                want = osc.trace_batch(rays, use_bvh=mode, counters=cnt)
+                got = ctx.trace_batch(rays, use_bvh=mode); st = ctx.stats()
+                assert same_records(got, want), (seed, builder, mode)
+                if mode:
+                    assert (st.nodes_visited, st.prims_tested) == (int(cnt[0]), int(cnt[1])), (seed, builder, mode)
+            ctx.enable_counters(False)
+    finally:
+        ctx.close()

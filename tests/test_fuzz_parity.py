@@ -141,3 +141,62 @@ def test_gpu_closest_hit_fuzz_vs_oracle(oracle, seed):
             ctx.enable_counters(False)
     finally:
         ctx.close()
+
+
+def room_scene(seed):
+    """A closed room of six quads (random materials, one wall emissive) with spheres of every material, a triangle cluster with
+    degenerate members and duplicated / coplanar primitives inside; the camera sits in the room, so paths bounce until the
+    depth limit. Returns (scene, camera)."""
+    rng = np.random.default_rng(4000 + seed)
+    b = S.SceneBuilder("room%d" % seed)
+    L = float(10.0 ** rng.uniform(-1, 2))
+    mats = [b.lambertian(tuple(rng.uniform(0.2, 0.9, 3))), b.metal(tuple(rng.uniform(0.5, 1.0, 3)), float(rng.choice([0.0, 0.3, 1.0]))),
+            b.dielectric(float(rng.choice([1.0, 1.33, 1.5, 2.4]))), b.emissive((4, 3, 2)), b.lambertian((0.7, 0.7, 0.7))]
+    walls = [((0, 0, 0), (0, -L, 0)), ((180, 0, 0), (0, L, 0)), ((0, 0, 90), (L, 0, 0)), ((0, 0, -90), (-L, 0, 0)),
+             ((90, 0, 0), (0, 0, -L)), ((-90, 0, 0), (0, 0, L))]
+    for k, (eul, tr) in enumerate(walls):
+        b.add_quad(2 * L, 2 * L, mats[3] if k == seed % 6 else mats[int(rng.integers(0, 5))], euler=eul, trans=tr)
+    if seed % 2:
+        b.add_quad(2 * L, 2 * L, mats[0], euler=walls[0][0], trans=walls[0][1])       # an exact duplicate of the floor: lowest id wins
+    for _ in range(int(rng.integers(2, 10))):
+        b.add_sphere(L * rng.uniform(0.05, 0.35), mats[int(rng.integers(0, 5))], trans=tuple(rng.uniform(-0.7, 0.7, 3) * L))
+    nt = int(rng.integers(4, 120))
+    c = rng.uniform(-0.6, 0.6, (nt, 1, 3)) * L
+    tv = c + rng.standard_normal((nt, 3, 3)) * L * rng.uniform(0.02, 0.3, (nt, 1, 1))
+    tv[0, 2] = tv[0, 1]; tv[1, 2] = 0.5 * (tv[1, 0] + tv[1, 1]); tv[2] = tv[3]
+    b.add_triangles(tv.astype(np.float32), None, rng.integers(0, 5, nt).astype(np.int32))
+    pos = rng.uniform(-0.5, 0.5, 3) * L
+    front = rng.standard_normal(3); front /= np.linalg.norm(front)
+    if seed % 5 == 4:
+        front = np.array([0.0, 0.0, -1.0])                                          # looking exactly down an axis
+    cam = S.Camera(pos=tuple(float(x) for x in pos.astype(np.float32)), front=tuple(float(x) for x in front.astype(np.float32)), width=40, height=28)
+    return b.build(), cam
+
+
+def same_image(a, b):
+    return bool(((a.view(np.uint32) == b.view(np.uint32)) | (np.isnan(a) & np.isnan(b))).all())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed", SEEDS)
+def test_gpu_image_fuzz_vs_oracle(oracle, seed):
+    """The whole estimator on the fuzz scenes (all four materials, degenerate triangles with NaN normals included): the
+    accumulation buffer and the per-bounce ray counts of every pipeline form against the oracle's render."""
+    from parallelraytracing_b200.capi import Context
+    sd, cam = room_scene(seed)
+    spp, depth = 3, 2 + seed % 11
+    want, rays = oracle.scene(sd).render(cam, spp, depth, seed=100 + seed)
+    ctx = Context(0)
+    try:
+        for opts in ({}, {"fused": 0}, {"fused": 0, "bvh_wide": 1}, {"fused": 1, "bvh_builder": 0}, {"fused": 0, "tail_bounce": 0}, {"tail_pool": 0}):
+            for k, v in opts.items():
+                ctx.set_option(k, v)
+            ctx.set_scene(sd); ctx.build_bvh(); ctx.set_camera(cam); ctx.clear_accum()
+            ctx.render(spp, depth, seed=100 + seed)
+            got = ctx.read_accum(); st = ctx.stats()
+            assert st.rays_total == rays, (seed, opts)
+            assert same_image(got, want), (seed, opts, util.image_metrics(np.nan_to_num(want) / spp, np.nan_to_num(got) / spp))
+            for k in opts:
+                ctx.set_option(k, {"fused": -1, "bvh_wide": -1, "bvh_builder": 1, "tail_bounce": 2, "tail_pool": 1}[k])
+    finally:
+        ctx.close()

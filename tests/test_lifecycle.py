@@ -1,0 +1,88 @@
+"""Life-cycle hygiene of the C-ABI context on the GPU: device memory comes back after prt_destroy, repeated scene / camera
+changes do not grow it, and the entry points can be called in any sensible order (the reference's backends leak their scene
+buffers, cuda_megakernel/renderer.cu:178-186; this library must not)."""
+import numpy as np
+import pytest
+
+from parallelraytracing_b200 import scene as S
+from parallelraytracing_b200.capi import Context, PrtError
+
+pytestmark = pytest.mark.gpu
+
+
+def free_bytes():
+    import torch
+    torch.cuda.synchronize()
+    return torch.cuda.mem_get_info(0)[0]
+
+
+def exercise(ctx, n_tris, W, H, spp=2):
+    sd = S.random_triangle_soup(n_tris, seed=n_tris)
+    ctx.set_scene(sd); ctx.build_bvh()
+    ctx.set_camera(S.Camera(pos=(0.0, 0.0, 150.0), front=(0.0, 0.0, -1.0), width=W, height=H))
+    ctx.clear_accum(); ctx.render(spp, 4, seed=1)
+    img = ctx.read_accum()
+    assert np.isfinite(img).all() and img.sum() > 0
+    ctx.resolve_display(1.0, 2.2)
+    return img
+
+
+def test_destroy_returns_device_memory():
+    c = Context(0); exercise(c, 2000, 64, 48); c.close()          # warm: CUDA modules, torch context
+    base = free_bytes()
+    for k in range(12):
+        c = Context(0)
+        exercise(c, 1000 + 3000 * (k % 4), 96 + 32 * (k % 3), 64)
+        c.close()
+    assert base - free_bytes() <= (2 << 20), "device memory lost across create/destroy cycles"
+
+
+def test_repeated_scene_and_camera_changes_do_not_grow():
+    c = Context(0)
+    try:
+        exercise(c, 40000, 256, 192)                               # the largest configuration first: buffers only ever grow to the maximum
+        c.trace_batch(np.zeros(70000, dtype=[("ox", "f4"), ("oy", "f4"), ("oz", "f4"), ("dx", "f4"), ("dy", "f4"), ("dz", "f4")]))
+        high = free_bytes()
+        ref = None
+        for k in range(20):
+            img = exercise(c, [500, 40000, 7000, 1][k % 4], [64, 256, 128][k % 3], [48, 192, 96][k % 3])
+            if k % 12 == 1:                                         # the same configuration gives the same image every time round
+                ref = img if ref is None else ref
+                assert np.array_equal(img, ref)
+        assert high - free_bytes() <= (2 << 20), "device memory grows with repeated prt_set_scene / prt_set_camera"
+    finally:
+        c.close()
+
+
+def test_calls_out_of_order_fail_cleanly():
+    c = Context(0)
+    try:
+        with pytest.raises(PrtError):
+            c.build_bvh()                                           # no scene
+        with pytest.raises(PrtError):
+            c.render(1, 4, seed=1)                                  # no scene, no camera
+        sd = S.cornell()
+        c.set_scene(sd)
+        with pytest.raises(PrtError):
+            c.render(1, 4, seed=1)                                  # no BVH, no camera
+        c.build_bvh()
+        with pytest.raises(PrtError):
+            c.render(1, 4, seed=1)                                  # no camera
+        c.set_camera(S.Camera(width=32, height=32))
+        with pytest.raises(PrtError):
+            c.render(-1, 4, seed=1)
+        with pytest.raises(PrtError):
+            c.render(1, -1, seed=1)
+        c.clear_accum(); c.render(2, 0, seed=1)                     # TraceRay(depth <= 0) = 0 (cpu/renderer.cpp:61): weight only
+        assert c.accum_spp() == 2 and not c.read_accum().any()
+        with pytest.raises(PrtError):
+            c.render(1, 33, seed=1)                                 # PRT_MAX_DEPTH = 32
+        c.clear_accum(); c.render(1, 4, seed=1)
+        a = c.read_accum()
+        c.set_scene(sd)                                             # a new scene invalidates the BVH, not the film
+        with pytest.raises(PrtError):
+            c.render(1, 4, seed=1)
+        c.build_bvh(); c.clear_accum(); c.render(1, 4, seed=1)
+        assert np.array_equal(a, c.read_accum())
+    finally:
+        c.close()

@@ -158,7 +158,10 @@ const char* prt_version(void);
  * Triangles = reference `Triangle` (shape.h:49-82) in world space: tri_verts = nt*9 floats
  * (v0,v1,v2), tri_normals = nt*9 floats or NULL (flat geometric normals), tri_material =
  * nt ints or NULL (all tri_material_default). Triangle i has prim_id tri_prim_base + i.
- * sky_rgb = radiance of a miss (the reference hard-codes (0.4,0.3,0.6): cpu/renderer.h:31). */
+ * sky_rgb = radiance of a miss (the reference hard-codes (0.4,0.3,0.6): cpu/renderer.h:31).
+ * Non-finite input: primitives with NaN / +-inf coordinates are tolerated - they are never hit and do not disturb the
+ * build or the hits on the others (tests/test_checked_build.py). Finite coordinates whose products overflow fp32
+ * (|x| beyond ~1e18) give unspecified hits at t = inf, as they do in the reference's own tests. */
 int  prt_set_scene(prt_ctx* ctx,
                    const prt_sphere* spheres, int n_spheres,
                    const prt_quad* quads, int n_quads,

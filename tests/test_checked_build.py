@@ -26,6 +26,15 @@ def test_checked_library_runs_clean_and_catches_a_provoked_overflow():
     assert provoked == 0x40000001, "PRT_CHK_STACK did not fire with a 28-entry stack: 0x%x" % provoked
 
 
+def test_non_finite_vertices_are_harmless():
+    """NaN / +-inf vertices (a broken exporter, an uninitialised buffer): the build and every walk terminate, no index leaves its
+    array, such triangles are never hit and the rest of the scene traces exactly as the list loop does."""
+    env = dict(os.environ, PRT_CHECKED="1", PYTHONPATH=os.pathsep.join([ROOT, os.path.join(ROOT, "tests"), os.path.join(ROOT, "oracle")]))
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "nonfinite_check.py")], capture_output=True, text=True, env=env, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "nonfinite ok 1 check_flags 0x40000000" in r.stdout, r.stdout[-1000:]
+
+
 def test_regular_library_has_no_checks():
     from parallelraytracing_b200.capi import Context
     with Context(0) as c:

@@ -705,16 +705,17 @@ k_shade(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ 
 // Results are bit-identical to the staged kernels (same device functions, same order).
 constexpr int FUSED_STACK = 16;   // fused kernels walk trees of <= fused_max_prims primitives; leaves room for the shade queue
 
-// Resident CTAs per SM asked of the register allocator for the two fused kernels (1 = no constraint: 56 / 64 registers).
-// Measured on one box, 10 timed steps, Mrays/s Cornell 256 spp / closed Cornell 64 spp (bounce, primary): (1,1) 37 556 /
-// 19 706 on the first run of the box, 38.7 K / 21.1 K in every other session; (5,1) 48 registers + 56 B of spills 38 870 /
-// 21 666; (6,1) 40 registers 38 026 / 21 358; (5,5) 38 860 / 21 374; (6,6) 37 272 / 20 824. Differences are inside the
-// run-to-run spread of the unconstrained build, so the constraint stays off.
+// Resident CTAs per SM asked of the register allocator for the two fused kernels (1 = no constraint). The list-loop form of
+// k_bounce (BRUTE) compiles to 70 registers unconstrained = 3 CTAs per SM; asked for 4 it takes 64 without a spill. Measured
+// on one box, Mrays/s Cornell 256 spp / closed Cornell 64 spp, (bounce, primary): (1,1) 37 527 / 19 696; (3,1) = (4,1)
+// 39 205 / 21 200; (5,1) 48 registers + 56 B of spills 38 758 / 21 666; (6,1) 37 978 / 21 347; (4,3) 38 660 / 21 095;
+// (4,4) 38 711 / 21 076; (5,3) 38 307 / 21 577; (5,4) 38 456 / 21 551. The BVH-walking form (9 .. 64 primitives, 91
+// registers) would spill at 4 and stays unconstrained; k_primary is best left alone.
 #ifndef PRT_PRIMARY_MIN_BLOCKS
 #define PRT_PRIMARY_MIN_BLOCKS 1
 #endif
 #ifndef PRT_BOUNCE_MIN_BLOCKS
-#define PRT_BOUNCE_MIN_BLOCKS 1
+#define PRT_BOUNCE_MIN_BLOCKS 4
 #endif
 template <bool COUNT, bool BRUTE, bool FAST>
 __global__ void __launch_bounds__(WF_THREADS, PRT_PRIMARY_MIN_BLOCKS)
@@ -759,7 +760,7 @@ k_primary(SceneView sc, CamView cam, int pix0, int npix, FastDiv div_npix, int n
 }
 
 template <bool COUNT, bool BRUTE, bool FAST>
-__global__ void __launch_bounds__(WF_THREADS, PRT_BOUNCE_MIN_BLOCKS)
+__global__ void __launch_bounds__(WF_THREADS, BRUTE ? PRT_BOUNCE_MIN_BLOCKS : 1)
 k_bounce(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ qd, const float4* __restrict__ qb,
          float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb, float4* __restrict__ contrib,
          uint32_t* __restrict__ qcount, int bounce, int max_depth, unsigned long long* __restrict__ stats) {

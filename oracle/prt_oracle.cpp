@@ -149,7 +149,10 @@ float isect_quad(const prt_quad& q, V3 o, V3 d, bool& front) {
 }
 
 /* watertight ray/triangle (Woop et al. 2013); reference is Moller-Trumbore shape.h:262-303 */
-struct Shear { int kx, ky, kz; float sx, sy, sz; };
+/* kx, ky = the two axes after kz in cyclic order; where the paper swaps them for d[kz] < 0 (winding), the sheared x row is
+ * negated instead - the same edge functions q - p, see prt_device.cuh:make_shear - with the flip folded into sx */
+struct Shear { int kx, ky, kz; float sx, sy, sz; uint32_t flip; };
+inline float flip_sign(float v, uint32_t m) { uint32_t u; memcpy(&u, &v, 4); u ^= m; memcpy(&v, &u, 4); return v; }
 Shear make_shear(V3 d) {
     Shear r;
     float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
@@ -157,17 +160,19 @@ Shear make_shear(V3 d) {
     r.kx = r.kz + 1; if (r.kx == 3) r.kx = 0;
     r.ky = r.kx + 1; if (r.ky == 3) r.ky = 0;
     float dz = comp(d, r.kz);
-    if (dz < 0.0f) std::swap(r.kx, r.ky);
     float dx = comp(d, r.kx), dy = comp(d, r.ky);
     r.sx = dx / dz; r.sy = dy / dz; r.sz = 1.0f / dz;
+    uint32_t sb; memcpy(&sb, &r.sz, 4);
+    r.flip = sb & 0x80000000u;
+    r.sx = flip_sign(r.sx, r.flip);
     return r;
 }
 float isect_tri(const Tri& tr, V3 o, const Shear& rs, float tmin, float tmax, float& b1, float& b2) {
     V3 A = sub(tr.v[0], o), B = sub(tr.v[1], o), C = sub(tr.v[2], o);
     float Akz = comp(A, rs.kz), Bkz = comp(B, rs.kz), Ckz = comp(C, rs.kz);
-    float Ax = fmaf(-rs.sx, Akz, comp(A, rs.kx)), Ay = fmaf(-rs.sy, Akz, comp(A, rs.ky));
-    float Bx = fmaf(-rs.sx, Bkz, comp(B, rs.kx)), By = fmaf(-rs.sy, Bkz, comp(B, rs.ky));
-    float Cx = fmaf(-rs.sx, Ckz, comp(C, rs.kx)), Cy = fmaf(-rs.sy, Ckz, comp(C, rs.ky));
+    float Ax = fmaf(-rs.sx, Akz, flip_sign(comp(A, rs.kx), rs.flip)), Ay = fmaf(-rs.sy, Akz, comp(A, rs.ky));
+    float Bx = fmaf(-rs.sx, Bkz, flip_sign(comp(B, rs.kx), rs.flip)), By = fmaf(-rs.sy, Bkz, comp(B, rs.ky));
+    float Cx = fmaf(-rs.sx, Ckz, flip_sign(comp(C, rs.kx), rs.flip)), Cy = fmaf(-rs.sy, Ckz, comp(C, rs.ky));
     float U = Cx * By - Cy * Bx;
     float V = Ax * Cy - Ay * Cx;
     float W = Bx * Ay - By * Ax;

@@ -250,18 +250,25 @@ PRT_DEV float isect_quad(const QuadRec& q, V3 o, V3 d, bool& front) {
 }
 
 // Watertight ray/triangle test (Woop, Benthin, Wald 2013). Per-ray constants:
-struct RayShear { int kx, ky, kz; float sx, sy, sz; };
+// kx, ky are the two axes after kz in cyclic order. The paper also swaps them when d[kz] < 0 (to keep the winding). Swapping
+// the sheared x and y rows turns every edge function p - q into q - p; NEGATING the x row (-Ax, -Bx, -Cx) does exactly the
+// same, bit for bit, signs of zero included ((-Cx)*By - Cy*(-Bx) = q - p), and costs three sign flips with a per-ray mask
+// (the sign of sz = 1/d[kz]; sx is stored with the flip applied) instead of a second set of component selections. With the
+// axes in cyclic order the selection needs the two predicates of kz only: 2 compares + 18 selects per triangle, where the
+// generic comp(v, k) form took 54 instructions (source-level ncu: 7.3 % of k_extend_wide's instructions on the 960 K mesh,
+// at 5.6 lanes). U, V, W, det, T equal the swap form's except for the sign of a zero (x - x is +0 either way round), which
+// showed as -0 / +0 barycentrics on rays through a vertex: the oracle (prt_oracle.cpp:make_shear) therefore states the same form.
+struct RayShear { int kz; float sx, sy, sz; };
 PRT_DEV RayShear make_shear(V3 d) {
     RayShear r;
     float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
     r.kz = (ax > ay) ? ((ax > az) ? 0 : 2) : ((ay > az) ? 1 : 2);
-    r.kx = r.kz + 1; if (r.kx == 3) r.kx = 0;
-    r.ky = r.kx + 1; if (r.ky == 3) r.ky = 0;
-    float dz = r.kz == 0 ? d.x : (r.kz == 1 ? d.y : d.z);
-    if (dz < 0.0f) { int t = r.kx; r.kx = r.ky; r.ky = t; }
-    float dx = r.kx == 0 ? d.x : (r.kx == 1 ? d.y : d.z);
-    float dy = r.ky == 0 ? d.x : (r.ky == 1 ? d.y : d.z);
+    const bool k0 = r.kz == 0, k1 = r.kz == 1;
+    float dz = k0 ? d.x : (k1 ? d.y : d.z);
+    float dx = k0 ? d.y : (k1 ? d.z : d.x);
+    float dy = k0 ? d.z : (k1 ? d.x : d.y);
     r.sx = dx / dz; r.sy = dy / dz; r.sz = 1.0f / dz;
+    r.sx = __uint_as_float(__float_as_uint(r.sx) ^ (__float_as_uint(r.sz) & 0x80000000u));
     return r;
 }
 PRT_DEV float comp(V3 v, int k) { return k == 0 ? v.x : (k == 1 ? v.y : v.z); }
@@ -271,10 +278,15 @@ PRT_DEV float comp(V3 v, int k) { return k == 0 ? v.x : (k == 1 ? v.y : v.z); }
 PRT_DEV float isect_tri(V3 v0, V3 v1, V3 v2, V3 o, const RayShear& rs, float tmin, float tmax,
                         float& b1, float& b2) {
     V3 A = v0 - o, B = v1 - o, C = v2 - o;
-    float Akz = comp(A, rs.kz), Bkz = comp(B, rs.kz), Ckz = comp(C, rs.kz);
-    float Ax = fmaf(-rs.sx, Akz, comp(A, rs.kx)), Ay = fmaf(-rs.sy, Akz, comp(A, rs.ky));
-    float Bx = fmaf(-rs.sx, Bkz, comp(B, rs.kx)), By = fmaf(-rs.sy, Bkz, comp(B, rs.ky));
-    float Cx = fmaf(-rs.sx, Ckz, comp(C, rs.kx)), Cy = fmaf(-rs.sy, Ckz, comp(C, rs.ky));
+    const bool k0 = rs.kz == 0, k1 = rs.kz == 1;
+    float Akz = k0 ? A.x : (k1 ? A.y : A.z), Bkz = k0 ? B.x : (k1 ? B.y : B.z), Ckz = k0 ? C.x : (k1 ? C.y : C.z);
+    float Akx = k0 ? A.y : (k1 ? A.z : A.x), Bkx = k0 ? B.y : (k1 ? B.z : B.x), Ckx = k0 ? C.y : (k1 ? C.z : C.x);
+    float Aky = k0 ? A.z : (k1 ? A.x : A.y), Bky = k0 ? B.z : (k1 ? B.x : B.y), Cky = k0 ? C.z : (k1 ? C.x : C.y);
+    const uint32_t flip = __float_as_uint(rs.sz) & 0x80000000u;            // d[kz] < 0: negate the x row (= the paper's swap)
+    Akx = __uint_as_float(__float_as_uint(Akx) ^ flip); Bkx = __uint_as_float(__float_as_uint(Bkx) ^ flip); Ckx = __uint_as_float(__float_as_uint(Ckx) ^ flip);
+    float Ax = fmaf(-rs.sx, Akz, Akx), Ay = fmaf(-rs.sy, Akz, Aky);
+    float Bx = fmaf(-rs.sx, Bkz, Bkx), By = fmaf(-rs.sy, Bkz, Bky);
+    float Cx = fmaf(-rs.sx, Ckz, Ckx), Cy = fmaf(-rs.sy, Ckz, Cky);
     float U = Cx * By - Cy * Bx;
     float V = Ax * Cy - Ay * Cx;
     float W = Bx * Ay - By * Ax;

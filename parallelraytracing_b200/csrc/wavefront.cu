@@ -112,7 +112,7 @@ __device__ __forceinline__ Best traverse(const SceneView& sc, V3 o, V3 d, int* _
     RayBox rb = make_raybox(sc, o, d);
     RayShear rs; V3 dn = d;
     if (sc.n_tris > 0) rs = make_shear(d);            // per-ray triangle-test constants: only if there are triangles
-    else { rs.kx = 0; rs.ky = 1; rs.kz = 2; rs.sx = rs.sy = rs.sz = 0.f; }
+    else { rs.kz = 2; rs.sx = rs.sy = rs.sz = 0.f; }
     if (sc.n_spheres > 0) dn = normalize(d);          // Circle's local direction (primitive.cpp:30): only if there are spheres
     int lstack[STACK_TOTAL - SS];
     int sp = 0;
@@ -191,7 +191,7 @@ k_extend_pt(SceneView sc, const float4* __restrict__ qo, const float4* __restric
     uint32_t nn = 0, np = 0;
     bool have = false, exhausted = (sc.n_prims == 0);
     uint32_t idx = 0; V3 o = mk(0, 0, 0), d = o, dn = o; RayBox rb; RayShear rs; Best best; int cur = PRT_DONE, sp = 0;
-    rb.o = o; rb.inv = o; rb.pad = o; rs.kx = 0; rs.ky = 1; rs.kz = 2; rs.sx = rs.sy = rs.sz = 0.f; best_init(best);
+    rb.o = o; rb.inv = o; rb.pad = o; rs.kz = 2; rs.sx = rs.sy = rs.sz = 0.f; best_init(best);
     if (sc.n_prims == 0) {          // nothing to hit: every ray is a miss
         for (uint32_t i = blockIdx.x * WF_THREADS + threadIdx.x; i < count; i += gridDim.x * WF_THREADS)
             st_stream(&hits[i], make_float4(best.t, __uint_as_float(best.code), 0.f, 0.f));
@@ -301,7 +301,7 @@ k_extend_wide(SceneView sc, const float4* __restrict__ qo, const float4* __restr
     uint32_t nn = 0, np = 0;
     bool have = false, exhausted = false;
     uint32_t idx = 0; V3 o = mk(0, 0, 0), d = o, dn = o, inv = o; RayShear rs; Best best; int cur = PRT_DONE, sp = 0;
-    rs.kx = 0; rs.ky = 1; rs.kz = 2; rs.sx = rs.sy = rs.sz = 0.f; best_init(best);
+    rs.kz = 2; rs.sx = rs.sy = rs.sz = 0.f; best_init(best);
     while (!exhausted || __any_sync(0xffffffffu, have)) {
         uint32_t idle = __ballot_sync(0xffffffffu, !have);
         if (idle && !exhausted) {
@@ -418,7 +418,7 @@ template <bool COUNT, int SS>
 __device__ __forceinline__ Best traverse_wide(const SceneView& sc, V3 o, V3 d, int* __restrict__ st, uint32_t& nn, uint32_t& np) {
     Best best; best_init(best);
     const V3 inv = mk(safe_inv(d.x), safe_inv(d.y), safe_inv(d.z));
-    RayShear rs; rs.kx = 0; rs.ky = 1; rs.kz = 2; rs.sx = rs.sy = rs.sz = 0.f;
+    RayShear rs; rs.kz = 2; rs.sx = rs.sy = rs.sz = 0.f;
     if (sc.n_tris > 0) rs = make_shear(d);
     const V3 dn = sc.n_spheres > 0 ? normalize(d) : d;
     const bool nx = inv.x < 0.0f, ny = inv.y < 0.0f, nz = inv.z < 0.0f;

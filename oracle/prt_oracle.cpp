@@ -161,7 +161,7 @@ Shear make_shear(V3 d) {
     r.ky = r.kx + 1; if (r.ky == 3) r.ky = 0;
     float dz = comp(d, r.kz);
     float dx = comp(d, r.kx), dy = comp(d, r.ky);
-    r.sx = dx / dz; r.sy = dy / dz; r.sz = 1.0f / dz;
+    r.sz = 1.0f / dz; r.sx = dx * r.sz; r.sy = dy * r.sz;
     uint32_t sb; memcpy(&sb, &r.sz, 4);
     r.flip = sb & 0x80000000u;
     r.sx = flip_sign(r.sx, r.flip);
@@ -189,9 +189,10 @@ float isect_tri(const Tri& tr, V3 o, const Shear& rs, float tmin, float tmax, fl
     if (det == 0.0f) return -1.0f;
     float Az = rs.sz * Akz, Bz = rs.sz * Bkz, Cz = rs.sz * Ckz;
     float T = fmaf(W, Cz, fmaf(V, Bz, U * Az));
-    float t = T / det;
+    float rdet = 1.0f / det;
+    float t = T * rdet;
     if (!(t >= tmin) || t > tmax) return -1.0f;
-    b1 = V / det; b2 = W / det;
+    b1 = V * rdet; b2 = W * rdet;
     return t;
 }
 

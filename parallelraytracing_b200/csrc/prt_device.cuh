@@ -267,7 +267,7 @@ PRT_DEV RayShear make_shear(V3 d) {
     float dz = k0 ? d.x : (k1 ? d.y : d.z);
     float dx = k0 ? d.y : (k1 ? d.z : d.x);
     float dy = k0 ? d.z : (k1 ? d.x : d.y);
-    r.sx = dx / dz; r.sy = dy / dz; r.sz = 1.0f / dz;
+    r.sz = 1.0f / dz; r.sx = dx * r.sz; r.sy = dy * r.sz;      // one division (as the paper's implementation; every vertex is sheared by the same sx, sy)
     r.sx = __uint_as_float(__float_as_uint(r.sx) ^ (__float_as_uint(r.sz) & 0x80000000u));
     return r;
 }
@@ -298,15 +298,17 @@ PRT_DEV float isect_tri(V3 v0, V3 v1, V3 v2, V3 o, const RayShear& rs, float tmi
         double BxAy = (double)Bx * (double)Ay, ByAx = (double)By * (double)Ax;
         W = (float)(BxAy - ByAx);
     }
-    if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f)) return -1.0f;
+    // some edge function negative AND some positive = outside (the paper's test; min / max form: 2 three-input min/max + 2 compares)
+    if (fminf(fminf(U, V), W) < 0.0f && fmaxf(fmaxf(U, V), W) > 0.0f) return -1.0f;
     float det = (U + V) + W;
     if (det == 0.0f) return -1.0f;
     float Az = rs.sz * Akz, Bz = rs.sz * Bkz, Cz = rs.sz * Ckz;
     float T = fmaf(W, Cz, fmaf(V, Bz, U * Az));
-    float t = T / det;
+    float rdet = 1.0f / det;                                             // one division per candidate, not three
+    float t = T * rdet;
     if (!(t >= tmin) || t > tmax) return -1.0f;
-    b1 = V / det;
-    b2 = W / det;
+    b1 = V * rdet;
+    b2 = W * rdet;
     return t;
 }
 

@@ -14,7 +14,7 @@ import sys
 import tempfile
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-SO = os.path.join(ROOT, "parallelraytracing_b200", "libprt_b200.so")
+SO = os.environ.get("PRT_LIB") or os.path.join(ROOT, "parallelraytracing_b200", "libprt_b200.so")   # PRT_LIB: the library the report was captured with
 
 
 def line_table():

@@ -171,6 +171,21 @@ int  prt_set_scene(prt_ctx* ctx,
                    const prt_material* materials, int n_materials,
                    const float sky_rgb[3]);
 
+/* prt_set_scene + prt_build_bvh in one call - what a backend's Init does (cuda_wavefront/renderer.cu:351-370 uploads the scene and
+ * allocates in one go; there is no build in the reference). Same arguments, same device state afterwards, bit for bit; the
+ * difference is time: the hierarchy is built from the vertex positions (boxes, Morton codes, sort, PLOC, wide nodes, vertex
+ * gather) as soon as THEY are on the device, while a second host thread is still sending the vertex normals and material
+ * indices - 40 of the 76 bytes per triangle - over PCIe; a last kernel drops those into their leaf slots. The BVH build of a
+ * 10 M-triangle mesh (3.8 ms) disappears behind 7 ms of upload. Synchronous: the arrays are free again on return. */
+int  prt_set_scene_build(prt_ctx* ctx,
+                         const prt_sphere* spheres, int n_spheres,
+                         const prt_quad* quads, int n_quads,
+                         const float* tri_verts, const float* tri_normals,
+                         const int32_t* tri_material, int tri_material_default,
+                         int n_tris, int tri_prim_base,
+                         const prt_material* materials, int n_materials,
+                         const float sky_rgb[3]);
+
 /* Page-locked host memory (cudaHostAlloc) for the big input arrays: prt_set_scene copies from such memory with plain
  * asynchronous DMA (~50 GB/s over PCIe 5); pageable arrays go through the context's own staging ring instead. Optional. */
 void* prt_host_alloc(size_t bytes);

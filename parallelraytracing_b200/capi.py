@@ -45,7 +45,7 @@ class PrtError(RuntimeError):
 
 
 EXPORTS = [
-    "prt_create", "prt_create_multi", "prt_destroy", "prt_last_error", "prt_version", "prt_set_scene", "prt_build_bvh",
+    "prt_create", "prt_create_multi", "prt_destroy", "prt_last_error", "prt_version", "prt_set_scene", "prt_set_scene_build", "prt_build_bvh",
     "prt_set_camera", "prt_render", "prt_render_fresh", "prt_render_region", "prt_wait_event", "prt_clear_accum", "prt_scale_accum", "prt_accum_device_ptr",
     "prt_set_accum_buffer", "prt_read_accum", "prt_accum_spp", "prt_set_accum_spp", "prt_resolve_display", "prt_trace_batch", "prt_trace_batch_static",
     "prt_debug_lbvh", "prt_debug_wide", "prt_debug_scatter", "prt_debug_ploc_trace", "prt_debug_check_flags", "prt_host_alloc", "prt_host_free", "prt_num_prims", "prt_enable_counters", "prt_get_stats", "prt_set_option",
@@ -83,6 +83,7 @@ def load_library():
     lib.prt_last_error.argtypes = [vp]; lib.prt_last_error.restype = C.c_char_p
     lib.prt_version.restype = C.c_char_p
     lib.prt_set_scene.argtypes = [vp, vp, i32, vp, i32, vp, vp, vp, i32, i32, i32, vp, i32, vp]
+    lib.prt_set_scene_build.argtypes = lib.prt_set_scene.argtypes
     lib.prt_build_bvh.argtypes = [vp]
     lib.prt_set_camera.argtypes = [vp, C.POINTER(CCamera)]
     lib.prt_render.argtypes = [vp, i32, i32, u64, i32]
@@ -183,16 +184,21 @@ class Context:
     def __exit__(self, *a):
         self.close()
 
-    def set_scene(self, scene):
+    def set_scene(self, scene, build=False):
+        """prt_set_scene; build=True: prt_set_scene_build (scene + BVH in one call, the build hidden behind the normals' upload)."""
         s = scene
         nt = 0 if s.tri_verts is None else int(s.tri_verts.shape[0])
         sky = np.asarray(s.sky, dtype=np.float32)
         self._keep = (s, sky)
-        self._check(self.lib.prt_set_scene(
+        fn, what = (self.lib.prt_set_scene_build, "prt_set_scene_build") if build else (self.lib.prt_set_scene, "prt_set_scene")
+        self._check(fn(
             self.h, _ptr(s.spheres), len(s.spheres), _ptr(s.quads), len(s.quads),
             _ptr(s.tri_verts) if nt else None, _ptr(s.tri_normals) if nt else None,
             _ptr(s.tri_material) if nt else None, -1, nt, int(s.tri_prim_base),
-            _ptr(s.materials), len(s.materials), _ptr(sky)), "prt_set_scene")
+            _ptr(s.materials), len(s.materials), _ptr(sky)), what)
+
+    def set_scene_build(self, scene):
+        self.set_scene(scene, build=True)
 
     def build_bvh(self):
         self._check(self.lib.prt_build_bvh(self.h), "prt_build_bvh")

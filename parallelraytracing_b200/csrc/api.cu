@@ -63,8 +63,9 @@ static void parallel_memcpy(void* dst, const void* src, size_t bytes, int n_thre
     for (auto& t : th) t.join();
 }
 
-static int upload_large(Ctx* c, DevBuf& b, const void* host, size_t bytes) {
-    int rc = dev_reserve(c, b, bytes);
+static int upload_large(Ctx* c, DevBuf& b, const void* host, size_t bytes, cudaStream_t st = nullptr, bool reserve = true) {
+    if (!st) st = c->stream;
+    int rc = reserve ? dev_reserve(c, b, bytes) : PRT_OK;
     if (rc || !bytes) return rc;
     const size_t CH = (size_t)32 << 20;
     cudaPointerAttributes at{};
@@ -72,7 +73,7 @@ static int upload_large(Ctx* c, DevBuf& b, const void* host, size_t bytes) {
     cudaGetLastError();
     if (pinned || bytes < ((size_t)8 << 20)) {
         for (size_t off = 0; off < bytes; off += CH)
-            PRT_CUDA(c, cudaMemcpyAsync((char*)b.p + off, (const char*)host + off, std::min(CH, bytes - off), cudaMemcpyHostToDevice, c->stream));
+            PRT_CUDA(c, cudaMemcpyAsync((char*)b.p + off, (const char*)host + off, std::min(CH, bytes - off), cudaMemcpyHostToDevice, st));
         return PRT_OK;
     }
     for (int k = 0; k < 2; ++k) {
@@ -84,8 +85,8 @@ static int upload_large(Ctx* c, DevBuf& b, const void* host, size_t bytes) {
         const size_t n = std::min(CH, bytes - off);
         PRT_CUDA(c, cudaEventSynchronize(c->stage_ev[k]));             // the DMA that last read this buffer is done (no-op the first time)
         parallel_memcpy(c->stage[k], (const char*)host + off, n, 4);
-        PRT_CUDA(c, cudaMemcpyAsync((char*)b.p + off, c->stage[k], n, cudaMemcpyHostToDevice, c->stream));
-        PRT_CUDA(c, cudaEventRecord(c->stage_ev[k], c->stream));
+        PRT_CUDA(c, cudaMemcpyAsync((char*)b.p + off, c->stage[k], n, cudaMemcpyHostToDevice, st));
+        PRT_CUDA(c, cudaEventRecord(c->stage_ev[k], st));
     }
     return PRT_OK;
 }
@@ -385,16 +386,19 @@ void prt_destroy(prt_ctx* ctx) {
     for (cudaEvent_t e : c->ev_pool) cudaEventDestroy(e);
     for (cudaEvent_t e : {c->ev_res[0], c->ev_res[1], c->ev_join}) if (e) cudaEventDestroy(e);
     if (c->stream2) { cudaStreamSynchronize(c->stream2); cudaStreamDestroy(c->stream2); }
+    if (c->up_stream) { cudaStreamSynchronize(c->up_stream); cudaStreamDestroy(c->up_stream); }
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete ctx;
 }
 
-int prt_set_scene(prt_ctx* ctx, const prt_sphere* spheres, int n_spheres, const prt_quad* quads, int n_quads,
-                  const float* tri_verts, const float* tri_normals, const int32_t* tri_material,
-                  int tri_material_default, int n_tris, int tri_prim_base,
-                  const prt_material* materials, int n_materials, const float sky_rgb[3]) {
+// prt_set_scene (build = false) and prt_set_scene_build (build = true: the BVH build runs on the positions while the vertex
+// normals and material indices are still crossing PCIe; see prt.h)
+static int set_scene_impl(prt_ctx* ctx, const prt_sphere* spheres, int n_spheres, const prt_quad* quads, int n_quads,
+                          const float* tri_verts, const float* tri_normals, const int32_t* tri_material,
+                          int tri_material_default, int n_tris, int tri_prim_base,
+                          const prt_material* materials, int n_materials, const float sky_rgb[3], bool build) {
     if (!ctx) return set_err(nullptr, PRT_ERR_INVALID, "prt_set_scene: ctx is NULL");
     Ctx* c = &ctx->c;
     if (n_spheres < 0 || n_quads < 0 || n_tris < 0 || n_materials < 0 ||
@@ -440,29 +444,82 @@ int prt_set_scene(prt_ctx* ctx, const prt_sphere* spheres, int n_spheres, const 
     if ((rc = upload(c, c->mats, hm.data(), hm.size() * sizeof(MatRec)))) return rc;
     // triangles: raw arrays straight to the device (staging buffers live in the context: no cudaMalloc/cudaFree per call),
     // expanded there (k_expand_tris)
+    const bool overlap = build && n_tris > 0 && (tri_normals || tri_material);
     if (n_tris > 0) {
         const size_t nt = (size_t)n_tris;
         rc = upload_large(c, c->raw_v, tri_verts, nt * 36);
-        if (!rc && tri_normals) rc = upload_large(c, c->raw_n, tri_normals, nt * 36);
-        if (!rc && tri_material) rc = upload_large(c, c->raw_m, tri_material, nt * 4);
+        if (!rc && tri_normals) rc = overlap ? dev_reserve(c, c->raw_n, nt * 36) : upload_large(c, c->raw_n, tri_normals, nt * 36);
+        if (!rc && tri_material) rc = overlap ? dev_reserve(c, c->raw_m, nt * 4) : upload_large(c, c->raw_m, tri_material, nt * 4);
         if (rc) return rc;
     }
     // records the build gathers + every triangle's box and their share of the bounds (k_ingest_tris)
-    if ((rc = lbvh_ingest_tris(c, n_spheres, n_quads, n_tris, tri_normals != nullptr, tri_material != nullptr, tri_material_default))) return rc;
-    PRT_CUDA(c, cudaStreamSynchronize(c->stream));                 // the caller's arrays (and the records above) are free again
-    PRT_CUDA(c, cudaGetLastError());
+    if ((rc = lbvh_ingest_tris(c, n_spheres, n_quads, n_tris, tri_normals != nullptr, tri_material != nullptr, tri_material_default, overlap))) return rc;
     c->n_spheres = n_spheres; c->n_quads = n_quads; c->n_tris = n_tris; c->n_mats = n_materials;
     c->n_prims = n_spheres + n_quads + n_tris;
     c->tri_prim_base = tri_prim_base;
     if (sky_rgb) { c->sky[0] = sky_rgb[0]; c->sky[1] = sky_rgb[1]; c->sky[2] = sky_rgb[2]; }
-    c->scene_set = true;
-    for (prt_ctx* p : ctx->peers) {                        // multi-device context: the scene is replicated
-        int rp = prt_set_scene(p, spheres, n_spheres, quads, n_quads, tri_verts, tri_normals, tri_material, tri_material_default,
-                               n_tris, tri_prim_base, materials, n_materials, sky_rgb);
+    if (!build) {
+        PRT_CUDA(c, cudaStreamSynchronize(c->stream));             // the caller's arrays (and the records above) are free again
+        PRT_CUDA(c, cudaGetLastError());
+        c->scene_set = true;
+    } else {
+        // The build needs positions only (boxes, Morton codes, sort, hierarchy, wide nodes, vertex gather): it runs on the
+        // render stream while a second host thread sends the normals and materials over a stream of its own (a pageable source keeps
+        // that thread busy filling the staging ring); k_finish_tris then drops them into their leaf slots.
+        c->scene_set = true;
+        int up_rc = PRT_OK; cudaError_t up_err = cudaSuccess;
+        std::thread uploader;
+        if (overlap) {
+            if (!c->up_stream) PRT_CUDA(c, cudaStreamCreateWithFlags(&c->up_stream, cudaStreamNonBlocking));
+            PRT_CUDA(c, cudaStreamSynchronize(c->stream));         // the staging ring is free (positions are on the device), boxes are done
+            uploader = std::thread([&] {
+                up_err = cudaSetDevice(c->device);
+                if (up_err != cudaSuccess) return;
+                const size_t nt = (size_t)n_tris;
+                if (tri_normals) up_rc = upload_large(c, c->raw_n, tri_normals, nt * 36, c->up_stream, false);
+                if (!up_rc && tri_material) up_rc = upload_large(c, c->raw_m, tri_material, nt * 4, c->up_stream, false);
+                if (!up_rc) up_err = cudaStreamSynchronize(c->up_stream);
+            });
+        }
+        c->positions_only = overlap;
+        rc = lbvh_build(c);
+        c->positions_only = false;
+        if (uploader.joinable()) uploader.join();
+        if (rc == PRT_OK && up_rc != PRT_OK) rc = up_rc;
+        if (rc == PRT_OK && up_err != cudaSuccess) rc = set_err(c, PRT_ERR_CUDA, std::string("prt_set_scene_build: upload: ") + cudaGetErrorString(up_err));
+        if (rc == PRT_OK && overlap) {
+            rc = lbvh_finish_tris(c, tri_normals != nullptr, tri_material != nullptr, tri_material_default);
+            if (rc == PRT_OK) {
+                cudaError_t e = cudaStreamSynchronize(c->stream);
+                if (e == cudaSuccess) e = cudaGetLastError();
+                if (e != cudaSuccess) rc = set_err(c, PRT_ERR_CUDA, std::string("prt_set_scene_build: ") + cudaGetErrorString(e));
+            }
+        }
+        if (rc != PRT_OK) { c->scene_set = false; c->bvh_built = false; return rc; }
+    }
+    for (prt_ctx* p : ctx->peers) {                        // multi-device context: the scene is replicated (every device builds its own BVH: identical bits)
+        int rp = set_scene_impl(p, spheres, n_spheres, quads, n_quads, tri_verts, tri_normals, tri_material, tri_material_default,
+                                n_tris, tri_prim_base, materials, n_materials, sky_rgb, build);
         if (rp != PRT_OK) return set_err(c, rp, p->c.err);
     }
     if (!ctx->peers.empty()) PRT_CUDA(c, cudaSetDevice(c->device));
     return PRT_OK;
+}
+
+int prt_set_scene(prt_ctx* ctx, const prt_sphere* spheres, int n_spheres, const prt_quad* quads, int n_quads,
+                  const float* tri_verts, const float* tri_normals, const int32_t* tri_material,
+                  int tri_material_default, int n_tris, int tri_prim_base,
+                  const prt_material* materials, int n_materials, const float sky_rgb[3]) {
+    return set_scene_impl(ctx, spheres, n_spheres, quads, n_quads, tri_verts, tri_normals, tri_material, tri_material_default,
+                          n_tris, tri_prim_base, materials, n_materials, sky_rgb, false);
+}
+
+int prt_set_scene_build(prt_ctx* ctx, const prt_sphere* spheres, int n_spheres, const prt_quad* quads, int n_quads,
+                        const float* tri_verts, const float* tri_normals, const int32_t* tri_material,
+                        int tri_material_default, int n_tris, int tri_prim_base,
+                        const prt_material* materials, int n_materials, const float sky_rgb[3]) {
+    return set_scene_impl(ctx, spheres, n_spheres, quads, n_quads, tri_verts, tri_normals, tri_material, tri_material_default,
+                          n_tris, tri_prim_base, materials, n_materials, sky_rgb, true);
 }
 
 int prt_build_bvh(prt_ctx* ctx) {

@@ -103,7 +103,7 @@ __global__ void k_prim_bounds(const SphereRec* __restrict__ spheres, int ns,
 // no pass over the triangles before the Morton codes. Flat normal when none is given: cross(v1 - v0, v2 - v0), unnormalised.
 __global__ void __launch_bounds__(256)
 k_ingest_tris(int n, const float* __restrict__ v, const float* __restrict__ nrm, const int* __restrict__ mat, int mat_default,
-              float4* __restrict__ out_v, float4* __restrict__ out_n, float4* __restrict__ box, int* __restrict__ tri_bounds) {
+              float4* __restrict__ out_v, float4* __restrict__ out_n, float4* __restrict__ box, int* __restrict__ tri_bounds, int positions_only) {
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     float lo[3] = {__int_as_float(0x7f800000), __int_as_float(0x7f800000), __int_as_float(0x7f800000)};
     float hi[3] = {__int_as_float(0xff800000), __int_as_float(0xff800000), __int_as_float(0xff800000)};
@@ -114,7 +114,9 @@ k_ingest_tris(int n, const float* __restrict__ v, const float* __restrict__ nrm,
 #pragma unroll
         for (int k = 0; k < 3; ++k)
             out_v[6 * (size_t)t + k] = make_float4(a[3 * k], a[3 * k + 1], a[3 * k + 2], k == 1 ? __int_as_float(mat ? mat[t] : mat_default) : 0.f);
-        if (nrm) {
+        if (positions_only) {
+            // prt_set_scene_build: normals and materials are still on their way over PCIe; k_finish_tris adds them behind the build
+        } else if (nrm) {
 #pragma unroll
             for (int k = 0; k < 3; ++k)
                 out_n[6 * (size_t)t + k] = make_float4(nrm[9 * (size_t)t + 3 * k], nrm[9 * (size_t)t + 3 * k + 1], nrm[9 * (size_t)t + 3 * k + 2], 0.f);
@@ -133,7 +135,7 @@ k_ingest_tris(int n, const float* __restrict__ v, const float* __restrict__ nrm,
 }
 
 // raw_* = the packed arrays already on the device; allocates the records and the primitive boxes (all primitives)
-int lbvh_ingest_tris(Ctx* c, int n_spheres, int n_quads, int n_tris, bool have_normals, bool have_mat, int mat_default) {
+int lbvh_ingest_tris(Ctx* c, int n_spheres, int n_quads, int n_tris, bool have_normals, bool have_mat, int mat_default, bool positions_only) {
     int rc;
     const size_t nn = (size_t)n_spheres + n_quads + n_tris, nt = (size_t)n_tris;
     if ((rc = dev_reserve(c, c->tri_in_v, nt * 96)) || (rc = dev_reserve(c, c->aabb_min, nn * 32)) || (rc = dev_reserve(c, c->tri_bounds, 12 * sizeof(int))))
@@ -142,7 +144,7 @@ int lbvh_ingest_tris(Ctx* c, int n_spheres, int n_quads, int n_tris, bool have_n
     if (n_tris > 0)
         k_ingest_tris<<<(unsigned)((nt + 255) / 256), 256, 0, c->stream>>>(n_tris, (const float*)c->raw_v.p, have_normals ? (const float*)c->raw_n.p : nullptr,
             have_mat ? (const int*)c->raw_m.p : nullptr, mat_default, (float4*)c->tri_in_v.p, (float4*)c->tri_in_v.p + 3,
-            (float4*)c->aabb_min.p + 2 * ((size_t)n_spheres + n_quads), (int*)c->tri_bounds.p);
+            (float4*)c->aabb_min.p + 2 * ((size_t)n_spheres + n_quads), (int*)c->tri_bounds.p, positions_only ? 1 : 0);
     return PRT_OK;
 }
 
@@ -483,7 +485,7 @@ __global__ void k_refit(int n, const uint32_t* __restrict__ sorted_prim, const f
 __global__ void k_gather_tris(int n, int ns, int nq, int tri_prim_base, const uint32_t* __restrict__ sorted_prim,
                               const float4* __restrict__ in_v, const float4* __restrict__ in_n,
                               float4* __restrict__ out_v, float4* __restrict__ out_n,
-                              const float4* __restrict__ prim_box, float4* __restrict__ leaf_box) {
+                              const float4* __restrict__ prim_box, float4* __restrict__ leaf_box, int positions_only) {
     int pos = blockIdx.x * blockDim.x + threadIdx.x;
     if (pos >= n) return;
     int q = (int)sorted_prim[pos];
@@ -493,12 +495,48 @@ __global__ void k_gather_tris(int n, int ns, int nq, int tri_prim_base, const ui
     int t = q - ns - nq;
     // one 96-byte input record per triangle (positions, material in v1.w, normals): one random gather instead of three
     float4 a, b, c, n0, n1, n2;                                          // 3 x 256-bit loads of the 96-byte record
-    ldg8(&in_v[6 * (size_t)t], a, b); ldg8(&in_v[6 * (size_t)t + 2], c, n0); ldg8(&in_v[6 * (size_t)t + 4], n1, n2);
+    if (positions_only) {                                                // normals / materials follow in k_finish_tris
+        ldg8(&in_v[6 * (size_t)t], a, b); c = __ldg(&in_v[6 * (size_t)t + 2]);
+        n0 = n1 = n2 = make_float4(0.f, 0.f, 0.f, 0.f);
+    } else {
+        ldg8(&in_v[6 * (size_t)t], a, b); ldg8(&in_v[6 * (size_t)t + 2], c, n0); ldg8(&in_v[6 * (size_t)t + 4], n1, n2);
+    }
     leaf_box[2 * (size_t)pos] = make_float4(fminf(fminf(a.x, b.x), c.x), fminf(fminf(a.y, b.y), c.y), fminf(fminf(a.z, b.z), c.z), 0.f);
     leaf_box[2 * (size_t)pos + 1] = make_float4(fmaxf(fmaxf(a.x, b.x), c.x), fmaxf(fmaxf(a.y, b.y), c.y), fmaxf(fmaxf(a.z, b.z), c.z), 0.f);
     a.w = __int_as_float(tri_prim_base + t); c.w = 0.f;
     out_v[3 * pos] = a; out_v[3 * pos + 1] = b; out_v[3 * pos + 2] = c;
+    if (positions_only) return;
     out_n[3 * pos] = n0; out_n[3 * pos + 1] = n1; out_n[3 * pos + 2] = n2;
+}
+
+// Second half of a positions-only build (prt_set_scene_build): the vertex normals and material indices, which crossed PCIe
+// while the hierarchy was being built, go to their leaf slots - the same values k_ingest_tris + k_gather_tris write.
+__global__ void k_finish_tris(int n, int ns, int nq, const uint32_t* __restrict__ sorted_prim, const float* __restrict__ nrm,
+                              const int* __restrict__ mat, int mat_default, float4* __restrict__ out_v, float4* __restrict__ out_n) {
+    int pos = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pos >= n) return;
+    int q = (int)sorted_prim[pos];
+    if (q < ns + nq) return;
+    size_t t = (size_t)(q - ns - nq);
+    out_v[3 * pos + 1].w = __int_as_float(mat ? mat[t] : mat_default);
+    if (nrm) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) out_n[3 * pos + k] = make_float4(nrm[9 * t + 3 * k], nrm[9 * t + 3 * k + 1], nrm[9 * t + 3 * k + 2], 0.f);
+    } else {                                                              // flat normal from the gathered vertices: k_ingest_tris' arithmetic
+        const float4 a = out_v[3 * pos], b = out_v[3 * pos + 1], c = out_v[3 * pos + 2];
+        float e1x = b.x - a.x, e1y = b.y - a.y, e1z = b.z - a.z, e2x = c.x - a.x, e2y = c.y - a.y, e2z = c.z - a.z;
+        float nx = e1y * e2z - e2y * e1z, ny = e1z * e2x - e2z * e1x, nz = e1x * e2y - e2x * e1y;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) out_n[3 * pos + k] = make_float4(nx, ny, nz, 0.f);
+    }
+}
+int lbvh_finish_tris(Ctx* c, bool have_normals, bool have_mat, int mat_default) {
+    const int n = c->n_prims;
+    if (n <= 0 || c->n_tris <= 0) return PRT_OK;
+    k_finish_tris<<<(n + 255) / 256, 256, 0, c->stream>>>(n, c->n_spheres, c->n_quads, (const uint32_t*)c->vals[c->sorted_slot].p,
+        have_normals ? (const float*)c->raw_n.p : nullptr, have_mat ? (const int*)c->raw_m.p : nullptr, mat_default,
+        (float4*)c->tri_v.p, (float4*)c->tri_n.p);
+    return PRT_OK;
 }
 
 // ------------------------------------------------------------------ PLOC: the tree-quality pass
@@ -926,7 +964,7 @@ int lbvh_build(Ctx* c) {
     if (n > 1) {
         k_gather_tris<<<G, T, 0, st>>>(n, ns, nq, c->tri_prim_base, sprim, (const float4*)c->tri_in_v.p,
                                        (const float4*)c->tri_in_v.p + 3, (float4*)c->tri_v.p, (float4*)c->tri_n.p,
-                                       (const float4*)c->aabb_min.p, (float4*)c->leaf_box.p);
+                                       (const float4*)c->aabb_min.p, (float4*)c->leaf_box.p, c->positions_only ? 1 : 0);
         bool ploc_done = false;
         if (want_ploc) {
             // PLOC over the sorted leaves; on failure (no convergence / a tree deeper than the traversal stack allows) the
@@ -977,7 +1015,7 @@ int lbvh_build(Ctx* c) {
     if (n == 1 && nt > 0)                                                 // n > 1: launched before the refit, above
         k_gather_tris<<<G, T, 0, st>>>(n, ns, nq, c->tri_prim_base, sprim, (const float4*)c->tri_in_v.p,
                                        (const float4*)c->tri_in_v.p + 3, (float4*)c->tri_v.p, (float4*)c->tri_n.p,
-                                       (const float4*)c->aabb_min.p, (float4*)c->leaf_box.p);
+                                       (const float4*)c->aabb_min.p, (float4*)c->leaf_box.p, c->positions_only ? 1 : 0);
     PRT_CUDA(c, cudaEventRecord(c->ev1, st));
     PRT_CUDA(c, cudaStreamSynchronize(st));
     PRT_CUDA(c, cudaGetLastError());

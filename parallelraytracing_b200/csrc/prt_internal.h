@@ -41,6 +41,8 @@ struct Ctx {
     DevBuf prim_id_of_q;                        // int per q: reference list index
     float sky[3] = {0.4f, 0.3f, 0.6f};
     bool scene_set = false;
+    bool positions_only = false;                // prt_set_scene_build: the build runs on the positions while normals / materials upload
+    cudaStream_t up_stream = nullptr;           //   ... on this stream, from a second host thread
 
     // ---- LBVH ----
     DevBuf aabb_min, leaf_box;                  // {min, max} float4 pairs (32 B per box): per q in input order / per leaf slot in sorted order
@@ -140,7 +142,8 @@ SceneView scene_view(const Ctx* c);
 
 // lbvh.cu
 int lbvh_build(Ctx* c);
-int lbvh_ingest_tris(Ctx* c, int n_spheres, int n_quads, int n_tris, bool have_normals, bool have_mat, int mat_default);
+int lbvh_ingest_tris(Ctx* c, int n_spheres, int n_quads, int n_tris, bool have_normals, bool have_mat, int mat_default, bool positions_only = false);
+int lbvh_finish_tris(Ctx* c, bool have_normals, bool have_mat, int mat_default);
 int sort_ray_queue(Ctx* c, cudaStream_t st, int set, int64_t capacity, const uint32_t* n_dev, const float4* so, const float4* sd,
                    const float4* sb, float4* to, float4* td, float4* tb);
 // wavefront.cu

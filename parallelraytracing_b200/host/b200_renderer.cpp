@@ -28,10 +28,10 @@ void B200Renderer::Init(Film& film, const Scene& scene, const Camera& camera)
     }
     const float sky[3] = {0.4f, 0.3f, 0.6f};              // m_SkyLight, cpu/renderer.h:31
     int nt = (int)fs.tri_material.size();
-    if (prt_set_scene(m_Ctx, fs.spheres.data(), (int)fs.spheres.size(), fs.quads.data(), (int)fs.quads.size(),
-                      fs.tri_verts.data(), fs.tri_normals.data(), fs.tri_material.data(), -1, nt, fs.tri_prim_base,
-                      fs.materials.data(), (int)fs.materials.size(), sky) != PRT_OK ||
-        prt_build_bvh(m_Ctx) != PRT_OK) {
+    // scene upload + BVH build in one call: the build runs on the positions while the normals are still crossing PCIe
+    if (prt_set_scene_build(m_Ctx, fs.spheres.data(), (int)fs.spheres.size(), fs.quads.data(), (int)fs.quads.size(),
+                            fs.tri_verts.data(), fs.tri_normals.data(), fs.tri_material.data(), -1, nt, fs.tri_prim_base,
+                            fs.materials.data(), (int)fs.materials.size(), sky) != PRT_OK) {
         std::fprintf(stderr, "[B200Renderer] %s\n", prt_last_error(m_Ctx));
         return;
     }

@@ -62,8 +62,7 @@ class B200Renderer:
         try:
             if self.ctx is None:
                 self.ctx = Context(self.m_Device)
-            self.ctx.set_scene(scene)
-            self.ctx.build_bvh()
+            self.ctx.set_scene_build(scene)            # scene upload + BVH build in one call (b200_renderer.cpp does the same)
             self.ok = True
         except PrtError as e:
             print("[B200Renderer]", e, file=sys.stderr)

@@ -86,3 +86,41 @@ def test_calls_out_of_order_fail_cleanly():
         assert np.array_equal(a, c.read_accum())
     finally:
         c.close()
+
+
+def test_set_scene_build_equals_the_two_calls():
+    """prt_set_scene_build (positions first, BVH build under the upload of normals and materials) leaves the device in the state
+    prt_set_scene + prt_build_bvh leave it in: integer outputs, node bytes, hit records with their normals and materials, and
+    images - with vertex normals, with flat normals (NULL), from pageable and from page-locked arrays, and without triangles."""
+    import dataclasses
+    import util
+    from parallelraytracing_b200.capi import pinned_copy
+    mesh = S.mesh_scene(S.bundled_mesh("dragon"), subdiv=1, name="dragon240k")        # 240 K triangles with vertex normals, 3 materials + ground
+    soup = S.random_triangle_soup(30000, seed=9)
+    flat = dataclasses.replace(soup, tri_normals=None)
+    pinned = dataclasses.replace(mesh, tri_verts=pinned_copy(mesh.tri_verts), tri_normals=pinned_copy(mesh.tri_normals),
+                                 tri_material=pinned_copy(mesh.tri_material))
+    cam = S.Camera(pos=(0.0, 1.0, 5.0), front=S._normalize(S._v3(0, -1, -5)), width=96, height=64)
+    a, b = Context(0), Context(0)
+    try:
+        for sd in (mesh, flat, pinned, S.make_scene(S.ScenePreset.RANDOM_BALLS_LARGE), S.cornell(), soup):
+            for builder in (1, 0):
+                for c in (a, b):
+                    c.set_option("bvh_builder", builder)
+                a.set_scene(sd); a.build_bvh()
+                b.set_scene_build(sd)
+                ga, gb = a.debug_lbvh(), b.debug_lbvh()
+                for k in ga:
+                    assert ga[k].tobytes() == gb[k].tobytes(), (sd.name, builder, k)
+                if sd.n_prims >= 4096:
+                    assert a.debug_wide().tobytes() == b.debug_wide().tobytes()
+                rays = util.fixed_ray_batch(sd, 20000, seed=2, clamp_extent=60.0)
+                ha, hb = a.trace_batch(rays, use_bvh=2), b.trace_batch(rays, use_bvh=2)
+                assert ha.tobytes() == hb.tobytes(), (sd.name, builder)
+                assert (ha["prim_id"] >= 0).sum() > 100
+                for c in (a, b):
+                    c.set_camera(cam); c.clear_accum(); c.render(2, 6, seed=3)
+                assert np.array_equal(a.read_accum(), b.read_accum()), (sd.name, builder)
+                assert a.stats().rays_total == b.stats().rays_total
+    finally:
+        a.close(); b.close()

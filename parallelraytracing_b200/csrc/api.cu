@@ -454,6 +454,7 @@ static int set_scene_impl(prt_ctx* ctx, const prt_sphere* spheres, int n_spheres
     }
     // records the build gathers + every triangle's box and their share of the bounds (k_ingest_tris)
     if ((rc = lbvh_ingest_tris(c, n_spheres, n_quads, n_tris, tri_normals != nullptr, tri_material != nullptr, tri_material_default, overlap))) return rc;
+    c->tri_deferred = overlap; c->def_normals = tri_normals != nullptr; c->def_mat = tri_material != nullptr; c->def_mat_default = tri_material_default;
     c->n_spheres = n_spheres; c->n_quads = n_quads; c->n_tris = n_tris; c->n_mats = n_materials;
     c->n_prims = n_spheres + n_quads + n_tris;
     c->tri_prim_base = tri_prim_base;
@@ -481,14 +482,14 @@ static int set_scene_impl(prt_ctx* ctx, const prt_sphere* spheres, int n_spheres
                 if (!up_rc) up_err = cudaStreamSynchronize(c->up_stream);
             });
         }
-        c->positions_only = overlap;
+        c->finish_later = overlap;                              // the normals are still in flight: k_finish_tris runs below, after the join
         rc = lbvh_build(c);
-        c->positions_only = false;
+        c->finish_later = false;
         if (uploader.joinable()) uploader.join();
         if (rc == PRT_OK && up_rc != PRT_OK) rc = up_rc;
         if (rc == PRT_OK && up_err != cudaSuccess) rc = set_err(c, PRT_ERR_CUDA, std::string("prt_set_scene_build: upload: ") + cudaGetErrorString(up_err));
         if (rc == PRT_OK && overlap) {
-            rc = lbvh_finish_tris(c, tri_normals != nullptr, tri_material != nullptr, tri_material_default);
+            rc = lbvh_finish_tris(c);
             if (rc == PRT_OK) {
                 cudaError_t e = cudaStreamSynchronize(c->stream);
                 if (e == cudaSuccess) e = cudaGetLastError();

@@ -143,7 +143,7 @@ int lbvh_ingest_tris(Ctx* c, int n_spheres, int n_quads, int n_tris, bool have_n
     k_init_bounds<<<1, 32, 0, c->stream>>>((int*)c->tri_bounds.p);
     if (n_tris > 0)
         k_ingest_tris<<<(unsigned)((nt + 255) / 256), 256, 0, c->stream>>>(n_tris, (const float*)c->raw_v.p, have_normals ? (const float*)c->raw_n.p : nullptr,
-            have_mat ? (const int*)c->raw_m.p : nullptr, mat_default, (float4*)c->tri_in_v.p, (float4*)c->tri_in_v.p + 3,
+            have_mat && !positions_only ? (const int*)c->raw_m.p : nullptr, mat_default, (float4*)c->tri_in_v.p, (float4*)c->tri_in_v.p + 3,
             (float4*)c->aabb_min.p + 2 * ((size_t)n_spheres + n_quads), (int*)c->tri_bounds.p, positions_only ? 1 : 0);
     return PRT_OK;
 }
@@ -530,11 +530,11 @@ __global__ void k_finish_tris(int n, int ns, int nq, const uint32_t* __restrict_
         for (int k = 0; k < 3; ++k) out_n[3 * pos + k] = make_float4(nx, ny, nz, 0.f);
     }
 }
-int lbvh_finish_tris(Ctx* c, bool have_normals, bool have_mat, int mat_default) {
+int lbvh_finish_tris(Ctx* c) {
     const int n = c->n_prims;
-    if (n <= 0 || c->n_tris <= 0) return PRT_OK;
+    if (n <= 0 || c->n_tris <= 0 || !c->tri_deferred) return PRT_OK;
     k_finish_tris<<<(n + 255) / 256, 256, 0, c->stream>>>(n, c->n_spheres, c->n_quads, (const uint32_t*)c->vals[c->sorted_slot].p,
-        have_normals ? (const float*)c->raw_n.p : nullptr, have_mat ? (const int*)c->raw_m.p : nullptr, mat_default,
+        c->def_normals ? (const float*)c->raw_n.p : nullptr, c->def_mat ? (const int*)c->raw_m.p : nullptr, c->def_mat_default,
         (float4*)c->tri_v.p, (float4*)c->tri_n.p);
     return PRT_OK;
 }
@@ -964,7 +964,7 @@ int lbvh_build(Ctx* c) {
     if (n > 1) {
         k_gather_tris<<<G, T, 0, st>>>(n, ns, nq, c->tri_prim_base, sprim, (const float4*)c->tri_in_v.p,
                                        (const float4*)c->tri_in_v.p + 3, (float4*)c->tri_v.p, (float4*)c->tri_n.p,
-                                       (const float4*)c->aabb_min.p, (float4*)c->leaf_box.p, c->positions_only ? 1 : 0);
+                                       (const float4*)c->aabb_min.p, (float4*)c->leaf_box.p, c->tri_deferred ? 1 : 0);
         bool ploc_done = false;
         if (want_ploc) {
             // PLOC over the sorted leaves; on failure (no convergence / a tree deeper than the traversal stack allows) the
@@ -1015,7 +1015,8 @@ int lbvh_build(Ctx* c) {
     if (n == 1 && nt > 0)                                                 // n > 1: launched before the refit, above
         k_gather_tris<<<G, T, 0, st>>>(n, ns, nq, c->tri_prim_base, sprim, (const float4*)c->tri_in_v.p,
                                        (const float4*)c->tri_in_v.p + 3, (float4*)c->tri_v.p, (float4*)c->tri_n.p,
-                                       (const float4*)c->aabb_min.p, (float4*)c->leaf_box.p, c->positions_only ? 1 : 0);
+                                       (const float4*)c->aabb_min.p, (float4*)c->leaf_box.p, c->tri_deferred ? 1 : 0);
+    if (c->tri_deferred && !c->finish_later && (rc = lbvh_finish_tris(c))) return rc;   // normals / materials into their leaf slots
     PRT_CUDA(c, cudaEventRecord(c->ev1, st));
     PRT_CUDA(c, cudaStreamSynchronize(st));
     PRT_CUDA(c, cudaGetLastError());

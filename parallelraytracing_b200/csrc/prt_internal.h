@@ -41,7 +41,10 @@ struct Ctx {
     DevBuf prim_id_of_q;                        // int per q: reference list index
     float sky[3] = {0.4f, 0.3f, 0.6f};
     bool scene_set = false;
-    bool positions_only = false;                // prt_set_scene_build: the build runs on the positions while normals / materials upload
+    // prt_set_scene_build: the input records hold positions only; normals / materials stay in raw_n / raw_m and every build ends
+    // with k_finish_tris (tri_deferred). While the upload is still in flight the API layer runs that step itself (finish_later).
+    bool tri_deferred = false, finish_later = false, def_normals = false, def_mat = false;
+    int def_mat_default = 0;
     cudaStream_t up_stream = nullptr;           //   ... on this stream, from a second host thread
 
     // ---- LBVH ----
@@ -143,7 +146,7 @@ SceneView scene_view(const Ctx* c);
 // lbvh.cu
 int lbvh_build(Ctx* c);
 int lbvh_ingest_tris(Ctx* c, int n_spheres, int n_quads, int n_tris, bool have_normals, bool have_mat, int mat_default, bool positions_only = false);
-int lbvh_finish_tris(Ctx* c, bool have_normals, bool have_mat, int mat_default);
+int lbvh_finish_tris(Ctx* c);
 int sort_ray_queue(Ctx* c, cudaStream_t st, int set, int64_t capacity, const uint32_t* n_dev, const float4* so, const float4* sd,
                    const float4* sb, float4* to, float4* td, float4* tb);
 // wavefront.cu

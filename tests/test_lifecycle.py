@@ -122,5 +122,11 @@ def test_set_scene_build_equals_the_two_calls():
                     c.set_camera(cam); c.clear_accum(); c.render(2, 6, seed=3)
                 assert np.array_equal(a.read_accum(), b.read_accum()), (sd.name, builder)
                 assert a.stats().rays_total == b.stats().rays_total
+            # a later prt_build_bvh with other options rebuilds from what prt_set_scene_build left on the device
+            for c in (a, b):
+                c.set_option("bvh_builder", 1); c.set_option("ploc_radius", 2); c.build_bvh(); c.set_option("ploc_radius", 4)
+                c.clear_accum(); c.render(2, 6, seed=4)
+            assert a.debug_lbvh()["node_children"].tobytes() == b.debug_lbvh()["node_children"].tobytes()
+            assert np.array_equal(a.read_accum(), b.read_accum()), (sd.name, "rebuild")
     finally:
         a.close(); b.close()

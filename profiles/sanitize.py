@@ -28,6 +28,9 @@ for builder in (1, 0):
     c.clear_accum(); c.render(2, 8, seed=1)                       # staged: raygen, extend_wide, shade, tail, resolve
     print("soup20k builder", builder, "rays", c.stats().rays_total, flush=True)
 c.set_option("bvh_builder", 1)
+c.set_scene_build(soup)                                             # Init in one call: positions-only ingest / gather, k_finish_tris
+c.clear_accum(); c.render(1, 4, seed=7)
+c.build_bvh()                                                      # a rebuild from the deferred arrays
 c.set_option("sort_rays", 1); c.set_option("sort_min_rays", 0)
 c.clear_accum(); c.render(1, 4, seed=2)
 c.set_option("sort_rays", 0)

@@ -200,3 +200,43 @@ def test_gpu_image_fuzz_vs_oracle(oracle, seed):
                 ctx.set_option(k, {"fused": -1, "bvh_wide": -1, "bvh_builder": 1, "tail_bounce": 2, "tail_pool": 1}[k])
     finally:
         ctx.close()
+
+
+BOUNDARY_SIZES = [2, 3, 4, 5, 7, 8, 9, 31, 32, 33, 255, 256, 257, 1023, 1024, 1025, 2049, 4095, 4096, 4097, 8193, 65537,
+                  163839, 163840, 163841, 327681]
+
+
+@pytest.mark.gpu
+def test_builder_at_boundary_sizes_vs_oracle(oracle):
+    """Primitive counts around every tile / threshold of the build (32-lane warps, 256-thread CTAs, 1024-cluster PLOC tiles,
+    4096-key sort tiles and the 4096-primitive wide-node threshold, the 160 K small-round switch of PLOC), plain and with a
+    quarter of the triangles duplicated: integer outputs, node boxes, hit records and traversal counters against the oracle,
+    both builders, through the one-call Init."""
+    import dataclasses
+    from parallelraytracing_b200.capi import Context
+    ctx = Context(0)
+    try:
+        for n in BOUNDARY_SIZES:
+            for dups in (False, True):
+                sd = S.random_triangle_soup(n, seed=n)
+                if dups:
+                    if n < 8:
+                        continue
+                    tv = sd.tri_verts.copy(); k = n // 4
+                    tv[:k] = tv[k:2 * k]; tv[2 * k:2 * k + k // 2] = tv[2 * k]
+                    sd = dataclasses.replace(sd, tri_verts=tv)
+                for builder in (1, 0):
+                    ctx.set_option("bvh_builder", builder); ctx.set_option("bvh_wide", 1)
+                    ctx.set_scene_build(sd)
+                    osc = oracle.scene(sd); osc.set_builder(builder, 4)
+                    g, o = ctx.debug_lbvh(), osc.get_lbvh()
+                    for key in ("morton", "sorted_prim", "node_children", "node_bounds"):
+                        assert g[key].tobytes() == o[key].tobytes(), (n, dups, builder, key)
+                    rays = util.incoherent_rays(2000, 50.0, seed=n)
+                    cnt = np.zeros(2, np.uint64)
+                    want = osc.trace_batch(rays, use_bvh=2, counters=cnt, n_threads=16)
+                    ctx.enable_counters(True); got = ctx.trace_batch(rays, use_bvh=2); st = ctx.stats(); ctx.enable_counters(False)
+                    assert same_records(got, want), (n, dups, builder)
+                    assert (st.nodes_visited, st.prims_tested) == (int(cnt[0]), int(cnt[1])), (n, dups, builder)
+    finally:
+        ctx.close()

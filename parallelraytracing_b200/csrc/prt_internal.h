@@ -114,7 +114,7 @@ struct Ctx {
     int brute_max_prims = 8;                    // fused kernels: sphere/quad scenes this small skip the BVH (uniform loop over the list)
     int persistent = 1;                         // staged extend = persistent threads with per-lane dynamic fetch
     int pt_refill_wide = 20;                    // same threshold for the 4-wide kernel (measured best 20: dragon960k, soup1m, soup10m)
-    int pt_refill = 16;                         // refill the warp when fewer lanes than this are traversing
+    int pt_refill = 10;                         // refill the warp when fewer lanes than this are traversing (two-child walk, scenes below wide_min_prims; 809 spheres, Mrays/s: 4: 9 289, 8: 9 580, 10: 9 593, 12: 9 554, 14: 9 479, 16: 9 360)
     int rr_start = -1;                          // estimator options, both OFF by default so that parity with the
     float firefly_clamp = 0.f;                  // reference's estimator stays checkable: Russian roulette / radiance clamp
     int stage_timing = 1;                       // CUDA-event pairs around the hot kernels

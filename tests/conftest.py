@@ -27,3 +27,23 @@ def ref():
     if lib is None:
         pytest.skip("oracle/_ref/libprt_ref.so not built (needs /root/reference; run `make -C oracle ref`)")
     return lib
+
+
+def pytest_sessionfinish(session, exitstatus):
+    """PRT_CHECKED=1 python -m pytest tests -m gpu runs every GPU test through the bounds-checked library; no check may have fired
+    in this process by the end (the provoked overflow of test_checked_build.py happens in a subprocess of its own)."""
+    if os.environ.get("PRT_CHECKED") != "1":
+        return
+    try:
+        import torch
+        if not torch.cuda.is_available():
+            return
+        from parallelraytracing_b200.capi import Context
+        with Context(0) as c:
+            flags = c.check_flags()
+    except Exception as e:                                            # no library / no device: nothing to report
+        print("\n[checked build] flags not read:", e)
+        return
+    print("\n[checked build] check flags at session end: 0x%x" % flags)
+    if flags != 0x40000000:
+        session.exitstatus = 1

@@ -130,3 +130,32 @@ def test_set_scene_build_equals_the_two_calls():
             assert np.array_equal(a.read_accum(), b.read_accum()), (sd.name, "rebuild")
     finally:
         a.close(); b.close()
+
+
+def test_two_contexts_in_two_host_threads():
+    """A context is not thread-safe, but contexts are independent of each other: two host threads, one context each, building
+    and rendering at the same time on the same GPU, get the images they get one after the other (ctypes drops the GIL
+    around every call, so the calls really overlap)."""
+    import threading
+    jobs = [(S.mesh_scene(S.bundled_mesh("dragon"), subdiv=1, name="dragon240k"), S.Camera(pos=(0.0, 1.0, 5.0), front=S._normalize(S._v3(0, -1, -5)), width=160, height=96), 6),
+            (S.cornell(), S.Camera(width=192, height=128), 8)]
+
+    def run(job, out, reps):
+        sd, cam, depth = job
+        with Context(0) as c:
+            for k in range(reps):
+                c.set_scene_build(sd); c.set_camera(cam); c.clear_accum()
+                c.render(4, depth, seed=11)
+                out.append((c.read_accum(), c.stats().rays_total))
+
+    want = []
+    for job in jobs:
+        o = []; run(job, o, 1); want.append(o[0])
+    outs = [[], []]
+    th = [threading.Thread(target=run, args=(jobs[k], outs[k], 12)) for k in range(2)]
+    for t in th: t.start()
+    for t in th: t.join()
+    for k in range(2):
+        assert len(outs[k]) == 12
+        for img, rays in outs[k]:
+            assert rays == want[k][1] and np.array_equal(img, want[k][0]), "context %d disturbed by its neighbour" % k

@@ -322,7 +322,7 @@ int  prt_enable_counters(prt_ctx* ctx, int on);
 int  prt_get_stats(prt_ctx* ctx, prt_stats* out);
 
 /* Tuning knobs (all optional): "wave_paths" (paths in flight per wave), "ctas_per_sm", "fused", "fused_max_prims",
- * "brute_max_prims", "persistent", "pt_refill", "pt_refill_wide", "bvh_wide", "wide_min_prims", "bvh_builder", "ploc_radius", "overlap",
+ * "brute_max_prims", "persistent", "pt_refill", "pt_refill_wide", "bvh_wide", "wide_min_prims", "wide_compact", "bvh_builder", "ploc_radius", "overlap",
  * "stage_timing", "use_graph", "fast_math" (tolerance-mode float math on the shading side: changes radiance within RMSE 1e-3 / max-rel 1e-2, never a hit id), "rr_start", "firefly_clamp_milli", "multi_partition", "multi_reduce" (multi-device contexts), and for small waves (one sample per call, the reference's
  * ProgressiveRender granularity) "tail_bounce" (0 = one launch per bounce always), "tail_adaptive", "tail_pool", "tail_rays", "tail_rays_staged",
  * "tail_max_paths": bounces from the tail start on run inside one kernel; "sort_rays", "sort_key_bits",

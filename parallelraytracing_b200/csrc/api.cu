@@ -372,7 +372,7 @@ void prt_destroy(prt_ctx* ctx) {
     DevBuf* bufs[] = {&c->spheres, &c->quads, &c->quad_mat, &c->mats, &c->tri_in_v, &c->tri_in_n, &c->tri_in_mat,
                       &c->prim_id_of_q, &c->aabb_min, &c->leaf_box, &c->scene_bounds, &c->keys[0], &c->keys[1],
                       &c->vals[0], &c->vals[1], &c->block_hist, &c->children, &c->parent, &c->node_min, &c->node_max,
-                      &c->flags, &c->nodes, &c->wnodes, &c->tri_v, &c->tri_n, &c->morton, &c->accum_own, &c->display,
+                      &c->flags, &c->nodes, &c->wnodes, &c->wnodes_c, &c->wc_queue, &c->tri_v, &c->tri_n, &c->morton, &c->accum_own, &c->display,
                       &c->q_o[0], &c->q_o[1], &c->q_d[0], &c->q_d[1], &c->q_b[0], &c->q_b[1], &c->hits, &c->contrib,
                       &c->q2_o[0], &c->q2_o[1], &c->q2_d[0], &c->q2_d[1], &c->q2_b[0], &c->q2_b[1], &c->hits2, &c->contrib2,
                       &c->qcount2, &c->qcount, &c->stats_dev, &c->ray_keys[0][0], &c->ray_keys[0][1], &c->ray_keys[1][0],
@@ -827,6 +827,7 @@ int prt_set_option(prt_ctx* ctx, const char* key, int64_t value) {
     else if (!strcmp(key, "brute_max_prims")) c->brute_max_prims = (int)value;
     else if (!strcmp(key, "bvh_wide")) c->bvh_wide = value < 0 ? -1 : (value ? 1 : 0);   // takes effect at the next prt_build_bvh
     else if (!strcmp(key, "wide_min_prims")) c->wide_min_prims = (int)value;
+    else if (!strcmp(key, "wide_compact")) c->wide_compact = value ? 1 : 0;                      // takes effect at the next prt_build_bvh
     else if (!strcmp(key, "bvh_builder")) c->bvh_builder = value ? 1 : 0;                        // takes effect at the next prt_build_bvh
     else if (!strcmp(key, "ploc_radius")) { if (value < 1 || value > 8) return set_err(c, PRT_ERR_INVALID, "ploc_radius out of range (1..8)"); c->ploc_radius = (int)value; }
     else if (!strcmp(key, "overlap")) c->overlap = value ? 1 : 0;

@@ -901,6 +901,72 @@ unsigned lbvh_check_flags() {
 }
 
 // ------------------------------------------------------------------ host driver
+// ------------------------------------------------------------------ compact wide nodes (option wide_compact)
+// k_emit_wide writes a record for EVERY internal node (any of them could be a wide root); the walk only ever reaches the ones a
+// reachable record names as a slot - about 45 % - so half of every 128-byte line of that array is dead weight in L1 and L2.
+// One breadth-first pass from the root copies the reachable records into a dense array: a node's internal children get
+// consecutive new indices (one atomicAdd per node), so siblings share cache lines, and the parent's copy is written with
+// the new indices in place. Cooperative launch: one grid.sync per level. The order within a level depends on the timing of
+// the atomics: the layout is not reproducible, the walk (order of visits, results, counters) is the same as on the full array.
+__global__ void __launch_bounds__(256) k_compact_wide(const WideNode* __restrict__ wide, WideNode* __restrict__ out, int* __restrict__ qa, int* __restrict__ qb,
+                                                      int* __restrict__ ctl /* [0..2] frontier counts of levels L, L+1, L+2 (rotating), [3] nodes placed */) {
+    cg::grid_group grid = cg::this_grid();
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+    if (tid == 0) { qa[0] = 0; qa[1] = 0; ctl[0] = 1; ctl[1] = 0; ctl[2] = 0; ctl[3] = 1; }     // frontier entries: (old index, new index) pairs
+    grid.sync();
+    int* fa = qa; int* fb = qb;
+    for (int level = 0; level < 4096; ++level) {
+        const int cnt = ((volatile int*)ctl)[level % 3];
+        if (cnt == 0) break;
+        int* cnt_next = ctl + (level + 1) % 3;
+        if (tid == 0) ctl[(level + 2) % 3] = 0;                           // the counter of the level after next: nobody reads or adds to it now
+        for (int i0 = tid & ~31; i0 < cnt; i0 += nth) {                  // whole warps: the two counters take ONE atomic per warp
+            const int i = i0 + (int)(threadIdx.x & 31u);
+            const bool act = i < cnt;
+            int old_i = 0, new_i = 0;
+            WideNode w;
+            int kid[4] = {0, 0, 0, 0}; int nk = 0;
+            if (act) {
+                old_i = fa[2 * i]; new_i = fa[2 * i + 1];
+                w = wide[old_i];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const bool empty = ((w.qlo[0] >> (8 * k)) & 255u) == 255u && ((w.qhi[0] >> (8 * k)) & 255u) == 0u;
+                    kid[k] = (!empty && w.code[k] >= 0) ? 1 : 0;
+                    nk += kid[k];
+                }
+            }
+            int incl = nk;                                               // warp prefix of the child counts
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, d); if ((int)(threadIdx.x & 31u) >= d) incl += v; }
+            const int total = __shfl_sync(0xffffffffu, incl, 31);
+            int base_new = 0, base_q = 0;
+            if ((threadIdx.x & 31u) == 31u && total) { base_new = atomicAdd(&ctl[3], total); base_q = atomicAdd(cnt_next, total); }
+            base_new = __shfl_sync(0xffffffffu, base_new, 31) + incl - nk;
+            base_q = __shfl_sync(0xffffffffu, base_q, 31) + incl - nk;
+            if (!act) continue;
+            if (nk) {
+                int j = 0;
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    if (kid[k]) {
+                        fb[2 * (base_q + j)] = w.code[k]; fb[2 * (base_q + j) + 1] = base_new + j;
+                        w.code[k] = base_new + j; ++j;
+                    }
+            }
+            // empty slots keep "the code of slot 0" (see WideNode)
+#pragma unroll
+            for (int k = 1; k < 4; ++k) {
+                const bool empty = ((w.qlo[0] >> (8 * k)) & 255u) == 255u && ((w.qhi[0] >> (8 * k)) & 255u) == 0u;
+                if (empty) w.code[k] = w.code[0];
+            }
+            out[new_i] = w;
+        }
+        grid.sync();
+        int* t = fa; fa = fb; fb = t;
+    }
+}
+
 int lbvh_build(Ctx* c) {
     const int n = c->n_prims, ns = c->n_spheres, nq = c->n_quads, nt = c->n_tris;
     c->bvh_built = false; c->wide_built = false;
@@ -1005,6 +1071,18 @@ int lbvh_build(Ctx* c) {
         if (want_wide) {
             k_emit_wide<<<G, T, 0, st>>>(n - 1, parent, (const BvhNode*)c->nodes.p, (WideNode*)c->wnodes.p);
             c->wide_built = true;
+            c->wide_compacted = false;
+            if (c->wide_compact && n > 2) {
+                if ((rc = dev_reserve(c, c->wnodes_c, nn * sizeof(WideNode))) || (rc = dev_reserve(c, c->wc_queue, nn * 16 + 64))) return rc;
+                const WideNode* src = (const WideNode*)c->wnodes.p; WideNode* dst = (WideNode*)c->wnodes_c.p;
+                int* qa = (int*)c->wc_queue.p; int* qb = qa + 2 * nn; int* ctl = qb + 2 * nn;
+                int per_sm = 0;
+                PRT_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_compact_wide, 256, 0));
+                const int grid = std::max(1, std::min((n + 255) / 256, c->num_sms * std::max(1, per_sm)));
+                void* args[] = {&src, &dst, &qa, &qb, &ctl};
+                PRT_CUDA(c, cudaLaunchCooperativeKernel((const void*)k_compact_wide, dim3(grid), dim3(256), args, 0, st));
+                c->wide_compacted = true;
+            }
         }
         c->root_code = 0;
     } else {

@@ -1059,7 +1059,7 @@ SceneView scene_view(const Ctx* c) {
     v.mats = (const MatRec*)c->mats.p; v.n_mats = c->n_mats;
     v.quad_mat = (const int*)c->quad_mat.p;
     v.nodes = (const BvhNode*)c->nodes.p; v.n_prims = c->n_prims;
-    v.wnodes = c->wide_built ? (const WideNode*)c->wnodes.p : nullptr;
+    v.wnodes = c->wide_built ? (const WideNode*)(c->wide_compacted ? c->wnodes_c.p : c->wnodes.p) : nullptr;
     v.root_code = c->root_code;
     v.tri_tmin = 0.001f;                                  // kShapeRayTMin, shape.h:128
     v.sky_r = c->sky[0]; v.sky_g = c->sky[1]; v.sky_b = c->sky[2];

@@ -140,7 +140,7 @@ typedef struct prt_stats {
 int  prt_create(prt_ctx** out, int device);
 /* ONE context over n_devices GPUs of this process (SURVEY 8b export list / 8e: single process, one stream per device,
  * ncclCommInitAll). device_ids[0] is the root: its accumulation buffer is the one every other entry point reads. The scene,
- * the BVH (built on every device, identical bits) and the camera are replicated; prt_render* split the call over the devices
+ * the BVH (built on every device: the same hierarchy, node for node) and the camera are replicated; prt_render* split the call over the devices
  * (option "multi_partition": PRT_PARTITION_SAMPLES default, PRT_PARTITION_TILES), enqueue every device's waves and, behind
  * them on the same streams with no host synchronisation in between, ONE float sum-reduce to the root: ncclReduce over
  * NVLink (libnccl.so.2 is loaded at run time; option "multi_reduce" = 1), or a peer-to-peer kernel on the root that reads

@@ -302,8 +302,9 @@ int  prt_debug_lbvh(prt_ctx* ctx, uint32_t* morton, uint32_t* sorted_prim,
                     float* node_bounds, float* scene_bounds);
 /* The 4-wide quantised nodes (only when built: option bvh_wide, or automatically for large scenes), raw device
  * layout: 16 words per internal node {ox, oy, oz, scale_x, code[4], qlo[3], qhi[3], scale_y, scale_z}, indexed like
- * the two-child nodes; every internal node has a record (greedy collapse by surface area, 2..4 slots). Returns
- * PRT_ERR_INVALID if not built. */
+ * the two-child nodes; every internal node has a record (greedy collapse by surface area, 2..4 slots). The walk itself
+ * reads a dense breadth-first copy of the records reachable from the root (option wide_compact, default on; same visits,
+ * hits and counters). Returns PRT_ERR_INVALID if not built. */
 int  prt_debug_wide(prt_ctx* ctx, uint32_t* words);
 /* The repo's own memcheck (compute-sanitizer is closed on the GPU pool): libprt_b200_checked.so is the same library compiled
  * with -DPRT_CHECKED=1 - every data-derived index in device code (traversal stack pointers, queue slots, node and leaf

@@ -188,7 +188,8 @@ struct SceneView {
     const MatRec*    mats;     int n_mats;
     const int*       quad_mat; // material per quad (quads' own record is full)
     const BvhNode*   nodes;    int n_prims;
-    const WideNode*  wnodes;   // 4-wide quantised nodes, indexed like `nodes` (only even-depth entries exist); NULL = none
+    const WideNode*  wnodes;   // 4-wide quantised nodes: the dense breadth-first copy of the reachable records (k_compact_wide; root = 0) or,
+                               // with wide_compact = 0, one record per internal node indexed like `nodes`; NULL = none
     int              root_code; // root: 0 if n_prims>1, leaf code (negative-as-~) if n_prims==1
     float            tri_tmin;
     float sky_r, sky_g, sky_b;

@@ -60,7 +60,7 @@ struct Ctx {
     int sort_min_rays = 1 << 20;                // ... only while the queue is expected to hold at least this many rays
     DevBuf children, parent, node_min, node_max, flags;
     DevBuf nodes;                               // BvhNode per internal node
-    DevBuf wnodes;                              // WideNode at the index of every even-depth internal node
+    DevBuf wnodes;                              // one WideNode per internal node (every node could be a wide root; prt_debug_wide returns this array)
     int bvh_wide = -1;                          // 4-wide quantised nodes for the staged extend: 1 always, 0 never, -1 by scene size
     int wide_min_prims = 4096;                  // auto: below this the two-child tree is L1-resident and its cheaper node step wins
     bool wide_built = false;

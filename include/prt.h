@@ -140,7 +140,7 @@ typedef struct prt_stats {
 int  prt_create(prt_ctx** out, int device);
 /* ONE context over n_devices GPUs of this process (SURVEY 8b export list / 8e: single process, one stream per device,
  * ncclCommInitAll). device_ids[0] is the root: its accumulation buffer is the one every other entry point reads. The scene,
- * the BVH (built on every device: the same hierarchy, node for node) and the camera are replicated; prt_render* split the call over the devices
+ * the BVH (built on every device, identical bits) and the camera are replicated; prt_render* split the call over the devices
  * (option "multi_partition": PRT_PARTITION_SAMPLES default, PRT_PARTITION_TILES), enqueue every device's waves and, behind
  * them on the same streams with no host synchronisation in between, ONE float sum-reduce to the root: ncclReduce over
  * NVLink (libnccl.so.2 is loaded at run time; option "multi_reduce" = 1), or a peer-to-peer kernel on the root that reads
@@ -306,6 +306,11 @@ int  prt_debug_lbvh(prt_ctx* ctx, uint32_t* morton, uint32_t* sorted_prim,
  * reads a dense breadth-first copy of the records reachable from the root (option wide_compact, default on; same visits,
  * hits and counters). Returns PRT_ERR_INVALID if not built. */
 int  prt_debug_wide(prt_ctx* ctx, uint32_t* words);
+/* The dense copy the walk reads (option wide_compact, default on): the records reachable from the root in breadth-first order,
+ * root first, a node's internal children at consecutive indices, internal child codes = indices into THIS array. *n_nodes =
+ * number of records; words (capacity_nodes x 16 words) may be NULL to ask for the count only. Deterministic: the same
+ * bytes on every run and device (tests rebuild it from prt_debug_wide's array on the host and compare). */
+int  prt_debug_wide_compact(prt_ctx* ctx, uint32_t* words, int capacity_nodes, int* n_nodes);
 /* The repo's own memcheck (compute-sanitizer is closed on the GPU pool): libprt_b200_checked.so is the same library compiled
  * with -DPRT_CHECKED=1 - every data-derived index in device code (traversal stack pointers, queue slots, node and leaf
  * codes, PLOC positions and node ids, sort scatter positions) is tested before the access, violations set PRT_CHK_* bits

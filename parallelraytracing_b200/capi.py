@@ -48,7 +48,7 @@ EXPORTS = [
     "prt_create", "prt_create_multi", "prt_destroy", "prt_last_error", "prt_version", "prt_set_scene", "prt_set_scene_build", "prt_build_bvh",
     "prt_set_camera", "prt_render", "prt_render_fresh", "prt_render_region", "prt_wait_event", "prt_clear_accum", "prt_scale_accum", "prt_accum_device_ptr",
     "prt_set_accum_buffer", "prt_read_accum", "prt_accum_spp", "prt_set_accum_spp", "prt_resolve_display", "prt_trace_batch", "prt_trace_batch_static",
-    "prt_debug_lbvh", "prt_debug_wide", "prt_debug_scatter", "prt_debug_ploc_trace", "prt_debug_check_flags", "prt_host_alloc", "prt_host_free", "prt_num_prims", "prt_enable_counters", "prt_get_stats", "prt_set_option",
+    "prt_debug_lbvh", "prt_debug_wide", "prt_debug_wide_compact", "prt_debug_scatter", "prt_debug_ploc_trace", "prt_debug_check_flags", "prt_host_alloc", "prt_host_free", "prt_num_prims", "prt_enable_counters", "prt_get_stats", "prt_set_option",
 ]
 
 _lib = None
@@ -102,6 +102,7 @@ def load_library():
     lib.prt_trace_batch_static.argtypes = [vp, vp, i32, vp, i32, vp]
     lib.prt_debug_lbvh.argtypes = [vp, vp, vp, vp, vp, vp, vp]
     lib.prt_debug_wide.argtypes = [vp, vp]
+    lib.prt_debug_wide_compact.argtypes = [vp, vp, i32, vp]
     lib.prt_debug_scatter.argtypes = [vp, vp, vp, vp, vp, vp, u64, i32, vp]
     lib.prt_debug_ploc_trace.argtypes = [vp, vp, vp, i32]
     lib.prt_debug_check_flags.argtypes = [vp]
@@ -271,6 +272,14 @@ class Context:
                                             _ptr(d["node_parent"]), _ptr(d["node_bounds"]), _ptr(d["scene_bounds"])),
                     "prt_debug_lbvh")
         return d
+
+    def debug_wide_compact(self):
+        """(n_live, 16) uint32: the dense breadth-first array of reachable WideNode records the walk reads."""
+        n = C.c_int(0)
+        self._check(self.lib.prt_debug_wide_compact(self.h, None, 0, C.byref(n)), "prt_debug_wide_compact")
+        w = np.zeros((n.value, 16), np.uint32)
+        self._check(self.lib.prt_debug_wide_compact(self.h, _ptr(w), n.value, C.byref(n)), "prt_debug_wide_compact")
+        return w
 
     def debug_wide(self):
         """(n-1, 16) uint32: raw WideNode records; rows of odd-depth nodes are undefined."""

@@ -771,6 +771,18 @@ int prt_debug_wide(prt_ctx* ctx, uint32_t* words) {
     return PRT_OK;
 }
 
+int prt_debug_wide_compact(prt_ctx* ctx, uint32_t* words, int capacity_nodes, int* n_nodes) {
+    if (!ctx || !n_nodes) return set_err(ctx ? &ctx->c : nullptr, PRT_ERR_INVALID, "prt_debug_wide_compact: NULL argument");
+    Ctx* c = &ctx->c;
+    if (!c->bvh_built || !c->wide_built || !c->wide_compacted) return set_err(c, PRT_ERR_INVALID, "prt_debug_wide_compact: no compact wide nodes (option wide_compact, scenes with wide nodes)");
+    *n_nodes = c->wide_live;
+    if (!words) return PRT_OK;
+    if (capacity_nodes < c->wide_live) return set_err(c, PRT_ERR_INVALID, "prt_debug_wide_compact: buffer too small");
+    PRT_CUDA(c, cudaSetDevice(c->device));
+    PRT_CUDA(c, cudaMemcpy(words, c->wnodes_c.p, (size_t)c->wide_live * sizeof(WideNode), cudaMemcpyDeviceToHost));
+    return PRT_OK;
+}
+
 int prt_enable_counters(prt_ctx* ctx, int on) {
     if (!ctx) return set_err(nullptr, PRT_ERR_INVALID, "prt_enable_counters: ctx is NULL");
     ctx->c.counters_on = on ? 1 : 0;

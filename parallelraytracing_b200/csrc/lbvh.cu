@@ -904,67 +904,88 @@ unsigned lbvh_check_flags() {
 // ------------------------------------------------------------------ compact wide nodes (option wide_compact)
 // k_emit_wide writes a record for EVERY internal node (any of them could be a wide root); the walk only ever reaches the ones a
 // reachable record names as a slot - about 45 % - so half of every 128-byte line of that array is dead weight in L1 and L2.
-// One breadth-first pass from the root copies the reachable records into a dense array: a node's internal children get
-// consecutive new indices (one atomicAdd per node), so siblings share cache lines, and the parent's copy is written with
-// the new indices in place. Cooperative launch: one grid.sync per level. The order within a level depends on the timing of
-// the atomics: the layout is not reproducible, the walk (order of visits, results, counters) is the same as on the full array.
-__global__ void __launch_bounds__(256) k_compact_wide(const WideNode* __restrict__ wide, WideNode* __restrict__ out, int* __restrict__ qa, int* __restrict__ qb,
-                                                      int* __restrict__ ctl /* [0..2] frontier counts of levels L, L+1, L+2 (rotating), [3] nodes placed */) {
+// One breadth-first pass from the root copies the reachable records into a dense array: level after level, in frontier order,
+// a node's internal children get consecutive new indices (siblings share cache lines) and the parent's copy is written with
+// the new indices in place. Deterministic: every CTA owns a contiguous piece of the frontier, counts its children (pass A),
+// and after a grid.sync takes the sum of the CTAs before it as its base (pass B) - no atomics, the same layout on every run
+// and every device. Cooperative launch, two grid.sync per level; frontier entries are (old index, new index) pairs.
+constexpr int CW_T = 256;
+__device__ __forceinline__ int cw_kids(const WideNode& w, int kid[4]) {
+    int nk = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const bool empty = ((w.qlo[0] >> (8 * k)) & 255u) == 255u && ((w.qhi[0] >> (8 * k)) & 255u) == 0u;
+        kid[k] = (!empty && w.code[k] >= 0) ? 1 : 0;
+        nk += kid[k];
+    }
+    return nk;
+}
+__device__ __forceinline__ int cw_block_sum(int v, int* s_w) {          // all CW_T threads; returns the sum to every thread
+    for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+    __syncthreads();
+    if ((threadIdx.x & 31u) == 0u) s_w[threadIdx.x >> 5] = v;
+    __syncthreads();
+    int t = 0;
+#pragma unroll
+    for (int k = 0; k < CW_T / 32; ++k) t += s_w[k];
+    return t;
+}
+__global__ void __launch_bounds__(CW_T) k_compact_wide(const WideNode* __restrict__ wide, WideNode* __restrict__ out, int* __restrict__ qa, int* __restrict__ qb,
+                                                       int* __restrict__ cta_tot /* 2 x gridDim: children per CTA, double-buffered by level */) {
     cg::grid_group grid = cg::this_grid();
-    const int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
-    if (tid == 0) { qa[0] = 0; qa[1] = 0; ctl[0] = 1; ctl[1] = 0; ctl[2] = 0; ctl[3] = 1; }     // frontier entries: (old index, new index) pairs
+    __shared__ int s_w[CW_T / 32];
+    const int B = (int)gridDim.x, b = (int)blockIdx.x, t = (int)threadIdx.x, lane = t & 31, wid = t >> 5;
+    if (b == 0 && t == 0) { qa[0] = 0; qa[1] = 0; }
     grid.sync();
+    int cnt = 1, placed = 1;                                             // the same on every CTA: all of them add up the same totals
     int* fa = qa; int* fb = qb;
-    for (int level = 0; level < 4096; ++level) {
-        const int cnt = ((volatile int*)ctl)[level % 3];
-        if (cnt == 0) break;
-        int* cnt_next = ctl + (level + 1) % 3;
-        if (tid == 0) ctl[(level + 2) % 3] = 0;                           // the counter of the level after next: nobody reads or adds to it now
-        for (int i0 = tid & ~31; i0 < cnt; i0 += nth) {                  // whole warps: the two counters take ONE atomic per warp
-            const int i = i0 + (int)(threadIdx.x & 31u);
-            const bool act = i < cnt;
-            int old_i = 0, new_i = 0;
-            WideNode w;
-            int kid[4] = {0, 0, 0, 0}; int nk = 0;
+    for (int level = 0; cnt > 0; ++level) {
+        int* tot = cta_tot + (level & 1) * B;
+        const int chunk = (((cnt + B - 1) / B + CW_T - 1) / CW_T) * CW_T;
+        const int lo = min(cnt, b * chunk), hi = min(cnt, lo + chunk);
+        int my = 0;                                                      // pass A: internal children of my piece of the frontier
+        for (int i = lo + t; i < hi; i += CW_T) { int kid[4]; const WideNode w = wide[fa[2 * i]]; my += cw_kids(w, kid); }
+        my = cw_block_sum(my, s_w);
+        if (t == 0) tot[b] = my;
+        grid.sync();
+        int before = 0, all = 0;                                         // pass B: my base = the children of the CTAs before me
+        for (int k = t; k < B; k += CW_T) { const int v = __ldcg(&tot[k]); all += v; if (k < b) before += v; }
+        before = cw_block_sum(before, s_w);
+        all = cw_block_sum(all, s_w);
+        int run = before;
+        for (int i0 = lo; i0 < hi; i0 += CW_T) {
+            const int i = i0 + t;
+            const bool act = i < hi;
+            WideNode w; int kid[4] = {0, 0, 0, 0}; int nk = 0, new_i = 0;
+            if (act) { w = wide[fa[2 * i]]; new_i = fa[2 * i + 1]; nk = cw_kids(w, kid); }
+            int incl = nk;                                               // block-wide exclusive prefix of nk
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += v; }
+            __syncthreads();
+            if (lane == 31) s_w[wid] = incl;
+            __syncthreads();
+            int wbase = 0, ctotal = 0;
+#pragma unroll
+            for (int k = 0; k < CW_T / 32; ++k) { const int v = s_w[k]; if (k < wid) wbase += v; ctotal += v; }
             if (act) {
-                old_i = fa[2 * i]; new_i = fa[2 * i + 1];
-                w = wide[old_i];
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const bool empty = ((w.qlo[0] >> (8 * k)) & 255u) == 255u && ((w.qhi[0] >> (8 * k)) & 255u) == 0u;
-                    kid[k] = (!empty && w.code[k] >= 0) ? 1 : 0;
-                    nk += kid[k];
-                }
-            }
-            int incl = nk;                                               // warp prefix of the child counts
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, d); if ((int)(threadIdx.x & 31u) >= d) incl += v; }
-            const int total = __shfl_sync(0xffffffffu, incl, 31);
-            int base_new = 0, base_q = 0;
-            if ((threadIdx.x & 31u) == 31u && total) { base_new = atomicAdd(&ctl[3], total); base_q = atomicAdd(cnt_next, total); }
-            base_new = __shfl_sync(0xffffffffu, base_new, 31) + incl - nk;
-            base_q = __shfl_sync(0xffffffffu, base_q, 31) + incl - nk;
-            if (!act) continue;
-            if (nk) {
-                int j = 0;
+                int pos = run + wbase + incl - nk;
 #pragma unroll
                 for (int k = 0; k < 4; ++k)
-                    if (kid[k]) {
-                        fb[2 * (base_q + j)] = w.code[k]; fb[2 * (base_q + j) + 1] = base_new + j;
-                        w.code[k] = base_new + j; ++j;
-                    }
-            }
-            // empty slots keep "the code of slot 0" (see WideNode)
+                    if (kid[k]) { fb[2 * pos] = w.code[k]; fb[2 * pos + 1] = placed + pos; w.code[k] = placed + pos; ++pos; }
 #pragma unroll
-            for (int k = 1; k < 4; ++k) {
-                const bool empty = ((w.qlo[0] >> (8 * k)) & 255u) == 255u && ((w.qhi[0] >> (8 * k)) & 255u) == 0u;
-                if (empty) w.code[k] = w.code[0];
+                for (int k = 1; k < 4; ++k) {                            // empty slots keep "the code of slot 0" (see WideNode)
+                    const bool empty = ((w.qlo[0] >> (8 * k)) & 255u) == 255u && ((w.qhi[0] >> (8 * k)) & 255u) == 0u;
+                    if (empty) w.code[k] = w.code[0];
+                }
+                out[new_i] = w;
             }
-            out[new_i] = w;
+            run += ctotal;
         }
+        placed += all; cnt = all;
+        int* x = fa; fa = fb; fb = x;
         grid.sync();
-        int* t = fa; fa = fb; fb = t;
     }
+    if (b == 0 && t == 0) cta_tot[2 * B] = placed;                       // records in the dense array
 }
 
 int lbvh_build(Ctx* c) {
@@ -1073,14 +1094,15 @@ int lbvh_build(Ctx* c) {
             c->wide_built = true;
             c->wide_compacted = false;
             if (c->wide_compact && n > 2) {
-                if ((rc = dev_reserve(c, c->wnodes_c, nn * sizeof(WideNode))) || (rc = dev_reserve(c, c->wc_queue, nn * 16 + 64))) return rc;
+                if ((rc = dev_reserve(c, c->wnodes_c, nn * sizeof(WideNode))) || (rc = dev_reserve(c, c->wc_queue, nn * 16 + 8 * (size_t)c->num_sms * 16 + 64))) return rc;
                 const WideNode* src = (const WideNode*)c->wnodes.p; WideNode* dst = (WideNode*)c->wnodes_c.p;
-                int* qa = (int*)c->wc_queue.p; int* qb = qa + 2 * nn; int* ctl = qb + 2 * nn;
+                int* qa = (int*)c->wc_queue.p; int* qb = qa + 2 * nn; int* ctl = qb + 2 * nn;       // ctl: 2 x grid CTA totals
                 int per_sm = 0;
                 PRT_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_compact_wide, 256, 0));
                 const int grid = std::max(1, std::min((n + 255) / 256, c->num_sms * std::max(1, per_sm)));
                 void* args[] = {&src, &dst, &qa, &qb, &ctl};
                 PRT_CUDA(c, cudaLaunchCooperativeKernel((const void*)k_compact_wide, dim3(grid), dim3(256), args, 0, st));
+                PRT_CUDA(c, cudaMemcpyAsync(&c->wide_live, ctl + 2 * grid, sizeof(int), cudaMemcpyDeviceToHost, st));   // read after the sync below
                 c->wide_compacted = true;
             }
         }

@@ -64,8 +64,9 @@ struct Ctx {
     int bvh_wide = -1;                          // 4-wide quantised nodes for the staged extend: 1 always, 0 never, -1 by scene size
     int wide_min_prims = 4096;                  // auto: below this the two-child tree is L1-resident and its cheaper node step wins
     bool wide_built = false;
-    int wide_compact = 1;                       // copy the reachable wide nodes (~45 %) into a dense, breadth-first array (lbvh.cu:k_compact_wide): soup 10 M +2.7 %, dragon 960 K +1.1 %, build +0.55 / +0.17 ms
+    int wide_compact = 1;                       // copy the reachable wide nodes (~45 %) into a dense, breadth-first array (lbvh.cu:k_compact_wide): soup 10 M +2.7 %, dragon 960 K +1.3 %, build +0.82 / +0.25 ms
     bool wide_compacted = false;
+    int wide_live = 0;                          // records in the dense array
     DevBuf wnodes_c, wc_queue;
     DevBuf ploc_code, ploc_box, ploc_status, ploc_ctl;   // PLOC scratch: cluster codes (2 x n), boxes (the other half is node_min), tile status, control words
     int bvh_builder = 1;                        // hierarchy over the sorted leaves: 1 PLOC (falls back to Karras when it fails), 0 Karras (plain LBVH)

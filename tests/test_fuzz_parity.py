@@ -240,3 +240,53 @@ def test_builder_at_boundary_sizes_vs_oracle(oracle):
                     assert (st.nodes_visited, st.prims_tested) == (int(cnt[0]), int(cnt[1])), (n, dups, builder)
     finally:
         ctx.close()
+
+
+def compact_wide_reference(full):
+    """Host restatement of lbvh.cu:k_compact_wide: breadth-first from record 0, frontier in order, a node's internal children
+    (slots in order, empty slots = qlo byte 255 and qhi byte 0 on x) get the next free indices; empty slots take slot 0's code."""
+    out = []
+    frontier = [(0, 0)]                                      # (old index, new index)
+    placed = 1
+    code = full[:, 4:8].view(np.int32)
+    while frontier:
+        nxt = []
+        for old, new in frontier:
+            w = full[old].copy(); c = w[4:8].view(np.int32)
+            empty = [((int(w[8]) >> (8 * k)) & 255) == 255 and ((int(w[11]) >> (8 * k)) & 255) == 0 for k in range(4)]
+            for k in range(4):
+                if not empty[k] and code[old, k] >= 0:
+                    nxt.append((int(code[old, k]), placed)); c[k] = placed; placed += 1
+            for k in range(1, 4):
+                if empty[k]:
+                    c[k] = c[0]
+            out.append((new, w))
+        frontier = nxt
+    arr = np.zeros((placed, 16), np.uint32)
+    for new, w in out:
+        arr[new] = w
+    return arr
+
+
+@pytest.mark.gpu
+def test_compact_wide_nodes_are_the_breadth_first_copy():
+    """The dense array the walk reads = the reachable records of prt_debug_wide's array in breadth-first order with remapped
+    child indices, byte for byte (so: deterministic), for both builders and sizes around the CTA / grid chunking of the pass;
+    about half of the records are reachable."""
+    from parallelraytracing_b200.capi import Context
+    ctx = Context(0)
+    try:
+        for n in (3, 4, 9, 257, 4097, 30000, 200000):
+            sd = S.random_triangle_soup(n, seed=3 * n)
+            for builder in (1, 0):
+                ctx.set_option("bvh_builder", builder); ctx.set_option("bvh_wide", 1)
+                ctx.set_scene_build(sd)
+                full, got = ctx.debug_wide(), ctx.debug_wide_compact()
+                want = compact_wide_reference(full)
+                assert got.shape == want.shape and got.tobytes() == want.tobytes(), (n, builder)
+                if n >= 4097:
+                    assert 0.3 < len(got) / len(full) < 0.7
+                ctx.set_scene_build(sd)                        # again: the same bytes
+                assert ctx.debug_wide_compact().tobytes() == got.tobytes()
+    finally:
+        ctx.close()

@@ -120,3 +120,46 @@ def test_random_scenes_vs_live_reference(ref, oracle, seed):
     assert m["flips"] <= 0.01 * m["n"], m
     assert m["rmse_nonflip"] <= IMG_TOL["rmse_nonflip"] and m["max_rel_nonflip"] <= IMG_TOL["max_rel_nonflip"], m
     assert abs(rays_n - ref_rays) <= 0.01 * ref_rays + 8
+
+
+@pytest.mark.parametrize("seed", list(range(12)))
+def test_random_triangle_scenes_vs_live_reference(ref, oracle, seed):
+    """Random triangles (some needle-thin, some sharing edges in a fan) as reference Triangle primitives - Moller-Trumbore,
+    shape.h:262-303 - against the oracle's watertight test: ids agree away from edges and near-ties, t / position within the
+    tolerance of the mesh test in test_oracle_pinned.py, interpolated normals within 2e-4."""
+    rng = np.random.default_rng(9000 + seed)
+    L = float(10.0 ** rng.uniform(-0.5, 1.5))
+    nt = int(rng.integers(20, 400))
+    c = rng.uniform(-1, 1, (nt, 1, 3)) * L
+    tv = c + rng.standard_normal((nt, 3, 3)) * L * rng.uniform(0.02, 0.5, (nt, 1, 1))
+    k = nt // 8
+    tv[:k, 1] = tv[:k, 0] + (tv[:k, 1] - tv[:k, 0]) * 0.02                       # needles
+    apex = rng.uniform(-1, 1, 3) * L
+    ring = apex + L * 0.4 * np.stack([np.cos(np.arange(9) * 0.7), np.sin(np.arange(9) * 0.7), np.full(9, 0.5)], 1)
+    tv = np.concatenate([tv, np.stack([np.repeat(apex[None], 8, 0), ring[:-1], ring[1:]], 1)]).astype(np.float32)
+    fn = np.cross(tv[:, 1] - tv[:, 0], tv[:, 2] - tv[:, 0]).astype(np.float32)
+    tn = (np.repeat(fn[:, None, :], 3, 1) + rng.standard_normal(tv.shape).astype(np.float32) * 0.1 * np.linalg.norm(fn, axis=1)[:, None, None]).astype(np.float32)
+    rs = ref.new_scene()
+    rs.add_quad(6 * L, 6 * L, (1, 0.5, 0.5, 0.5, 0.0, (0, 0, 0)), trans=(0.0, float(np.float32(-1.5 * L)), 0.0))
+    rs.add_triangles(tv, tn, (1, 0.8, 0.3, 0.3, 0.0, (0, 0, 0)))
+    sd = rs.flatten("reftri%d" % seed)
+    assert sd.n_tris == len(tv) and np.array_equal(sd.tri_verts.reshape(-1, 3, 3), tv)
+    rays = np.concatenate([util.fixed_ray_batch(sd, 6000, seed=seed + 1, clamp_extent=3 * L), util.incoherent_rays(3000, L, seed=seed + 2)])
+    ref_hits, second = rs.trace_batch(rays)
+    osc = oracle.scene(sd)
+    brute = osc.trace_batch(rays, use_bvh=0)
+    for mode in (1, 2):
+        assert np.array_equal(osc.trace_batch(rays, use_bvh=mode), brute), mode
+    with np.errstate(invalid="ignore"):
+        near = np.abs(second - ref_hits["t"]) <= 1e-4 * np.maximum(1.0, ref_hits["t"])
+    idm = ref_hits["prim_id"] != brute["prim_id"]
+    assert (idm & ~near).sum() <= 4, (idm & ~near).sum()                          # edge-grazing rays: MT and the watertight test may differ
+    ok = (ref_hits["prim_id"] >= 0) & ~idm
+    assert ok.sum() > 500
+    tol = 3e-4 * np.maximum(1.0, np.maximum(ref_hits["t"][ok], L))
+    assert np.all(np.abs(ref_hits["t"][ok] - brute["t"][ok]) <= tol)
+    for k2 in ("px", "py", "pz"):
+        assert np.all(np.abs(ref_hits[k2][ok] - brute[k2][ok]) <= tol), k2
+    for k2 in ("nx", "ny", "nz"):
+        assert np.all(np.abs(ref_hits[k2][ok] - brute[k2][ok]) <= 2e-4), k2
+    assert (ref_hits["front"][ok] == brute["front"][ok]).mean() > 0.999

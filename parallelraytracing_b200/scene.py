@@ -115,6 +115,31 @@ def _transform(scale, euler_deg, trans):
     return (r0 * sx).astype(f32), (r1 * sy).astype(f32), (r2 * sz).astype(f32), _v3(*trans)
 
 
+def _inverse_row1(c0, c1, c2, t):
+    """(Mi[0][1], Mi[1][1], Mi[2][1]) of Mi = glm::inverse(M), M = [c0 c1 c2 t; 0 0 0 1] (glm is column-major: m[col][row]),
+    with the operations and their order of glm/detail/func_matrix.inl compute_inverse<4,4> in float32 - what
+    TransformNormal(Mi, (0,1,0)) reads (geometry.h:139-148, primitive.cpp:39)."""
+    m = [[f32(c0[0]), f32(c0[1]), f32(c0[2]), f32(0)], [f32(c1[0]), f32(c1[1]), f32(c1[2]), f32(0)],
+         [f32(c2[0]), f32(c2[1]), f32(c2[2]), f32(0)], [f32(t[0]), f32(t[1]), f32(t[2]), f32(1)]]
+
+    def coef(a, b, c, d):                       # m[a0][a1]*m[b0][b1] - m[c0][c1]*m[d0][d1]
+        return f32(f32(m[a[0]][a[1]] * m[b[0]][b[1]]) - f32(m[c[0]][c[1]] * m[d[0]][d[1]]))
+    C00 = coef((2, 2), (3, 3), (3, 2), (2, 3)); C04 = coef((2, 1), (3, 3), (3, 1), (2, 3)); C08 = coef((2, 1), (3, 2), (3, 1), (2, 2))
+    C12 = coef((2, 0), (3, 3), (3, 0), (2, 3)); C16 = coef((2, 0), (3, 2), (3, 0), (2, 2)); C20 = coef((2, 0), (3, 1), (3, 0), (2, 1))
+
+    def comb(a, fa, b, fb, c, fc):              # a*fa - b*fb + c*fc, left to right
+        return f32(f32(f32(a * fa) - f32(b * fb)) + f32(c * fc))
+    inv0x = comb(m[1][1], C00, m[1][2], C04, m[1][3], C08); inv0y = comb(m[0][1], C00, m[0][2], C04, m[0][3], C08)
+    inv1x = comb(m[1][0], C00, m[1][2], C12, m[1][3], C16); inv1y = comb(m[0][0], C00, m[0][2], C12, m[0][3], C16)
+    inv2x = comb(m[1][0], C04, m[1][1], C12, m[1][3], C20); inv2y = comb(m[0][0], C04, m[0][1], C12, m[0][3], C20)
+    inv3x = comb(m[1][0], C08, m[1][1], C16, m[1][2], C20)
+    row0 = [inv0x, f32(-inv1x), inv2x, f32(-inv3x)]                                   # Inverse[k][0]: SignA / SignB
+    d = [f32(m[0][k] * row0[k]) for k in range(4)]
+    det = f32(f32(d[0] + d[1]) + f32(d[2] + d[3]))
+    ood = f32(f32(1) / det)
+    return _v3(f32(f32(-inv0y) * ood), f32(inv1y * ood), f32(f32(-inv2y) * ood))
+
+
 class SceneBuilder:
     """Appends primitives in list order (list index = prim_id, the tie-break of
     PrimitiveList::Intersect, primitive.cpp:44) and flattens them like host/flatten.h."""
@@ -145,7 +170,7 @@ class SceneBuilder:
     def add_quad(self, width, height, mat, scale=(1, 1, 1), euler=(0, 0, 0), trans=(0, 0, 0)):
         c0, c1, c2, t = _transform(scale, euler, trans)
         s0, s1, s2 = _length(c0), _length(c1), _length(c2)
-        u, v, n = (c0 / s0).astype(f32), (c2 / s2).astype(f32), _normalize(c1)
+        u, v, n = (c0 / s0).astype(f32), (c2 / s2).astype(f32), _normalize(_inverse_row1(c0, c1, c2, t))   # the normal goes through glm::inverse, like flatten.h
         self._quads.append((t[0], t[1], t[2], f32(f32(f32(width) / f32(2)) * s0), u[0], u[1], u[2],
                             f32(f32(f32(height) / f32(2)) * s2), v[0], v[1], v[2], f32(K_SHAPE_RAY_TMIN * s1),
                             n[0], n[1], n[2], mat, self._n, (0, 0, 0)))

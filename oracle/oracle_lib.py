@@ -219,17 +219,17 @@ class Ref:
 
     def camera(self, cam):
         out = CCamera()
-        self.lib.ref_camera(_ptr(cam.pos), _ptr(cam.front), cam.width, cam.height, C.byref(out))
+        self.lib.ref_camera(_ptr(cam.pos), _ptr(cam.front_in), cam.width, cam.height, C.byref(out))
         return out
 
     def camera_dirs(self, cam):
         out = np.empty((cam.height, cam.width, 3), np.float32)
-        self.lib.ref_camera_dirs(_ptr(cam.pos), _ptr(cam.front), cam.width, cam.height, _ptr(out))
+        self.lib.ref_camera_dirs(_ptr(cam.pos), _ptr(cam.front_in), cam.width, cam.height, _ptr(out))
         return out
 
     def render_shipped(self, preset, cam, spp, want_accum=True):
         acc = np.zeros((cam.height, cam.width, 3), np.float32) if want_accum else None
-        sec = self.lib.ref_render_shipped(int(preset), _ptr(cam.pos), _ptr(cam.front), cam.width, cam.height, spp, _ptr(acc))
+        sec = self.lib.ref_render_shipped(int(preset), _ptr(cam.pos), _ptr(cam.front_in), cam.width, cam.height, spp, _ptr(acc))
         return sec, acc
 
     def film_display(self, accum_sum, spp, exposure=1.0, gamma=2.2):
@@ -308,13 +308,13 @@ class RefScene:
     def render(self, cam, spp, depth, seed=1, sample_begin=0, n_threads=8, accum=None, y_begin=0, y_end=0):
         if accum is None:
             accum = np.zeros((cam.height, cam.width, 3), np.float32)
-        rays = self.lib.ref_render(self.h, _ptr(cam.pos), _ptr(cam.front), cam.width, cam.height, spp, depth, seed,
+        rays = self.lib.ref_render(self.h, _ptr(cam.pos), _ptr(cam.front_in), cam.width, cam.height, spp, depth, seed,
                                    sample_begin, _ptr(accum), n_threads, y_begin, y_end)
         return accum, int(rays)
 
     def trace_pixel(self, cam, x, y, sample, depth, seed=1):
         out = np.zeros(3, np.float32)
-        self.lib.ref_trace_pixel(self.h, _ptr(cam.pos), _ptr(cam.front), cam.width, cam.height, x, y, sample, depth, seed, _ptr(out))
+        self.lib.ref_trace_pixel(self.h, _ptr(cam.pos), _ptr(cam.front_in), cam.width, cam.height, x, y, sample, depth, seed, _ptr(out))
         return out
 
 

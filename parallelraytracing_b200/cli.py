@@ -75,7 +75,7 @@ def main(argv=None):
         pos = np.asarray(args.camera_pos if args.camera_pos is not None else (5.0, 5.0, 8.0), dtype=np.float32)
         front = S._normalize(np.asarray(args.camera_target, dtype=np.float32) - pos)
         cam = S.Camera(pos=tuple(float(x) for x in pos), front=front)
-    cam = S.Camera(pos=tuple(float(x) for x in cam.pos), front=cam.front, width=args.width, height=args.height)
+    cam = S.Camera(pos=tuple(float(x) for x in cam.pos), front=cam.front_in, width=args.width, height=args.height)
 
     film = Film(args.width, args.height)
     devices = [int(d) for d in args.devices.split(",")] if args.devices else None

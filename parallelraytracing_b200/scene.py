@@ -321,7 +321,8 @@ class Camera:
         self.pos = _v3(*pos)
         if front is None:                          # main.cpp:142-150: normalize(0 - pos)
             front = _normalize((_v3(0, 0, 0) - self.pos).astype(f32))
-        self.front = _v3(*front)
+        self.front_in = _v3(*front)                # what the caller hands to Camera(position, front, ...): pass THIS on when copying a camera
+        self.front = _normalize(self.front_in)     # the reference ctor normalises it (camera.h:13), main.cpp's already normalised vector included
         self.width, self.height = int(width), int(height)
 
     @property

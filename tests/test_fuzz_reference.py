@@ -158,3 +158,21 @@ def test_random_triangle_scenes_vs_live_reference(ref, oracle, seed):
     for k2 in ("nx", "ny", "nz"):
         assert np.all(np.abs(ref_hits[k2][ok] - brute[k2][ok]) <= 2e-4), k2
     assert (ref_hits["front"][ok] == brute["front"][ok]).mean() > 0.999
+
+
+def test_random_cameras_vs_live_reference(ref, oracle):
+    """Camera::GetCameraRay (camera.h:104-132) for random positions, view directions and film sizes: the oracle's directions and
+    the host mirror's camera struct against the reference's, bit for bit."""
+    rng = np.random.default_rng(123)
+    for k in range(40):
+        pos = tuple(float(x) for x in (rng.uniform(-50, 50, 3)).astype(np.float32))
+        f = rng.standard_normal(3)
+        if k % 5 == 0:
+            f = np.array([0.0, 0.0, -1.0]) if k % 10 == 0 else np.array([1.0, 0.0, 0.0])
+        f = (f / np.linalg.norm(f)).astype(np.float32)
+        if abs(float(f[1])) > 0.999:                         # looking straight up or down: Right = cross(Front, worldUp) degenerates in the reference too
+            continue
+        W, H = int(rng.integers(1, 97)), int(rng.integers(1, 65))
+        cam = S.Camera(pos=pos, front=tuple(float(x) for x in f), width=W, height=H)
+        want = ref.camera_dirs(cam)
+        assert np.array_equal(oracle.camera_dirs(cam), want), (k, pos, f, W, H)

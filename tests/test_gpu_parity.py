@@ -766,7 +766,7 @@ def test_full_size_mesh_vs_oracle(oracle, big_scenes, name):
             assert (stt.nodes_visited, stt.prims_tested) == (int(cnt[0]), int(cnt[1])), mode
             assert (got["prim_id"] >= 0).mean() > 0.05
         c.enable_counters(False)
-        band = S.Camera(pos=tuple(cam.pos), front=tuple(cam.front), width=cam.width, height=cam.height)
+        band = S.Camera(pos=tuple(cam.pos), front=tuple(cam.front_in), width=cam.width, height=cam.height)
         y0 = cam.height // 2 - 32
         c.set_camera(band); c.clear_accum()
         c.render_region(1, w["depth"], seed=3, pixel_begin=y0 * cam.width, pixel_count=64 * cam.width)

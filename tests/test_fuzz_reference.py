@@ -176,3 +176,48 @@ def test_random_cameras_vs_live_reference(ref, oracle):
         cam = S.Camera(pos=pos, front=tuple(float(x) for x in f), width=W, height=H)
         want = ref.camera_dirs(cam)
         assert np.array_equal(oracle.camera_dirs(cam), want), (k, pos, f, W, H)
+
+
+def test_random_scatter_records_vs_live_reference(ref, oracle):
+    """MaterialHandle::Scatter / Emit (material.h:11-161) on 4 000 random records - all four materials, roughness and ior over
+    their ranges (ior below 1 and exactly 1 included), random incoming directions and hit normals (facing the ray or not),
+    both face flags, the interposed rand() stream of (seed, pixel, sample, bounce): decision, attenuation, direction and
+    emission bit for bit."""
+    rng = np.random.default_rng(4242)
+    n_scat = 0
+    for k in range(4000):
+        t = int(rng.integers(1, 5))
+        rgb = [float(x) for x in rng.uniform(0, 1, 3).astype(np.float32)]
+        par = float(np.float32(rng.choice([0.0, 0.05, 0.3, 1.0, 2.5]) if t == 2 else rng.choice([0.5, 1.0, 1.33, 1.5, 2.4]) if t == 3 else 0.0))
+        if t == 4:
+            rgb = [float(x) for x in rng.uniform(0, 20, 3).astype(np.float32)]
+        mat = (t, rgb[0], rgb[1], rgb[2], par, (0, 0, 0))
+        d = rng.standard_normal(3); d = (d / np.linalg.norm(d)).astype(np.float32)
+        nrm = rng.standard_normal(3); nrm /= np.linalg.norm(nrm)
+        if k % 4 and float(np.dot(nrm, d)) > 0:
+            nrm = -nrm                                       # three quarters of the normals face the ray, as Intersect delivers them
+        nrm = nrm.astype(np.float32)
+        front = int(rng.integers(0, 2))
+        key = (int(rng.integers(0, 2 ** 31)), int(rng.integers(0, 1 << 21)), int(rng.integers(0, 4096)), int(rng.integers(0, 32)))
+        ok, a, o, e = ref.scatter(mat, d, np.zeros(3, np.float32), nrm, front, *key)
+        got = oracle.scatter(mat, d, nrm, front, *key)
+        assert bool(got[0]) == ok, (k, mat)
+        assert np.array_equal(got[7:10], e), (k, mat, "emission")
+        if ok:
+            n_scat += 1
+            assert np.array_equal(got[1:4], a), (k, mat, "attenuation")
+            assert got[4:7].tobytes() == o.tobytes() or np.array_equal(got[4:7], o), (k, mat, got[4:7], o)
+    assert 2000 < n_scat < 3900
+
+
+def test_random_film_resolve_vs_live_reference(ref, oracle):
+    """Film::UpdateDisplay (film.cu:134-194): accumulated radiance over nine decades, zeros, negative values and infinities,
+    several sample counts, exposures and gammas - RGBA8 exact."""
+    rng = np.random.default_rng(99)
+    for k in range(12):
+        a = (10.0 ** rng.uniform(-6, 3, (24, 40, 3))).astype(np.float32)
+        a[rng.random(a.shape) < 0.05] = 0.0
+        a[rng.random(a.shape) < 0.02] *= -1.0
+        a[0, 0] = np.inf; a[0, 1, 1] = 0.0
+        spp = int(rng.choice([1, 3, 16, 1000])); exposure = float(np.float32(rng.choice([0.25, 1.0, 4.0]))); gamma = float(np.float32(rng.choice([1.0, 2.2, 2.4])))
+        assert np.array_equal(oracle.resolve_display(a, spp, exposure, gamma), ref.film_display(a, spp, exposure, gamma)), (k, spp, exposure, gamma)

@@ -221,3 +221,58 @@ def test_random_film_resolve_vs_live_reference(ref, oracle):
         a[0, 0] = np.inf; a[0, 1, 1] = 0.0
         spp = int(rng.choice([1, 3, 16, 1000])); exposure = float(np.float32(rng.choice([0.25, 1.0, 4.0]))); gamma = float(np.float32(rng.choice([1.0, 2.2, 2.4])))
         assert np.array_equal(oracle.resolve_display(a, spp, exposure, gamma), ref.film_display(a, spp, exposure, gamma)), (k, spp, exposure, gamma)
+
+
+def _write_ply_variant(path, v, n, f, rng):
+    """A random legal spelling of the same mesh: ascii or binary little-endian, int or uint indices, uchar or ushort list
+    counts, comments, an extra vertex property the loaders must skip, normals present or not."""
+    ascii_ = bool(rng.integers(0, 2)); idx_t = ["int", "uint"][int(rng.integers(0, 2))]
+    extra = bool(rng.integers(0, 2)); name = "vertex_indices"            # the only spelling mesh.cpp asks tinyply for (load_ply also takes vertex_index)
+    head = "ply\nformat %s 1.0\ncomment made by the fuzz\n" % ("ascii" if ascii_ else "binary_little_endian")
+    head += "element vertex %d\nproperty float x\nproperty float y\nproperty float z\n" % len(v)
+    if n is not None:
+        head += "property float nx\nproperty float ny\nproperty float nz\n"
+    if extra:
+        head += "property uchar red\n"
+    head += "element face %d\nproperty list uchar %s %s\nend_header\n" % (len(f), idx_t, name)
+    cols = [v] + ([n] if n is not None else [])
+    with open(path, "wb") as fh:
+        fh.write(head.encode())
+        if ascii_:
+            for i in range(len(v)):
+                row = " ".join(repr(float(x)) for c in cols for x in c[i]) + (" %d" % (i % 256) if extra else "")
+                fh.write((row + "\n").encode())
+            for t in f:
+                fh.write(("3 %d %d %d\n" % tuple(int(x) for x in t)).encode())
+        else:
+            dt = [("p", "<f4", (3 * len(cols),))] + ([("c", "u1")] if extra else [])
+            rec = np.zeros(len(v), dtype=dt)
+            rec["p"] = np.concatenate(cols, axis=1)
+            if extra:
+                rec["c"] = np.arange(len(v)) % 256
+            fh.write(rec.tobytes())
+            fr = np.zeros(len(f), dtype=[("k", "u1"), ("i", "<i4" if idx_t == "int" else "<u4", (3,))])
+            fr["k"] = 3; fr["i"] = f
+            fh.write(fr.tobytes())
+
+
+def test_random_ply_files_vs_live_reference(ref, tmp_path):
+    """scene.load_ply against the reference's Mesh (tinyply, mesh.cpp:23-184) on random spellings of random meshes: positions,
+    normals (the file's, or the ones the loader makes when the file has none) and indices, bit for bit."""
+    rng = np.random.default_rng(2024)
+    for k in range(24):
+        nv, nf = int(rng.integers(3, 200)), int(rng.integers(1, 300))
+        v = (rng.standard_normal((nv, 3)) * 10.0 ** rng.uniform(-2, 2)).astype(np.float32)
+        f = rng.integers(0, nv, (nf, 3)).astype(np.uint32)
+        n = None
+        if k % 3:
+            n = rng.standard_normal((nv, 3)).astype(np.float32)
+        path = str(tmp_path / ("fuzz%d.ply" % k))
+        _write_ply_variant(path, v, n, f, rng)
+        rv, rn, rf = ref.load_mesh(path)
+        mv, mn, mf = S.load_ply(path)
+        assert np.array_equal(mv, rv) and np.array_equal(np.asarray(mf).reshape(-1, 3), rf), k
+        if rn is None:
+            assert mn is None or len(mn) == 0, k
+        else:
+            assert mn is not None and mn.tobytes() == rn.tobytes(), k

@@ -664,8 +664,13 @@ __device__ __forceinline__ int sq_batch(const SceneView& sc, float* __restrict__
 }
 
 
+// Resident CTAs per SM asked for k_shade (48 / 56 registers unconstrained = 5 / 4 CTAs). Same box, Mrays/s dragon 960 K 64 spp /
+// 809 spheres 64 spp: unconstrained 7 670 / 9 410, 5 CTAs 7 777 / 9 578, 6 CTAs 7 733 / 9 540.
+#ifndef PRT_SHADE_MIN_BLOCKS
+#define PRT_SHADE_MIN_BLOCKS 5
+#endif
 template <bool FAST, bool PRIMARY = false>
-__global__ void __launch_bounds__(WF_THREADS)
+__global__ void __launch_bounds__(WF_THREADS, PRT_SHADE_MIN_BLOCKS)
 k_shade(SceneView sc, const float4* __restrict__ qo, const float4* __restrict__ qd, const float4* __restrict__ qb,
         const float4* __restrict__ hits, float4* __restrict__ no, float4* __restrict__ nd, float4* __restrict__ nb,
         float4* __restrict__ contrib, uint32_t* __restrict__ qcount, int bounce, int max_depth, PrimaryGen pg) {
